@@ -1,0 +1,194 @@
+// internal.h -- shared declarations of the sr459 CUDA engine (not part of the public ABI).
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <atomic>
+#include <vector>
+#include "../../include/sr459.h"
+
+namespace sr459 {
+
+// ---- error plumbing ---------------------------------------------------------
+void set_error(const char* fmt, ...);
+extern std::atomic<uint64_t> g_launches;
+inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+#define SR_CUDA(call)                                                                       \
+    do {                                                                                    \
+        cudaError_t _e = (call);                                                            \
+        if (_e != cudaSuccess) {                                                            \
+            sr459::set_error("%s failed at %s:%d: %s", #call, __FILE__, __LINE__,           \
+                             cudaGetErrorString(_e));                                       \
+            return SR459_ECUDA;                                                             \
+        }                                                                                   \
+    } while (0)
+
+#define SR_LAUNCH_CHECK(name)                                                               \
+    do {                                                                                    \
+        cudaError_t _e = cudaGetLastError();                                                \
+        if (_e != cudaSuccess) {                                                            \
+            sr459::set_error("launch of %s failed at %s:%d: %s", name, __FILE__, __LINE__,  \
+                             cudaGetErrorString(_e));                                       \
+            return SR459_ECUDA;                                                             \
+        }                                                                                   \
+        sr459::count_launch();                                                              \
+    } while (0)
+
+#define SR_TRY(call)                                                                        \
+    do {                                                                                    \
+        int _r = (call);                                                                    \
+        if (_r != SR459_OK) return _r;                                                      \
+    } while (0)
+
+// ---- cubic B-spline machinery (scipy.ndimage restated; see spline.cu) ---------
+constexpr int   kPad       = 12;      // scipy _prepad_for_spline_filter(mode='nearest')
+constexpr float kPoleF     = -0.26794919243112270647f;   // sqrt(3) - 2
+constexpr float kSqrt3F    = 1.73205080756887729353f;
+
+struct AxisTap {            // one output sample along one axis: 4 taps into the coefficient line
+    int   idx[4];
+    float w[4];
+};
+
+// how the prefilter kernel reads its (virtual) input image
+enum SrcMode : int {
+    SRC_PLAIN      = 0,     // the array itself, mirror boundary            (zoom path)
+    SRC_EDGEPAD    = 1,     // np.pad(a, 12, 'edge'), reflect boundary      (shift path)
+    SRC_ZI_EDGEPAD = 2      // zero-inserted LR residual -> HR, then as 1   (back_project path)
+};
+
+struct PrefilterJob {
+    const float* src;       // source image
+    float*       dst;       // coefficient image, ny x nx, pitch nx
+    int sh, sw;             // source dims
+    int vh, vw;             // virtual (unpadded) dims: == sh,sw except SRC_ZI_EDGEPAD (HR dims)
+    int ny, nx;             // coefficient dims (vh+24, vw+24 for the padded modes)
+    int mode;
+    int factor;             // zero-insert stride for SRC_ZI_EDGEPAD
+};
+
+int launch_prefilter2d(const PrefilterJob* h_jobs, int njobs, cudaStream_t st);
+
+// host-side table builders (double precision, converted to float weights)
+void build_zoom_axis(int n_in, int n_out, std::vector<AxisTap>& out);
+// shift tables: output o = 0..n_out-1 at stride `stride` (decimation), coordinate o*stride - s + 12
+void build_shift_axis(int n, double s, int n_out, int stride, std::vector<AxisTap>& out);
+
+// out[y,x] = scale * sum_k R_k(y,x);   tables stacked per frame: ty[k*Hout + y], tx[k*Wout + x]
+struct ResampleSumArgs {
+    const float* coef[8];
+    int   cpitch[8];
+    int   n;
+    const AxisTap* ty;
+    const AxisTap* tx;
+    int   Hout, Wout;
+    float scale;
+    float* out;
+};
+int launch_resample_sum(const ResampleSumArgs& a, cudaStream_t st);
+
+// per frame k: sim = R_k(i,j); if lr: err = lr_k - sim stored to out_k and sum(err^2) -> partial sums
+struct ResampleErrArgs {
+    const float* coef;      // shared coefficient image (prefiltered padded blur)
+    int   cpitch;
+    int   n;
+    const AxisTap* ty;      // [k*h + i]
+    const AxisTap* tx;      // [k*w + j]
+    int   h, w;
+    const float* lr[8];     // may be all null -> store sim
+    float* out[8];
+    double* partial;        // [gridDim.x*gridDim.y*n] or null
+};
+int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_out);
+
+// ---- correlation / convolution ------------------------------------------------
+// out[y,x] = sum_t w[t] * in0[y+dy[t], x+dx[t]]   (zero outside), taps with w==0 dropped
+struct TapList {
+    int    ntaps = 0;
+    int    reach = 0;       // max |dy|,|dx|
+    float* d_w   = nullptr; // device
+    int*   d_dy  = nullptr;
+    int*   d_dx  = nullptr;
+    std::vector<float> w; std::vector<int> dy, dx;   // host copies
+};
+// true convolution 'same' with k (flip=false) or with k[::-1, ::-1] (flip=true)
+void build_taps_host(const double* k, int kh, int kw, bool flip, TapList& t);
+int  upload_taps(TapList& t);
+void free_taps(TapList& t);
+
+struct CorrArgs {
+    const float* in; int H, W;
+    const TapList* taps;
+    float* out;
+    // epilogue: mode 0 -> out = v ; mode 1 -> out = clamp(base + alpha*v, lo, hi)
+    int mode; const float* base; float alpha, lo, hi;
+};
+int launch_corr2d(const CorrArgs& a, cudaStream_t st);
+
+// ---- fused integer-shift IBP iteration ------------------------------------------
+constexpr int kMaxFrames = 8;
+constexpr int kMaxIntShift = 4;
+
+struct IbpGeom {
+    int H, W, h, w;                 // global HR / LR dims (factor 2)
+    int n;
+    int sy[kMaxFrames], sx[kMaxFrames];   // integer HR shifts
+    int smax;
+    float alpha, lo, hi;            // step/n, clip bounds
+    // local buffers (row bands): local hr row 0 == global row hr_lo, rows [hr_lo, hr_hi) present
+    int hr_lo, hr_hi;
+    int lr_lo, lr_hi;               // LR rows present in the local LR buffers
+    // rows this launch may update / LR rows whose residuals it counts
+    int upd_y0, upd_y1;             // HR rows (even bounds)
+    int own_i0, own_i1;             // LR rows
+};
+
+struct Rect { int y0, x0, y1, x1; };
+
+struct DenseArgs {
+    IbpGeom g;
+    const float* lr[kMaxFrames];
+    const float* hr_in;
+    float* hr_out;
+    const float* wf; const int* fdy; const int* fdx; int nf;   // forward taps (device)
+    const float* wb; const int* bdy; const int* bdx; int nb;   // backward taps
+    int R;                          // tap reach
+    Rect rect[4]; int nrect;        // regions (even bounds) tiled by tile_h x tile_w
+    int tile_h, tile_w;
+    int tiles_before[5];            // prefix sums of tiles per rect
+    int tiles_x[4];
+    double* partial;                // one slot per CTA (this launch's slice)
+};
+int launch_ibp_dense(const DenseArgs& a, cudaStream_t st);
+size_t ibp_dense_smem(int R, int smax, int tile_h, int tile_w, int nf, int nb);
+
+struct FastArgs {
+    IbpGeom g;
+    const float* lr[kMaxFrames];
+    const float* hr_in;
+    float* hr_out;
+    float psf[49];                  // 7x7 (R=3) row-major k[u][v]; smaller odd kernels centred & zero padded
+    Rect interior;                  // pixels this kernel may store (even bounds, x multiple of 4)
+    int phase_mask;                 // bit (p*2+q) set when some frame has shift parity (p,q)
+    int tiles_x, tiles_y;
+    int ty_origin;                  // global HR row of tile row 0 (even)
+    double* partial;
+};
+int  launch_ibp_fast(const FastArgs& a, cudaStream_t st);
+bool ibp_fast_supported(int kh, int kw, int smax);
+void ibp_fast_tile(int* th, int* tw);
+
+// errors[it] = sum(partials of iteration it) * scale
+int launch_reduce_partials(const double* partial, int per_iter, int n_iter, double scale,
+                           double* d_errors, cudaStream_t st);
+
+// ---- misc kernels (misc.cu) -------------------------------------------------------
+int launch_u8_to_f32(const uint8_t* in, int64_t n, float* out, cudaStream_t st);
+int launch_f32_to_u8(const float* in, int64_t n, uint8_t* out, cudaStream_t st);
+int launch_extract_red(const void* in, int is_f32, int H, int W, int ro, int co, float* out, cudaStream_t st);
+int launch_mean_frames(const float* const* h_frames, int n, int64_t npx, float* out, cudaStream_t st);
+int launch_argmax(const void* imgs, int is_f32, int n_img, int64_t npx, long long* d_out /*n_img packed*/, cudaStream_t st);
+int launch_patch_sum(const void* imgs, int is_f32, int n_img, int H, int W, const int* d_peaks, int margin,
+                     double* d_patch /* (2m+1)^2 */, cudaStream_t st);
+
+}  // namespace sr459

@@ -1,0 +1,140 @@
+// misc.cu -- frame ingest / egress and measured-PSF reductions.
+//
+//   load_gray        uint8 -> float            mono_cal_target/run_sr.py:73-75
+//   extract_red      img[0::2, 0::2]           rgb_cal_target/run_sr.py:73-75
+//   np.mean(frames)  rep / frame averaging     run_sr.py:274, rgb_cal_target/run_sr.py:107-108
+//   uint8 cast       clip(0,255) + truncation  run_sr.py:303
+//   load_measured_psf: argmax (first maximum, row-major) and 19x19 patch mean
+//                                              run_sr.py:127, :132, :137
+#include "internal.h"
+
+namespace sr459 {
+
+__global__ void k_u8_to_f32(const uint8_t* __restrict__ in, int64_t n, float* __restrict__ out) {
+    int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
+    if (i4 + 3 < n && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
+        uchar4 v = *reinterpret_cast<const uchar4*>(in + i4);
+        *reinterpret_cast<float4*>(out + i4) = make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w);
+    } else {
+        for (int64_t i = i4; i < n && i < i4 + 4; ++i) out[i] = (float)in[i];
+    }
+}
+
+int launch_u8_to_f32(const uint8_t* in, int64_t n, float* out, cudaStream_t st) {
+    if (n <= 0) return SR459_OK;
+    int64_t nt = (n + 3) / 4;
+    k_u8_to_f32<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(in, n, out);
+    SR_LAUNCH_CHECK("k_u8_to_f32");
+    return SR459_OK;
+}
+
+__global__ void k_f32_to_u8(const float* __restrict__ in, int64_t n, uint8_t* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float v = fminf(fmaxf(in[i], 0.0f), 255.0f);
+    out[i] = (uint8_t)(int)v;          // truncation toward zero, like ndarray.astype(np.uint8)
+}
+
+int launch_f32_to_u8(const float* in, int64_t n, uint8_t* out, cudaStream_t st) {
+    if (n <= 0) return SR459_OK;
+    k_f32_to_u8<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, n, out);
+    SR_LAUNCH_CHECK("k_f32_to_u8");
+    return SR459_OK;
+}
+
+template <typename T>
+__global__ void k_extract_red(const T* __restrict__ in, int H, int W, int ro, int co, int oh, int ow,
+                              float* __restrict__ out) {
+    int j = blockIdx.x * blockDim.x + threadIdx.x;
+    int i = blockIdx.y * blockDim.y + threadIdx.y;
+    if (i >= oh || j >= ow) return;
+    out[(size_t)i * ow + j] = (float)in[(size_t)(2 * i + ro) * W + 2 * j + co];
+}
+
+int launch_extract_red(const void* in, int is_f32, int H, int W, int ro, int co, float* out, cudaStream_t st) {
+    int oh = (H - ro + 1) / 2, ow = (W - co + 1) / 2;
+    if (oh <= 0 || ow <= 0) return SR459_OK;
+    dim3 block(32, 8), grid((ow + 31) / 32, (oh + 7) / 8);
+    if (is_f32) k_extract_red<float><<<grid, block, 0, st>>>((const float*)in, H, W, ro, co, oh, ow, out);
+    else        k_extract_red<uint8_t><<<grid, block, 0, st>>>((const uint8_t*)in, H, W, ro, co, oh, ow, out);
+    SR_LAUNCH_CHECK("k_extract_red");
+    return SR459_OK;
+}
+
+struct FramePtrs { const float* p[32]; };
+
+__global__ void k_mean_frames(FramePtrs f, int n, int64_t npx, float fn, float* __restrict__ out) {
+    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npx) return;
+    float s = 0.0f;
+    for (int k = 0; k < n; ++k) s += __ldg(f.p[k] + i);
+    out[i] = s / fn;
+}
+
+int launch_mean_frames(const float* const* h_frames, int n, int64_t npx, float* out, cudaStream_t st) {
+    if (n < 1 || n > 32) { set_error("mean_frames supports 1..32 frames, got %d", n); return SR459_EINVAL; }
+    FramePtrs f;
+    for (int k = 0; k < n; ++k) f.p[k] = h_frames[k];
+    k_mean_frames<<<(unsigned)((npx + 255) / 256), 256, 0, st>>>(f, n, npx, (float)n, out);
+    SR_LAUNCH_CHECK("k_mean_frames");
+    return SR459_OK;
+}
+
+// ---- argmax: first maximum in row-major order (np.argmax) -------------------------------------
+// key = (value-bits << 32) | (0xffffffff - index): a max over keys picks the largest value and,
+// among equals, the smallest index.  Pixel values are non-negative so float bits order correctly.
+template <typename T>
+__global__ void k_argmax(const T* __restrict__ imgs, int64_t npx, unsigned long long* __restrict__ out) {
+    const T* img = imgs + (size_t)blockIdx.y * npx;
+    unsigned long long best = 0ULL;
+    for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < npx; i += (int64_t)gridDim.x * blockDim.x) {
+        float v = (float)img[i];
+        unsigned long long key = ((unsigned long long)__float_as_uint(v) << 32) | (unsigned long long)(0xffffffffu - (unsigned)i);
+        best = key > best ? key : best;
+    }
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        unsigned long long other = __shfl_xor_sync(0xffffffffu, best, o);
+        best = other > best ? other : best;
+    }
+    if ((threadIdx.x & 31) == 0) atomicMax(out + blockIdx.y, best);
+}
+
+int launch_argmax(const void* imgs, int is_f32, int n_img, int64_t npx, long long* d_out, cudaStream_t st) {
+    if (npx >= (1LL << 32)) { set_error("image too large for argmax key"); return SR459_EUNSUPPORTED; }
+    SR_CUDA(cudaMemsetAsync(d_out, 0, sizeof(long long) * n_img, st));
+    dim3 grid(296, n_img);
+    if (is_f32) k_argmax<float><<<grid, 256, 0, st>>>((const float*)imgs, npx, (unsigned long long*)d_out);
+    else        k_argmax<uint8_t><<<grid, 256, 0, st>>>((const uint8_t*)imgs, npx, (unsigned long long*)d_out);
+    SR_LAUNCH_CHECK("k_argmax");
+    return SR459_OK;
+}
+
+// patch[py,px] = sum over accepted images of img[pr-m+py, pc-m+px]   (double accumulation)
+template <typename T>
+__global__ void k_patch_sum(const T* __restrict__ imgs, int n_img, int H, int W, const int* __restrict__ peaks,
+                            int margin, double* __restrict__ patch) {
+    int side = 2 * margin + 1;
+    int t = blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= side * side) return;
+    int py = t / side, px = t - py * side;
+    double s = 0.0;
+    for (int k = 0; k < n_img; ++k) {
+        int pr = peaks[2 * k], pc = peaks[2 * k + 1];
+        if (pr < 0) continue;
+        s += (double)imgs[(size_t)k * H * W + (size_t)(pr - margin + py) * W + (pc - margin + px)];
+    }
+    patch[t] = s;
+}
+
+int launch_patch_sum(const void* imgs, int is_f32, int n_img, int H, int W, const int* d_peaks, int margin,
+                     double* d_patch, cudaStream_t st) {
+    int side = 2 * margin + 1;
+    int nt = side * side;
+    if (is_f32) k_patch_sum<float><<<(nt + 127) / 128, 128, 0, st>>>((const float*)imgs, n_img, H, W, d_peaks, margin, d_patch);
+    else        k_patch_sum<uint8_t><<<(nt + 127) / 128, 128, 0, st>>>((const uint8_t*)imgs, n_img, H, W, d_peaks, margin, d_patch);
+    SR_LAUNCH_CHECK("k_patch_sum");
+    return SR459_OK;
+}
+
+}  // namespace sr459

@@ -1,0 +1,147 @@
+/* sr459.h -- C ABI of the B200-native SAA / SAA+IBP super-resolution engine.
+ *
+ * This is the drop-in boundary for the hot path of the reference's four
+ * run_sr.py scripts (benedikthoward/ENPH459-Super-Resolution).  The reference
+ * has no FFI layer of its own -- its "operator API" is a set of module-level
+ * Python functions -- so every entry point below names the reference function
+ * (file:line in mono_cal_target/run_sr.py unless noted) it replaces.  The
+ * Python mirror of that surface (enph459-super-resolution_b200/ops.py) binds
+ * these symbols with ctypes; INTEGRATION.md shows the stub a maintainer of the
+ * reference would add.
+ *
+ * Conventions
+ *   - return 0 on success, a negative SR459_E* code otherwise; never throws.
+ *     sr459_last_error() returns a thread-local human-readable message.
+ *   - every image pointer named d_* is CALLER-OWNED DEVICE memory: float32,
+ *     row-major, pitch == width (tensor.data_ptr() of a contiguous CUDA
+ *     tensor).  Pointers named h_* are host memory.
+ *   - stream is a cudaStream_t passed as void* (0 = legacy default stream).
+ *     Functions enqueue work and return without synchronising unless the
+ *     description says otherwise.
+ *   - a plan owns its scratch buffers and tables; one plan must not be used
+ *     from two host threads at once; distinct plans are independent.
+ *   - there is no CPU fallback anywhere behind this ABI.
+ */
+#ifndef SR459_H
+#define SR459_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+#if defined(__GNUC__)
+#pragma GCC visibility push(default)   /* the library is built with -fvisibility=hidden */
+#endif
+
+#define SR459_OK            0
+#define SR459_EINVAL       -1   /* bad argument (shape mismatch, null pointer, ...) */
+#define SR459_ECUDA        -2   /* a CUDA runtime call or kernel launch failed      */
+#define SR459_ENOMEM       -3
+#define SR459_EUNSUPPORTED -4
+
+typedef struct sr459_plan sr459_plan;
+
+/* ---- library ---------------------------------------------------------- */
+int         sr459_version(void);                 /* 100*major + minor */
+const char* sr459_last_error(void);
+/* number of CUDA kernels this library has launched since load (per process);
+ * bench.py reports the delta over its timed region as gpu_launches.          */
+uint64_t    sr459_launch_count(void);
+
+/* ---- PSF construction ------------------------------------------------- */
+/* make_gaussian_psf(size, sigma)                     run_sr.py:104-111.
+ * out must hold (2*(size/2)+1)^2 doubles (the reference builds mgrid[-hw:hw+1]). */
+int sr459_psf_gaussian(int size, double sigma, double* h_out);
+
+/* load_measured_psf(psf_dir)                         run_sr.py:114-152,
+ * with the PNG decode done by the caller.  d_imgs: n_img images, uint8
+ * (is_f32==0) or float32 (is_f32==1), each H x W, contiguous one after the
+ * other.  For every image the first-maximum argmax is found on the device
+ * (run_sr.py:127), images whose peak is within halfwidth+6 of an edge are
+ * skipped (:128-131), the (2*(halfwidth+6)+1)^2 patches are averaged (:137), the
+ * centre (2*halfwidth+1)^2 is cut (:141-142), the mean of the four 3x3 corner
+ * blocks subtracted (:144-148), clipped at 0 and normalised (:149-150).
+ * h_peaks (2*n_img ints, may be NULL) receives (row, col) per image, or (-1,-1)
+ * for skipped ones; *h_n_used the number of patches.  Synchronises the stream. */
+int sr459_psf_measured(const void* d_imgs, int is_f32, int n_img, int H, int W,
+                       int halfwidth, double* h_out, int* h_peaks, int* h_n_used,
+                       void* stream);
+
+/* ---- frame ingest / egress (load_gray, extract_red, rep-mean, uint8 cast) -- */
+/* load_gray for a mono PNG: uint8 -> float32           run_sr.py:73-75        */
+int sr459_u8_to_f32(const uint8_t* d_in, int64_t n, float* d_out, void* stream);
+/* extract_red: out[i,j] = in[2i+row_off, 2j+col_off]  rgb_cal_target/run_sr.py:73-75
+ * in is H x W uint8 (is_f32==0) or float32; out is ceil((H-row_off)/2) x ceil((W-col_off)/2) f32 */
+int sr459_extract_red(const void* d_in, int is_f32, int H, int W, int row_off, int col_off,
+                      float* d_out, void* stream);
+/* np.mean(frames, axis=0) over n_frames device images  run_sr.py:274, rgb_cal_target/run_sr.py:107-108 */
+int sr459_mean_frames(const float* const* h_d_frames, int n_frames, int64_t n_px,
+                      float* d_out, void* stream);
+/* np.clip(img,0,255).astype(np.uint8)  (truncation)    run_sr.py:303          */
+int sr459_f32_to_u8(const float* d_in, int64_t n, uint8_t* d_out, void* stream);
+
+/* ---- stand-alone operators (the reference's module-level functions) ---- */
+/* blur(img, kernel) = fftconvolve(img, kernel, 'same')  run_sr.py:157-158.
+ * h_psf is kh x kw doubles; zero-padded true convolution.                    */
+int sr459_blur(const float* d_img, int H, int W, const double* h_psf, int kh, int kw,
+               float* d_out, void* stream);
+/* scipy.ndimage.zoom(a, factor, order=3), defaults      call sites run_sr.py:185, :279.
+ * out is round(h*factor) x round(w*factor).                                   */
+int sr459_zoom(const float* d_in, int h, int w, int factor, float* d_out, void* stream);
+/* scipy.ndimage.shift(a, (sy,sx), order=3, mode='nearest')  call sites :163,:176,:186 */
+int sr459_shift(const float* d_in, int H, int W, double sy, double sx, float* d_out, void* stream);
+/* forward_model(hr, kernel, shift_yx, factor)           run_sr.py:161-165.
+ * out is ceil(H/factor) x ceil(W/factor).                                     */
+int sr459_forward_model(const float* d_hr, int H, int W, const double* h_psf, int kh, int kw,
+                        double dy, double dx, int factor, float* d_out_lr, void* stream);
+/* back_project(err, kernel, shift_yx, factor, hr_shape)  run_sr.py:168-178    */
+int sr459_back_project(const float* d_err, int h, int w, const double* h_psf, int kh, int kw,
+                       double dy, double dx, int factor, int H, int W, float* d_out_hr,
+                       void* stream);
+
+/* ---- plans: Native-2x, SAA, SAA+IBP on a fixed geometry ---------------- */
+/* Geometry: n_frames LR frames of h x w, HR = (factor*h) x (factor*w).
+ * h_shifts_yx: 2*n_frames doubles, (dy,dx) per frame in LR pixels (the
+ * reference's shifts_lr).  h_psf: kh x kw doubles.  step / clip_lo / clip_hi are
+ * ibp()'s step and the literals 0 and 255 of run_sr.py:205.                   */
+int sr459_plan_create(sr459_plan** out, int device, int n_frames, int h, int w, int factor,
+                      const double* h_shifts_yx, const double* h_psf, int kh, int kw,
+                      double step, double clip_lo, double clip_hi);
+void sr459_plan_destroy(sr459_plan* plan);
+
+/* 1 if every factor*shift is an integer (closed-form fused IBP kernels are
+ * used), 0 if the cubic-spline warp path is used.                            */
+int sr459_plan_is_integer(const sr459_plan* plan);
+/* Force a code path, for tests: 0 = automatic, 1 = generic stage-by-stage path,
+ * 2 = dense fused integer kernel everywhere, 3 = fast interior + dense border. */
+int sr459_plan_set_path(sr459_plan* plan, int path);
+/* Bytes of device scratch the plan holds.                                     */
+int64_t sr459_plan_scratch_bytes(const sr459_plan* plan);
+
+/* Native-2x: ndi_zoom(mean_lr, factor, order=3)         run_sr.py:279         */
+int sr459_native2x(sr459_plan* plan, const float* d_mean_lr, float* d_hr, void* stream);
+/* shift_and_add(lr_list, shifts, factor, order=3)       run_sr.py:181-187.
+ * h_d_lr: host array of n_frames device pointers.                             */
+int sr459_saa(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, void* stream);
+/* ibp(lr_list, shifts, kernel, hr_init, factor, n_iter, step)  run_sr.py:190-209.
+ * d_hr_inout holds hr_init on entry and the result on exit (the Python mirror
+ * copies hr_init first, as the reference does at :191).  If h_errors != NULL it
+ * receives the n_iter per-iteration MSE values (errors list, :206) and the call
+ * synchronises the stream; with NULL nothing is synchronised and the values
+ * can be fetched later with sr459_ibp_errors().                               */
+int sr459_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr_inout, int n_iter,
+              double* h_errors, void* stream);
+int sr459_ibp_errors(sr459_plan* plan, int n_iter, double* h_errors, void* stream);
+/* SAA followed by IBP in one call (process_session, run_sr.py:284-292):
+ * d_hr receives the SAA+IBP result; d_saa (may be NULL) a copy of the SAA image. */
+int sr459_saa_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, float* d_saa,
+                  int n_iter, double* h_errors, void* stream);
+
+#if defined(__GNUC__)
+#pragma GCC visibility pop
+#endif
+#ifdef __cplusplus
+}
+#endif
+#endif /* SR459_H */

@@ -1,0 +1,11 @@
+"""Import alias: ``import sr459`` is ``enph459-super-resolution_b200`` (whose directory
+name, fixed by the project layout, is not a valid Python identifier)."""
+import importlib as _importlib
+import os as _os
+import sys as _sys
+
+_root = _os.path.abspath(_os.path.join(_os.path.dirname(__file__), ".."))
+if _root not in _sys.path:
+    _sys.path.insert(0, _root)
+_pkg = _importlib.import_module("enph459-super-resolution_b200")
+_sys.modules[__name__] = _pkg

@@ -1,0 +1,340 @@
+"""GPU parity: the CUDA path (through the C ABI) against the oracle and the committed
+reference-generated golden vectors.  Tolerances are those of BASELINE.json's north_star:
+max-abs <= 1e-4 on [0,1] images (0.0255 on the reference's [0,255] scale), |dPSNR| < 0.01 dB,
+MSE vector rel-err <= 1e-4; integer decisions (argmax, shapes) exact."""
+import numpy as np
+import pytest
+
+from conftest import TOL_ABS_255, TOL_MSE_REL, TOL_PSNR_DB, golden
+from oracle import sr_oracle as O
+
+pytestmark = pytest.mark.gpu
+
+NOMINAL = [(+0.5, -0.5), (+0.5, +0.5), (-0.5, -0.5), (-0.5, +0.5)]
+CALIBRATED = [(0.47225, -0.43385), (0.4897, 0.4641), (-0.4798, -0.4553), (-0.4856, 0.4369)]
+
+
+def _close(a, b, tol=TOL_ABS_255, what=""):
+    d = O.max_abs(a, b)
+    assert d <= tol, f"{what}: max abs diff {d:.3e} > {tol:.3e}"
+
+
+def _errs_close(e, ref, what=""):
+    e, ref = np.asarray(e), np.asarray(ref)
+    assert e.shape == ref.shape
+    rel = np.max(np.abs(e - ref) / np.maximum(np.abs(ref), 1e-12))
+    assert rel <= TOL_MSE_REL, f"{what}: MSE rel err {rel:.3e}"
+
+
+# ---------------------------------------------------------------- primitives
+def test_gaussian_psf_matches_reference(sr):
+    g = golden("g_int4")
+    k = sr.make_gaussian_psf()
+    assert k.shape == (7, 7)
+    assert np.max(np.abs(k - g["psf"])) < 1e-15
+    assert sr.make_gaussian_psf(6, 2.0).shape == (7, 7)   # reference builds mgrid[-hw:hw+1]
+    np.testing.assert_allclose(sr.make_gaussian_psf(5, 0.7), O.make_gaussian_psf(5, 0.7), rtol=0, atol=1e-15)
+
+
+def test_measured_psf_exact_decisions_and_values(sr):
+    g = golden("g_psf")
+    crops = g["crops"]
+    k7, peaks, used = sr.measured_psf_from_images(list(crops), 3, return_peaks=True)
+    ok7, opeaks = O.measured_psf_from_images(list(crops), 3)
+    assert used == len(opeaks) == crops.shape[0]
+    assert [tuple(p) for p in peaks.tolist()] == opeaks          # argmax coordinates exact
+    assert np.array_equal(k7 == 0, g["k7"] == 0)                 # support / zero pattern exact
+    assert np.max(np.abs(k7 - g["k7"])) < 1e-14
+    k31 = sr.measured_psf_from_images(list(crops), 15)
+    assert k31.shape == (31, 31)
+    assert np.array_equal(k31 == 0, g["k31"] == 0)
+    assert np.max(np.abs(k31 - g["k31"])) < 1e-14
+
+
+def test_measured_psf_edge_skip(sr):
+    rng = np.random.default_rng(3)
+    imgs = [rng.integers(0, 50, (64, 80), dtype=np.uint8) for _ in range(4)]
+    for i, (r, c) in enumerate([(30, 40), (4, 40), (30, 75), (20, 20)]):
+        imgs[i][r, c] = 255
+    k, peaks, used = sr.measured_psf_from_images(imgs, 3, return_peaks=True)
+    ok, opeaks = O.measured_psf_from_images(imgs, 3)
+    assert used == 2 and peaks.tolist() == [[30, 40], [-1, -1], [-1, -1], [20, 20]]
+    assert np.max(np.abs(k - ok)) < 1e-14
+    with pytest.raises(Exception):
+        sr.measured_psf_from_images([imgs[1]], 3)
+
+
+def test_argmax_first_maximum_tie_break(sr):
+    img = np.zeros((40, 50), dtype=np.uint8)
+    img[25, 30] = 200
+    img[12, 33] = 200       # earlier in row-major order -> must win
+    img[12, 40] = 200
+    _, peaks, _ = sr.measured_psf_from_images([img], 1, return_peaks=True)
+    assert peaks.tolist() == [[12, 33]]
+
+
+def test_ingest_helpers(sr):
+    rng = np.random.default_rng(5)
+    raw = rng.integers(0, 256, (37, 52), dtype=np.uint8)
+    red = sr.extract_red(raw)
+    assert red.shape == (19, 26) and np.array_equal(red, raw[0::2, 0::2].astype(np.float64))
+    frames = [rng.integers(0, 256, (21, 34)).astype(np.float64) for _ in range(5)]
+    m = sr.mean_frames(frames)
+    assert np.max(np.abs(m - np.mean(frames, axis=0))) < 1e-4
+    x = rng.uniform(-20, 280, (33, 41))
+    assert np.array_equal(sr.to_uint8(x), np.clip(x.astype(np.float32), 0, 255).astype(np.uint8))
+
+
+@pytest.mark.parametrize("key", ["blur_gauss", "blur_k7", "blur_k31"])
+def test_blur_vs_reference_golden(sr, key):
+    g = golden("g_prims")
+    k = {"blur_gauss": golden("g_int4")["psf"], "blur_k7": g["k7"], "blur_k31": golden("g_psf")["k31"]}[key]
+    _close(sr.blur(g["a"], k), g[key], what=key)
+
+
+def test_blur_even_and_rectangular_kernels(sr):
+    rng = np.random.default_rng(6)
+    a = rng.uniform(0, 255, (45, 38))
+    for shape in [(1, 1), (2, 2), (4, 3), (5, 8), (3, 3)]:
+        k = rng.uniform(0, 1, shape)
+        k /= k.sum()
+        _close(sr.blur(a, k), O.conv2_same_zero(a, k), what=f"blur {shape}")
+
+
+def test_zoom_vs_reference_golden_and_odd_sizes(sr):
+    g = golden("g_prims")
+    _close(sr.ndi_zoom(g["e"], 2), g["zoom"], what="zoom golden")
+    rng = np.random.default_rng(7)
+    for shape in [(33, 47), (5, 3), (64, 96), (255, 257), (1, 9), (2, 2)]:
+        a = rng.uniform(0, 255, shape)
+        _close(sr.native_2x(a), O.ndi_zoom_cubic(a, 2), what=f"zoom {shape}")
+    a = rng.uniform(0, 255, (20, 31))
+    _close(sr.ndi_zoom(a, 3), O.ndi_zoom_cubic(a, 3), what="zoom x3")
+
+
+@pytest.mark.parametrize("s", [(1.0, -1.0), (0.0, 0.0), (0.9445, -0.8677), (-0.37, 0.61), (3.0, -2.0), (5.3, 7.9)])
+def test_shift_vs_oracle(sr, s):
+    rng = np.random.default_rng(8)
+    for shape in [(33, 47), (64, 96), (7, 5)]:
+        a = rng.uniform(0, 255, shape)
+        _close(sr.ndi_shift(a, s), O.ndi_shift_cubic_nearest(a, s), what=f"shift {s} {shape}")
+
+
+@pytest.mark.parametrize("tag,s", [("int", (0.5, -0.5)), ("frac", CALIBRATED[0]), ("zero", (0.0, 0.0))])
+def test_forward_and_back_project_vs_reference_golden(sr, tag, s):
+    g = golden("g_prims")
+    _close(sr.forward_model(g["a"], g["k7"], s, 2), g[f"fwd_{tag}"], what=f"forward {tag}")
+    _close(sr.back_project(g["e"], g["k7"], s, 2, g["a"].shape), g[f"bp_{tag}"], what=f"back_project {tag}")
+
+
+# ---------------------------------------------------------------- pipelines vs reference goldens
+def _run_pipeline(sr, lrs, shifts, psf, n_iter, path=0):
+    import torch
+    n, (h, w) = len(lrs), lrs[0].shape
+    plan = sr.Plan(n, h, w, shifts, psf)
+    if path:
+        plan.set_path(path)
+    dl = [torch.from_numpy(np.asarray(l, dtype=np.float32)).cuda() for l in lrs]
+    native = plan.native_2x(sr.mean_frames(dl)).cpu().numpy()
+    saa = plan.saa(dl)
+    hr = saa.clone()
+    errs = plan.ibp_(dl, hr, n_iter)
+    plan.close()
+    return native, saa.cpu().numpy(), hr.cpu().numpy(), errs
+
+
+def _check_against(g, native, saa, hr, errs, peak=255.0, scale=1.0, what=""):
+    tol = TOL_ABS_255 * scale
+    _close(native, g["native"], tol, what + " native")
+    _close(saa, g["saa"], tol, what + " saa")
+    _close(hr, g["ibp"], tol, what + " ibp")
+    _errs_close(errs, g["errors"], what + " errors")
+    if "truth" in g:
+        d = abs(O.psnr(hr, g["truth"], peak) - O.psnr(g["ibp"], g["truth"], peak))
+        assert d < TOL_PSNR_DB, f"{what}: PSNR differs by {d} dB"
+
+
+@pytest.mark.parametrize("path", [0, 1, 2, 3])
+@pytest.mark.parametrize("name", ["g_int4", "g_int5", "g_real"])
+def test_integer_shift_goldens_all_paths(sr, name, path):
+    g = golden(name)
+    lrs = list(g["lr"]) if "lr" in g else [g["raw"][k][0::2, 0::2].astype(np.float64) for k in range(4)]
+    res = _run_pipeline(sr, lrs, g["shifts"], g["psf"], len(g["errors"]), path)
+    _check_against(g, *res, what=f"{name} path{path}")
+
+
+def test_real_crop_uint8_outputs_exact(sr):
+    g = golden("g_real")
+    lrs = [sr.extract_red(g["raw"][k]) for k in range(4)]
+    native, saa, hr, errs = _run_pipeline(sr, lrs, g["shifts"], g["psf"], len(g["errors"]))
+    for got, ref in ((native, g["native"]), (saa, g["saa"])):
+        a, b = sr.to_uint8(got), O.to_uint8(ref)
+        # truncating cast: a float32 result an ulp below an integer may land one DN lower
+        bad = np.flatnonzero(a.ravel() != b.ravel())
+        assert bad.size <= 1e-4 * a.size
+        assert np.all(np.abs(a.ravel()[bad].astype(int) - b.ravel()[bad].astype(int)) == 1)
+        frac = np.abs(ref.ravel()[bad] - np.round(ref.ravel()[bad]))
+        assert np.all(frac < 1e-3)
+
+
+def test_fractional_shift_golden(sr):
+    g = golden("g_frac4")
+    res = _run_pipeline(sr, list(g["lr"]), g["shifts"], g["psf"], len(g["errors"]))
+    _check_against(g, *res, what="g_frac4")
+
+
+def test_unit_range_golden(sr):
+    """The BASELINE tolerance statement itself: [0,1] float32 frames, max-abs <= 1e-4."""
+    g = golden("g_unit")
+    res = _run_pipeline(sr, list(g["lr"]), g["shifts"], g["psf"], len(g["errors"]))
+    _check_against(g, *res, peak=1.0, scale=1.0 / 255.0, what="g_unit")
+
+
+# ---------------------------------------------------------------- module-level drop-in surface
+def test_dropin_functions_numpy_in_numpy_out(sr):
+    g = golden("g_int4")
+    lrs, shifts, psf = list(g["lr"]), [tuple(s) for s in g["shifts"]], g["psf"]
+    saa = sr.shift_and_add(lrs, shifts, factor=2, order=3)
+    assert isinstance(saa, np.ndarray) and saa.dtype == np.float64 and saa.shape == (66, 94)
+    _close(saa, g["saa"], what="saa")
+    init = saa.copy()
+    hr, errs = sr.ibp(lrs, shifts, psf, saa, factor=2, n_iter=8, step=0.5)
+    assert np.array_equal(saa, init), "hr_init must not be modified (reference copies it)"
+    assert isinstance(errs, list) and len(errs) == 8 and isinstance(errs[0], float)
+    _close(hr, g["ibp"], what="ibp")
+    _errs_close(errs, g["errors"])
+
+
+def test_dropin_functions_cuda_tensors(sr):
+    import torch
+    g = golden("g_int4")
+    lrs = [torch.from_numpy(l.astype(np.float32)).cuda() for l in g["lr"]]
+    saa = sr.shift_and_add(lrs, g["shifts"])
+    assert saa.is_cuda and saa.dtype == torch.float32
+    keep = saa.clone()
+    hr, errs = sr.ibp(lrs, g["shifts"], g["psf"], saa, n_iter=8)
+    assert torch.equal(saa, keep) and hr.data_ptr() != saa.data_ptr()
+    _close(hr.cpu().numpy(), g["ibp"], what="ibp cuda")
+
+
+def test_error_behaviour(sr):
+    g = golden("g_int4")
+    lrs = list(g["lr"])
+    with pytest.raises(ValueError):
+        sr.ibp(lrs, g["shifts"], g["psf"], np.zeros((10, 10)), n_iter=1)
+    with pytest.raises(ValueError):
+        sr.shift_and_add(lrs[:3], g["shifts"])
+    with pytest.raises(ValueError):
+        sr.shift_and_add([lrs[0], lrs[1][:-1]], g["shifts"][:2])
+    with pytest.raises(FileNotFoundError):
+        sr.load_measured_psf("/nonexistent/dir")
+    hr, errs = sr.ibp(lrs, g["shifts"], g["psf"], g["saa"], n_iter=0)
+    assert errs == [] and np.max(np.abs(hr - g["saa"])) < 1e-4
+
+
+# ---------------------------------------------------------------- oracle-diff on seeded inputs, borders
+@pytest.mark.parametrize("shape", [(33, 47), (64, 96), (20, 130), (6, 6), (2, 2)])
+@pytest.mark.parametrize("path", [1, 2, 3])
+def test_integer_paths_vs_oracle_odd_sizes(sr, shape, path):
+    rng = np.random.default_rng(459)
+    lrs = [rng.uniform(0, 255, shape) for _ in NOMINAL]
+    psf = O.make_gaussian_psf()
+    h, w = shape
+    if path == 3 and (w % 2):
+        pytest.skip("fast kernel needs W % 4 == 0")
+    saa_o = O.shift_and_add(lrs, NOMINAL)
+    hr_o, e_o = O.ibp(lrs, NOMINAL, psf, saa_o, n_iter=5)
+    native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 5, path)
+    _close(saa, saa_o, what="saa")
+    _close(hr, hr_o, what=f"ibp {shape} path{path}")
+    # borders separately from the interior
+    _close(hr[:8], hr_o[:8], what="top rows"); _close(hr[-8:], hr_o[-8:], what="bottom rows")
+    _close(hr[:, :8], hr_o[:, :8], what="left cols"); _close(hr[:, -8:], hr_o[:, -8:], what="right cols")
+    _errs_close(errs, e_o)
+
+
+@pytest.mark.parametrize("shifts", [
+    [(0.0, 0.0)],
+    [(0.0, 0.0), (0.5, 0.0), (0.0, 0.5), (0.5, 0.5)],
+    [(-0.5, -0.5), (0.5, 0.5)],
+    [(1.0, -1.5), (-2.0, 0.5), (0.0, 1.0)],
+    [(0.5, -0.5)] * 8,
+])
+def test_general_integer_shift_sets(sr, shifts):
+    rng = np.random.default_rng(11)
+    lrs = [rng.uniform(0, 255, (40, 52)) for _ in shifts]
+    psf = O.make_gaussian_psf()
+    saa_o = O.shift_and_add(lrs, shifts)
+    hr_o, e_o = O.ibp(lrs, shifts, psf, saa_o, n_iter=4)
+    for path in (0, 1, 2):
+        native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 4, path)
+        _close(saa, saa_o, what=f"saa {shifts}")
+        _close(hr, hr_o, what=f"ibp {shifts} path{path}")
+        _errs_close(errs, e_o)
+
+
+@pytest.mark.parametrize("ksize", [3, 5, 7, 9])
+def test_psf_sizes_integer_shifts(sr, ksize):
+    rng = np.random.default_rng(12)
+    lrs = [rng.uniform(0, 255, (48, 64)) for _ in NOMINAL]
+    psf = O.make_gaussian_psf(ksize, 0.8)
+    saa_o = O.shift_and_add(lrs, NOMINAL)
+    hr_o, e_o = O.ibp(lrs, NOMINAL, psf, saa_o, n_iter=4)
+    native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 4)
+    _close(hr, hr_o, what=f"psf {ksize}")
+    _errs_close(errs, e_o)
+
+
+def test_measured_psf_31_integer_and_fractional(sr):
+    g = golden("g_psf")
+    rng = np.random.default_rng(13)
+    lrs = [rng.uniform(0, 255, (40, 56)) for _ in NOMINAL]
+    for shifts in (NOMINAL, CALIBRATED):
+        saa_o = O.shift_and_add(lrs, shifts)
+        hr_o, e_o = O.ibp(lrs, shifts, g["k31"], saa_o, n_iter=3)
+        native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, g["k31"], 3)
+        _close(hr, hr_o, what="k31")
+        _errs_close(errs, e_o)
+
+
+def test_clip_is_active_and_matches(sr):
+    """S1 noise drives hr to both clip bounds (quirk Q5: literals 0 and 255)."""
+    rng = np.random.default_rng(14)
+    lrs = [rng.uniform(0, 255, (64, 96)) for _ in NOMINAL]
+    psf = O.make_gaussian_psf()
+    saa_o = O.shift_and_add(lrs, NOMINAL)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=30)
+    assert (hr_o == 0).any() and (hr_o == 255).any()
+    for path in (2, 3):
+        native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 30, path)
+        _close(hr, hr_o, what=f"clip path{path}")
+        _errs_close(errs, e_o)
+        assert hr.min() >= 0.0 and hr.max() <= 255.0
+
+
+# ---------------------------------------------------------------- full size, size-independent properties
+def test_full_size_fast_equals_dense_and_properties(sr):
+    """Config-1 shape (4x1536x2048 -> 3072x4096): the polyphase kernel against the literal dense
+    kernel on the GPU, SAA linearity, and a few oracle-checked windows."""
+    import torch
+    rng = np.random.default_rng(459)
+    h, w = 1536, 2048
+    lrs = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in NOMINAL]
+    psf = O.make_gaussian_psf()
+    plan = sr.Plan(4, h, w, NOMINAL, psf)
+    saa = plan.saa(lrs)
+    assert saa.shape == (3072, 4096)
+    # linearity of SAA: saa(2a+b) == 2saa(a)+saa(b)
+    other = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in NOMINAL]
+    mix = plan.saa([2 * a + b for a, b in zip(lrs, other)])
+    assert float((mix - (2 * saa + plan.saa(other))).abs().max()) < 2e-3
+    hr_fast = saa.clone(); e_fast = plan.set_path(3).ibp_(lrs, hr_fast, 6)
+    hr_dense = saa.clone(); e_dense = plan.set_path(2).ibp_(lrs, hr_dense, 6)
+    assert float((hr_fast - hr_dense).abs().max()) < 2e-3
+    np.testing.assert_allclose(e_fast, e_dense, rtol=1e-6)
+    assert all(b < a for a, b in zip(e_fast, e_fast[1:])), "IBP residual must decrease"
+    # oracle on a corner window: a 96x128 LR crop reproduces the top-left HR block exactly far from the cut
+    crop = [l[:96, :128].cpu().numpy().astype(np.float64) for l in lrs]
+    saa_c = O.shift_and_add(crop, NOMINAL)
+    _close(saa[:120, :160].cpu().numpy(), saa_c[:120, :160], what="full-size saa window")
+    plan.close()
