@@ -1,0 +1,136 @@
+"""Batched / streaming driver: independent frame sets through SAA + IBP on one GPU.
+
+The reference processes sessions and reps in plain ``for`` loops
+(mono_cal_target/run_sr.py:358-360, mono_barcodes/run_sr.py:301, :393-395); every
+iteration is an independent SR job.  On a B200 one job is a few milliseconds, so
+the PCIe copies either side of it matter as much as the kernels.  FrameSetPipeline
+keeps ``depth`` jobs in flight on three CUDA streams (H2D, compute, D2H) with
+pinned host staging, so the copy of job i+1 and the read-back of job i-1 overlap
+the kernels of job i.  Multi-GPU batch mode (one process per GPU) simply gives
+every rank its own pipeline and its own share of the frame sets: no collective is
+needed on the data path.
+"""
+from __future__ import annotations
+
+import time
+from typing import Iterable, List, Optional, Sequence
+
+import numpy as np
+
+from . import ops
+
+
+class FrameSetPipeline:
+    """SAA+IBP over a stream of frame sets with overlapped host<->device traffic.
+
+    in_dtype : 'f32' (synthetic / pre-converted frames) or 'u8' (camera / PNG frames,
+               converted on the device -- load_gray, run_sr.py:73-75)
+    out_dtype: 'f32' (the HR float image) or 'u8' (clip + truncation, run_sr.py:303)
+    """
+
+    def __init__(self, n_frames, h, w, shifts_yx, kernel, n_iter, factor=2, step=ops.IBP_STEP_SIZE,
+                 depth=3, in_dtype="f32", out_dtype="f32", device=None):
+        torch = ops._torch()
+        self.torch = torch
+        if device is not None:
+            torch.cuda.set_device(device)
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.plan = ops.Plan(n_frames, h, w, shifts_yx, kernel, factor, step)
+        self.n, self.h, self.w, self.n_iter = int(n_frames), int(h), int(w), int(n_iter)
+        self.H, self.W = self.plan.H, self.plan.W
+        self.depth = int(depth)
+        self.in_dtype, self.out_dtype = in_dtype, out_dtype
+        tin = torch.uint8 if in_dtype == "u8" else torch.float32
+        tout = torch.uint8 if out_dtype == "u8" else torch.float32
+        self.s_h2d, self.s_cmp, self.s_d2h = (torch.cuda.Stream() for _ in range(3))
+        self.slots = []
+        for _ in range(self.depth):
+            self.slots.append(dict(
+                raw=torch.empty((self.n, self.h, self.w), dtype=tin, device=self.dev),
+                lr=torch.empty((self.n, self.h, self.w), dtype=torch.float32, device=self.dev) if in_dtype == "u8" else None,
+                hr=torch.empty((self.H, self.W), dtype=torch.float32, device=self.dev),
+                out=torch.empty((self.H, self.W), dtype=torch.uint8, device=self.dev) if out_dtype == "u8" else None,
+                host_out=torch.empty((self.H, self.W), dtype=tout).pin_memory(),
+                ev_in=torch.cuda.Event(), ev_cmp=torch.cuda.Event(), ev_out=torch.cuda.Event(),
+                busy=False, errors=None,
+            ))
+        self.h2d_bytes = self.n * self.h * self.w * (1 if in_dtype == "u8" else 4)
+        self.d2h_bytes = self.H * self.W * (1 if out_dtype == "u8" else 4)
+        self._next = 0
+
+    def close(self):
+        self.plan.close()
+
+    # -- one job ------------------------------------------------------------------------
+    def _submit(self, slot, host_frames):
+        torch = self.torch
+        lib = ops._lib.load()
+        import ctypes as C
+        if slot["busy"]:
+            slot["ev_out"].synchronize()            # the slot's previous result has landed
+        with torch.cuda.stream(self.s_h2d):
+            self.s_h2d.wait_event(slot["ev_cmp"])   # previous compute on this slot is done with raw/lr
+            slot["raw"].copy_(host_frames, non_blocking=True)
+            slot["ev_in"].record(self.s_h2d)
+        with torch.cuda.stream(self.s_cmp):
+            self.s_cmp.wait_event(slot["ev_in"])
+            self.s_cmp.wait_event(slot["ev_out"])   # previous D2H of this slot finished reading hr/out
+            if self.in_dtype == "u8":
+                ops._lib.check(lib.sr459_u8_to_f32(ops._ptr(slot["raw"]), slot["raw"].numel(), ops._ptr(slot["lr"]),
+                                                   C.c_void_p(self.s_cmp.cuda_stream)))
+                frames = slot["lr"]
+            else:
+                frames = slot["raw"]
+            self.plan.saa_ibp([frames[k] for k in range(self.n)], self.n_iter, out=slot["hr"], want_errors=False)
+            if self.out_dtype == "u8":
+                ops._lib.check(lib.sr459_f32_to_u8(ops._ptr(slot["hr"]), slot["hr"].numel(), ops._ptr(slot["out"]),
+                                                   C.c_void_p(self.s_cmp.cuda_stream)))
+            slot["ev_cmp"].record(self.s_cmp)
+        with torch.cuda.stream(self.s_d2h):
+            self.s_d2h.wait_event(slot["ev_cmp"])
+            src = slot["out"] if self.out_dtype == "u8" else slot["hr"]
+            slot["host_out"].copy_(src, non_blocking=True)
+            slot["ev_out"].record(self.s_d2h)
+        slot["busy"] = True
+
+    def run(self, host_sets: Sequence, on_result=None, keep_results=False):
+        """Process pinned host tensors of shape (n, h, w); returns results (copies) if keep_results.
+
+        on_result(index, pinned_host_tensor) is called when a job's output has landed; the tensor is
+        only valid during the callback (its slot is re-used)."""
+        results = [] if keep_results else None
+        pending: List[tuple] = []
+        for idx, hs in enumerate(host_sets):
+            slot = self.slots[self._next]
+            self._next = (self._next + 1) % self.depth
+            if slot["busy"] and pending and pending[0][1] is slot:
+                i0, s0 = pending.pop(0)
+                s0["ev_out"].synchronize()
+                if on_result: on_result(i0, s0["host_out"])
+                if keep_results: results.append(s0["host_out"].clone())
+                s0["busy"] = False
+            self._submit(slot, hs)
+            pending.append((idx, slot))
+        for i0, s0 in pending:
+            s0["ev_out"].synchronize()
+            if on_result: on_result(i0, s0["host_out"])
+            if keep_results: results.append(s0["host_out"].clone())
+            s0["busy"] = False
+        return results
+
+    def run_latency(self, host_sets: Sequence):
+        """Unpipelined: per-job wall latency (submit -> result landed), seconds."""
+        lat = []
+        for hs in host_sets:
+            slot = self.slots[0]
+            t0 = time.perf_counter()
+            self._submit(slot, hs)
+            slot["ev_out"].synchronize()
+            slot["busy"] = False
+            lat.append(time.perf_counter() - t0)
+        return lat
+
+
+def shard_indices(n_items: int, rank: int, world: int) -> List[int]:
+    """Item i goes to rank i mod world (batch mode)."""
+    return list(range(rank, n_items, world))

@@ -380,6 +380,19 @@ def clamp_gather(a: np.ndarray, sy: int, sx: int) -> np.ndarray:
     return a[np.ix_(yy, xx)]
 
 
+def shift_and_add_integer(lr_list, shifts_yx, factor=2):
+    """SAA when every factor*shift is an integer: the order-3 shift of the zoomed frame is a
+    pure clamp-gather (weights (1/6, 4/6, 1/6, 0) return the padded sample itself)."""
+    acc = None
+    for lr, (dy, dx) in zip(lr_list, shifts_yx):
+        sy, sx = dy * factor, dx * factor
+        if sy != round(sy) or sx != round(sx):
+            raise ValueError("non-integer HR shift")
+        term = clamp_gather(ndi_zoom_cubic(lr, factor), int(round(sy)), int(round(sx)))
+        acc = term if acc is None else acc + term
+    return acc / len(lr_list)
+
+
 def ibp_integer_shifts(lr_list, shifts_yx, kernel, hr_init, factor=2, n_iter=80, step=0.5,
                        clip_lo=0.0, clip_hi=255.0):
     """IBP when every factor*shift is an integer (SURVEY.md section 8a 'verified restatement').

@@ -133,7 +133,13 @@ def _run_pipeline(sr, lrs, shifts, psf, n_iter, path=0):
     n, (h, w) = len(lrs), lrs[0].shape
     plan = sr.Plan(n, h, w, shifts, psf)
     if path:
-        plan.set_path(path)
+        try:
+            plan.set_path(path)
+        except sr.Sr459Error as exc:
+            plan.close()
+            if exc.code == -4:
+                pytest.skip(f"path {path} not available for this geometry: {exc}")
+            raise
     dl = [torch.from_numpy(np.asarray(l, dtype=np.float32)).cuda() for l in lrs]
     native = plan.native_2x(sr.mean_frames(dl)).cpu().numpy()
     saa = plan.saa(dl)
@@ -333,8 +339,19 @@ def test_full_size_fast_equals_dense_and_properties(sr):
     assert float((hr_fast - hr_dense).abs().max()) < 2e-3
     np.testing.assert_allclose(e_fast, e_dense, rtol=1e-6)
     assert all(b < a for a, b in zip(e_fast, e_fast[1:])), "IBP residual must decrease"
-    # oracle on a corner window: a 96x128 LR crop reproduces the top-left HR block exactly far from the cut
-    crop = [l[:96, :128].cpu().numpy().astype(np.float64) for l in lrs]
-    saa_c = O.shift_and_add(crop, NOMINAL)
-    _close(saa[:120, :160].cpu().numpy(), saa_c[:120, :160], what="full-size saa window")
+    # full-size SAA against the oracle (integer shifts: zoom + clamp-gather)
+    saa_o = O.shift_and_add_integer([l.cpu().numpy().astype(np.float64) for l in lrs], NOMINAL)
+    _close(saa.cpu().numpy(), saa_o, what="full-size saa")
+    # IBP is local (dependence radius 2r+2 = 8 px per iteration): oracle IBP on corner windows of the
+    # GPU's own SAA image must agree away from the cut after 3 iterations
+    hr3 = saa.clone(); plan.set_path(0).ibp_(lrs, hr3, 3)
+    for (ys, xs) in [(slice(0, 96), slice(0, 128)), (slice(h - 96, h), slice(w - 128, w))]:
+        crop = [l[ys, xs].cpu().numpy().astype(np.float64) for l in lrs]
+        Ys = slice(2 * ys.start, 2 * ys.stop); Xs = slice(2 * xs.start, 2 * xs.stop)
+        hr_c, _ = O.ibp_integer_shifts(crop, NOMINAL, psf, saa_o[Ys, Xs], n_iter=3)
+        got = hr3[Ys, Xs].cpu().numpy()
+        if ys.start == 0:
+            _close(got[:160, :224], hr_c[:160, :224], what="ibp top-left window")
+        else:
+            _close(got[-160:, -224:], hr_c[-160:, -224:], what="ibp bottom-right window")
     plan.close()
