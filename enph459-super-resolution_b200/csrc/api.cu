@@ -348,48 +348,30 @@ static int dense_launch(const sr459_plan* p, const IbpGeom& g, const float* cons
 
 // number of partial-sum slots one fused iteration writes, and the launch recipe
 struct FusedRecipe {
-    bool use_fast; Rect interior; int fast_tx, fast_ty, fast_origin;
-    DensePass rows, cols, all;
-    int n_fast, n_rows, n_cols, n_all, per_iter;
+    bool use_fast;
+    int fast_tx, fast_ty;
+    DensePass all;
+    int n_fast, n_all, per_iter;
 };
 
 static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     FusedRecipe r{};
-    const int H = p->H, W = p->W;
+    const int W = p->W;
     int fth, ftw;
     ibp_fast_tile(&fth, &ftw);
-    const int mg = 4;
-    Rect in{std::max(uy0, mg), mg, std::min(uy1, H - mg), W - mg};
-    bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && !(p->path == 1);
-    bool big = (long long)(in.y1 - in.y0) * (in.x1 - in.x0) >= 48 * 48;
-    auto count = [](const DensePass& d) {
-        int t = 0;
-        for (int i = 0; i < d.nrect; ++i) {
-            const Rect& rc = d.rects[i];
-            if (rc.y1 <= rc.y0 || rc.x1 <= rc.x0) continue;
-            t += ((rc.x1 - rc.x0 + d.tile_w - 1) / d.tile_w) * ((rc.y1 - rc.y0 + d.tile_h - 1) / d.tile_h);
-        }
-        return t;
-    };
-    if (fast_ok && in.y1 - in.y0 >= 2 && in.x1 - in.x0 >= 2 && (big || p->path == 3)) {
-        r.use_fast = true; r.interior = in;
-        r.fast_origin = in.y0;                           // even (uy0 and mg are even)
-        r.fast_tx = (in.x1 + ftw - 1) / ftw;
-        r.fast_ty = (in.y1 - r.fast_origin + fth - 1) / fth;
+    bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1;
+    bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
+    if (fast_ok && (big || p->path == 3)) {
+        r.use_fast = true;
+        r.fast_tx = (W + ftw - 1) / ftw;
+        r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
         r.n_fast = r.fast_tx * r.fast_ty;
-        r.rows.tile_h = 8; r.rows.tile_w = 128; r.rows.nrect = 2;
-        r.rows.rects[0] = Rect{uy0, 0, in.y0, W};
-        r.rows.rects[1] = Rect{in.y1, 0, uy1, W};
-        r.cols.tile_h = 64; r.cols.tile_w = 8; r.cols.nrect = 2;
-        r.cols.rects[0] = Rect{in.y0, 0, in.y1, mg};
-        r.cols.rects[1] = Rect{in.y0, W - mg, in.y1, W};
-        r.n_rows = count(r.rows); r.n_cols = count(r.cols);
     } else {
         r.all.tile_h = 32; r.all.tile_w = 32; r.all.nrect = 1;
         r.all.rects[0] = Rect{uy0, 0, uy1, W};
-        r.n_all = count(r.all);
+        r.n_all = ((W + 31) / 32) * ((uy1 - uy0 + 31) / 32);
     }
-    r.per_iter = r.n_fast + r.n_rows + r.n_cols + r.n_all;
+    r.per_iter = r.n_fast + r.n_all;
     return r;
 }
 
@@ -397,25 +379,22 @@ static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const
                          double* partial, int uy0, int uy1, cudaStream_t st) {
     IbpGeom g;
     fill_geom(p, g, uy0, uy1);
-    int nt = 0;
     if (r.use_fast) {
         FastArgs f{};
         f.g = g;
         for (int k = 0; k < p->n; ++k) f.lr[k] = lr[k];
         f.hr_in = cur; f.hr_out = nxt;
         memcpy(f.psf, p->psf7, sizeof(f.psf));
-        f.interior = r.interior;
-        f.phase_mask = 0;
-        for (int k = 0; k < p->n; ++k) f.phase_mask |= 1 << (((p->isy[k] & 1) << 1) | (p->isx[k] & 1));
-        f.tiles_x = r.fast_tx; f.tiles_y = r.fast_ty; f.ty_origin = r.fast_origin;
+        for (int k = 0; k < p->n; ++k) {
+            int ph = ((p->isy[k] & 1) << 1) | (p->isx[k] & 1);
+            f.ph_k[ph][f.ph_n[ph]++] = k;
+        }
+        f.tiles_x = r.fast_tx; f.tiles_y = r.fast_ty; f.ty_origin = uy0;
         f.partial = partial;
-        SR_TRY(launch_ibp_fast(f, st));
-        SR_TRY(dense_launch(p, g, lr, cur, nxt, r.rows, partial + r.n_fast, &nt, st));
-        SR_TRY(dense_launch(p, g, lr, cur, nxt, r.cols, partial + r.n_fast + r.n_rows, &nt, st));
-    } else {
-        SR_TRY(dense_launch(p, g, lr, cur, nxt, r.all, partial, &nt, st));
+        return launch_ibp_fast(f, st);
     }
-    return SR459_OK;
+    int nt = 0;
+    return dense_launch(p, g, lr, cur, nxt, r.all, partial, &nt, st);
 }
 
 static bool use_fused(const sr459_plan* p) {

@@ -1,151 +1,176 @@
-// ibp_fast.cu -- fused IBP iteration, integer HR shifts, polyphase interior kernel.
+// ibp_fast.cu -- fused IBP iteration, integer HR shifts, polyphase kernel (the throughput path).
 //
 // Same mathematics as ibp_dense.cu (the body of ibp(), mono_cal_target/run_sr.py:190-209,
 // for integer factor*shift), specialised for what the reference actually runs:
-// factor 2, |HR shift| <= 1, odd square PSF up to 7x7.  Away from the image
-// border no clamp of ndi_shift(mode='nearest') is active, and then
-//   * frame k only ever samples the blurred image B on ONE polyphase lattice,
-//     the sites with (y,x) parity == parity of its shift (sy_k, sx_k)         (:163-165)
-//   * the zero-inserted, back-shifted residuals live on that same lattice      (:170-176)
-// so B is evaluated only on the active lattices (1 of 4 for the nominal
-// +-0.5 px corner shifts), and the transposed blur (:178) only visits the taps
-// that can meet a non-zero site: ~12 MAC per HR pixel each way instead of 49.
+// factor 2, |HR shift| <= 1, odd square PSF up to 7x7.  Where no clamp of
+// ndi_shift(mode='nearest') is active,
+//   * frame k samples the blurred image B only on ONE polyphase lattice, the sites whose
+//     (y,x) parity equals the parity of its shift (sy_k, sx_k)                    (:163-165)
+//   * its zero-inserted, back-shifted residual lives on that same lattice          (:170-176)
+// so B is evaluated only on the active lattices (1 of 4 for the nominal +-0.5 px corner
+// shifts) and the transposed blur (:178) only visits taps that can meet a non-zero site:
+// ~12 MAC per HR pixel each way instead of 49.
 //
 // One CTA owns a 64x128 HR tile:
-//   stage 1  hr tile + 8 px halo -> shared memory with float4 global loads, split into
-//            even-column / odd-column planes so that lattice sampling is unit-stride
-//            (bank-conflict free) for a warp.
-//   stage 2  per active lattice: each thread walks a 4-site column strip, 13 rows x 7
-//            taps from shared memory, PSF taps as constant-bank FFMA operands; LR
-//            samples are fetched coalesced straight from global; residual energy is
-//            accumulated for the LR sites the tile owns; summed residuals are stored
-//            to a 36x68 shared-memory lattice plane.
+//   stage 1  hr tile + 8 px halo -> shared memory (float4 loads, zero outside the image =
+//            fftconvolve's zero padding).
+//   stage 2  per active lattice: a thread walks a 4-site column strip -- 13 staged rows x 4
+//            LDS.64 (unit-stride across the warp: conflict free), PSF taps as constant-bank
+//            FFMA operands -- fetches the matching LR samples coalesced from global,
+//            accumulates the residual energy of the sites the tile owns, and stores the
+//            summed residuals to a 36x68 shared-memory lattice plane.
 //   stage 3  transposed blur from the lattice plane(s), update, clip, float2 stores.
-// Pixels within R+1 of the image border are left to ibp_dense.cu (DenseArgs rects).
+// The ndi_shift clamps only bite at the top and left image edges when |shift| <= 1:
+//   * LR row 0 of a frame with sy=+1 reads B[clamp(-1)] = B[0]: a residual that enters the
+//     MSE (:202) but is never back-projected;
+//   * HR row 0 receives a duplicate of the residuals frames with sy=-1 deposit on row 1;
+// (same for columns).  CTAs on the first tile row / column evaluate those few terms
+// literally ("fix-ups") and all edge CTAs run a bounds-checked instantiation; the other
+// ~90 % of the CTAs run with no checks at all.
 #include "internal.h"
 
 namespace sr459 {
 
-constexpr int FT_H   = 64;              // tile rows (HR)
-constexpr int FT_W   = 128;             // tile cols (HR)
+constexpr int FT_H    = 64;             // tile rows (HR)
+constexpr int FT_W    = 128;            // tile cols (HR)
 constexpr int FH_ROWS = FT_H + 16;      // staged hr rows  y0-8 .. y0+71
 constexpr int FH_COLS = FT_W + 16;      // staged hr cols  x0-8 .. x0+135
-constexpr int FP_C   = FH_COLS / 2;     // 72: columns of each parity plane
-constexpr int FA_R   = FT_H / 2 + 4;    // 36: lattice-plane rows   y' = y0-4+2a+p
-constexpr int FA_C   = FT_W / 2 + 4;    // 68: lattice-plane cols   x' = x0-4+2b+q
+constexpr int FA_R    = FT_H / 2 + 4;   // 36: lattice-plane rows   y' = y0-4+2a+P
+constexpr int FA_C    = FT_W / 2 + 4;   // 68: lattice-plane cols   x' = x0-4+2b+Q
 constexpr int F_THREADS = 256;
+constexpr int F_PRE   = 4;              // frames per lattice whose LR samples are prefetched
 
 void ibp_fast_tile(int* th, int* tw) { *th = FT_H; *tw = FT_W; }
 
 bool ibp_fast_supported(int kh, int kw, int smax) {
-    return kh == kw && (kh == 3 || kh == 5 || kh == 7) && smax <= 1;
+    return kh == kw && (kh == 1 || kh == 3 || kh == 5 || kh == 7) && smax <= 1;
 }
 
-struct FastShared {
-    float* E;      // even-column plane, FH_ROWS x FP_C
-    float* O;      // odd-column plane
-    float* A;      // lattice planes, one per active phase, FA_R x FA_C each
+struct TileCtx {
+    int y0, x0;                 // tile origin (global HR)
+    int oy0, oy1, ox0, ox1;     // sites / pixels this tile owns (global HR, half open)
+    int ilo, ihi;               // LR rows that exist and are local
 };
 
-// ---- stage 2: B on lattice (P,Q), residuals, accumulation ----------------------------------
-template <int R, int P, int Q>
-__device__ __forceinline__ void stage_forward(const FastArgs& a, const FastShared& s, float* __restrict__ plane,
-                                              int y0, int x0, int vy0, int vy1, int vx0, int vx1,
-                                              int oi0, int oi1, int oj0, int oj1, float& e2) {
-    constexpr int K = 2 * R + 1;
+// ---- stage 2: B on lattice (P,Q), residuals, accumulation ------------------------------------------
+template <int P, int Q, bool CHK>
+__device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __restrict__ hs,
+                                              float* __restrict__ plane, const TileCtx& c, float& e2) {
     const IbpGeom& g = a.g;
+    constexpr int ph = P * 2 + Q;
+    const int m = a.ph_n[ph];
+    const int mpre = m < F_PRE ? m : F_PRE;
+    const int ibase = (c.y0 - 4) >> 1, jbase = (c.x0 - 4) >> 1;
+
     for (int t = threadIdx.x; t < (FA_R / 4) * FA_C; t += F_THREADS) {
         const int grp = t / FA_C, b = t - grp * FA_C;
         const int a0 = grp * 4;
-        const int xg = x0 - 4 + 2 * b + Q;
-        const bool xok = (xg >= vx0) && (xg < vx1);
 
-        // LR samples first (global latency overlaps the shared-memory FMA block below)
-        float lrv[4][kMaxFrames];
+        // LR samples first: their global latency overlaps the shared-memory FMA block below
+        float lrv[4][F_PRE];
         #pragma unroll
-        for (int sI = 0; sI < 4; ++sI) {
-            const int yg = y0 - 4 + 2 * (a0 + sI) + P;
-            const bool ok = xok && (yg >= vy0) && (yg < vy1);
+        for (int f = 0; f < F_PRE; ++f) {
             #pragma unroll
-            for (int k = 0; k < kMaxFrames; ++k) {
-                lrv[sI][k] = 0.0f;
-                if (k < g.n && ((g.sy[k] & 1) == P) && ((g.sx[k] & 1) == Q) && ok) {
-                    const int i = (yg + g.sy[k]) >> 1, j = (xg + g.sx[k]) >> 1;
-                    lrv[sI][k] = __ldg(a.lr[k] + (size_t)(i - g.lr_lo) * g.w + j);
-                }
-            }
-        }
-
-        float B[4] = {0.f, 0.f, 0.f, 0.f};
-        const int lyb = 2 * a0 + P + 4 - R;             // first staged row of the strip
-        #pragma unroll
-        for (int rr = 0; rr < 7 + 2 * R; ++rr) {
-            float v[K];
-            #pragma unroll
-            for (int d = 0; d < K; ++d) {
-                constexpr int dummy = 0; (void)dummy;
-                const int off = Q + 4 + (d - R);       // staged col = 2b + off
-                const float* pl = (off & 1) ? s.O : s.E;
-                v[d] = pl[(lyb + rr) * FP_C + b + (off >> 1)];
-            }
-            #pragma unroll
-            for (int sI = 0; sI < 4; ++sI) {
-                const int dy = rr - R - 2 * sI;         // staged row - site centre row
-                if (dy >= -R && dy <= R) {
-                    #pragma unroll
-                    for (int d = 0; d < K; ++d)
-                        B[sI] = fmaf(a.psf[(R - dy) * K + (R - (d - R))], v[d], B[sI]);
-                }
-            }
-        }
-
-        #pragma unroll
-        for (int sI = 0; sI < 4; ++sI) {
-            const int yg = y0 - 4 + 2 * (a0 + sI) + P;
-            const bool ok = xok && (yg >= vy0) && (yg < vy1);
-            float acc = 0.0f;
-            if (ok) {
+            for (int s = 0; s < 4; ++s) lrv[s][f] = 0.0f;
+            if (f < mpre) {
+                const int k = a.ph_k[ph][f];
+                const int oy = (P + g.sy[k]) >> 1, ox = (Q + g.sx[k]) >> 1;
+                const float* p = a.lr[k] + (ptrdiff_t)(ibase + oy - g.lr_lo) * g.w + (jbase + ox);
+                const int j = jbase + ox + b;
                 #pragma unroll
-                for (int k = 0; k < kMaxFrames; ++k) {
-                    if (k < g.n && ((g.sy[k] & 1) == P) && ((g.sx[k] & 1) == Q)) {
-                        const float e = lrv[sI][k] - B[sI];
+                for (int s = 0; s < 4; ++s) {
+                    const int i = ibase + oy + a0 + s;
+                    bool ok = true;
+                    if (CHK) ok = (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) &&
+                                  (c.y0 - 4 + 2 * (a0 + s) + P >= 0) && (c.x0 - 4 + 2 * b + Q >= 0);
+                    if (ok) lrv[s][f] = __ldg(p + (ptrdiff_t)(a0 + s) * g.w + b);
+                }
+            }
+        }
+
+        // B at the 4 sites: staged rows 8*grp+P+1 .. +12, staged cols 2b+Q+1 .. 2b+Q+7
+        float B[4] = {0.f, 0.f, 0.f, 0.f};
+        const float* base = hs + (2 * a0 + P + 1) * FH_COLS + 2 * b + (Q ? 2 : 0);
+        #pragma unroll
+        for (int rr = 0; rr < 13; ++rr) {
+            float v[8];
+            #pragma unroll
+            for (int q = 0; q < 4; ++q) {
+                const float2 t2 = *reinterpret_cast<const float2*>(base + rr * FH_COLS + 2 * q);
+                v[2 * q] = t2.x; v[2 * q + 1] = t2.y;
+            }
+            #pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int dy = rr - 3 - 2 * s;           // staged row - site centre row
+                if (dy >= -3 && dy <= 3) {
+                    #pragma unroll
+                    for (int dx = -3; dx <= 3; ++dx)
+                        B[s] = fmaf(a.psf[(3 - dy) * 7 + (3 - dx)], v[dx + (Q ? 3 : 4)], B[s]);
+                }
+            }
+        }
+
+        #pragma unroll
+        for (int s = 0; s < 4; ++s) {
+            const int yg = c.y0 - 4 + 2 * (a0 + s) + P, xg = c.x0 - 4 + 2 * b + Q;
+            const bool own = (yg >= c.oy0) && (yg < c.oy1) && (xg >= c.ox0) && (xg < c.ox1);
+            float acc = 0.0f, sq = 0.0f;
+            #pragma unroll
+            for (int f = 0; f < F_PRE; ++f) {
+                if (f < mpre) {
+                    bool ok = true;
+                    if (CHK) {
+                        const int k = a.ph_k[ph][f];
+                        const int i = ibase + ((P + g.sy[k]) >> 1) + a0 + s, j = jbase + ((Q + g.sx[k]) >> 1) + b;
+                        ok = (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) && (yg >= 0) && (xg >= 0);
+                    }
+                    if (ok) {
+                        const float e = lrv[s][f] - B[s];
                         acc += e;
-                        const int i = (yg + g.sy[k]) >> 1, j = (xg + g.sx[k]) >> 1;
-                        if (i >= oi0 && i < oi1 && j >= oj0 && j < oj1) e2 = fmaf(e, e, e2);
+                        sq = fmaf(e, e, sq);
                     }
                 }
             }
-            plane[(a0 + sI) * FA_C + b] = acc;
+            for (int f = F_PRE; f < m; ++f) {            // more than 4 frames on one lattice: rare
+                const int k = a.ph_k[ph][f];
+                const int i = ibase + ((P + g.sy[k]) >> 1) + a0 + s, j = jbase + ((Q + g.sx[k]) >> 1) + b;
+                if ((i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) && (yg >= 0) && (xg >= 0)) {
+                    const float e = __ldg(a.lr[k] + (ptrdiff_t)(i - g.lr_lo) * g.w + j) - B[s];
+                    acc += e;
+                    sq = fmaf(e, e, sq);
+                }
+            }
+            if (own) e2 += sq;
+            plane[(a0 + s) * FA_C + b] = acc;
         }
     }
 }
 
-// ---- stage 3: transposed blur contribution of lattice (P,Q) to a 4-cell column strip --------
-template <int R, int P, int Q>
+// ---- stage 3: transposed-blur contribution of lattice (P,Q) to a 4-cell column strip --------------
+template <int P, int Q>
 __device__ __forceinline__ void stage_backward(const FastArgs& a, const float* __restrict__ plane,
                                                int i0, int j, float (&o)[4][2][2]) {
-    constexpr int K = 2 * R + 1;
     #pragma unroll
     for (int ar = 0; ar < 8; ++ar) {
         float v[5];
         #pragma unroll
-        for (int c = 0; c < 5; ++c) v[c] = plane[(i0 + ar) * FA_C + j + c];
+        for (int cc = 0; cc < 5; ++cc) v[cc] = plane[(i0 + ar) * FA_C + j + cc];
         #pragma unroll
         for (int cell = 0; cell < 4; ++cell) {
             #pragma unroll
             for (int oy = 0; oy < 2; ++oy) {
                 #pragma unroll
-                for (int ta = 0; ta < K; ++ta) {
-                    if (((ta + P + R + oy) & 1) != 0) continue;
-                    const int da = (oy + ta - R + 4 - P) / 2;      // exact: numerator is even
+                for (int ta = 0; ta < 7; ++ta) {
+                    if (((ta + P + 3 + oy) & 1) != 0) continue;
+                    const int da = (oy + ta + 1 - P) / 2;      // exact: numerator is even
                     if (cell + da != ar) continue;
                     #pragma unroll
                     for (int ox = 0; ox < 2; ++ox) {
                         #pragma unroll
-                        for (int tb = 0; tb < K; ++tb) {
-                            if (((tb + Q + R + ox) & 1) != 0) continue;
-                            const int db = (ox + tb - R + 4 - Q) / 2;
-                            o[cell][oy][ox] = fmaf(a.psf[ta * K + tb], v[db], o[cell][oy][ox]);
+                        for (int tb = 0; tb < 7; ++tb) {
+                            if (((tb + Q + 3 + ox) & 1) != 0) continue;
+                            const int db = (ox + tb + 1 - Q) / 2;
+                            o[cell][oy][ox] = fmaf(a.psf[ta * 7 + tb], v[db], o[cell][oy][ox]);
                         }
                     }
                 }
@@ -154,83 +179,181 @@ __device__ __forceinline__ void stage_backward(const FastArgs& a, const float* _
     }
 }
 
-template <int R>
+// literal B = conv0(hr, psf) at one global site, from the staged tile (edge fix-ups only)
+__device__ __noinline__ float b_direct(const FastArgs& a, const float* __restrict__ hs, int y0, int x0, int gy, int gx) {
+    const float* c = hs + (gy - (y0 - 8)) * FH_COLS + (gx - (x0 - 8));
+    float v = 0.0f;
+    for (int u = 0; u < 7; ++u)
+        for (int w = 0; w < 7; ++w) v = fmaf(a.psf[u * 7 + w], c[(3 - u) * FH_COLS + (3 - w)], v);
+    return v;
+}
+
+__device__ __forceinline__ int clampi2(int v, int lo, int hi) { return min(max(v, lo), hi); }
+
+template <int DUMMY>
 __global__ void __launch_bounds__(F_THREADS, 2) k_ibp_fast(const __grid_constant__ FastArgs a) {
     extern __shared__ __align__(16) float sm[];
+    __shared__ float R0[FT_W + 8];       // duplicates deposited on HR row 0, x = x0-4 .. x0+131
+    __shared__ float C0[FT_H + 8];       // duplicates deposited on HR col 0, y = y0-4 .. y0+67
+    __shared__ double red[F_THREADS / 32];
     const IbpGeom& g = a.g;
-    FastShared s;
-    s.E = sm;
-    s.O = sm + FH_ROWS * FP_C;
-    s.A = sm + 2 * FH_ROWS * FP_C;
+    float* hs = sm;                                        // FH_ROWS x FH_COLS
+    float* planes = sm + FH_ROWS * FH_COLS;                // one FA_R x FA_C plane per active lattice
     const int tid = threadIdx.x;
-    const int y0 = a.ty_origin + blockIdx.y * FT_H;
-    const int x0 = blockIdx.x * FT_W;
+    TileCtx c;
+    c.y0 = a.ty_origin + blockIdx.y * FT_H;
+    c.x0 = blockIdx.x * FT_W;
+    c.oy0 = max(c.y0, g.upd_y0); c.oy1 = min(min(c.y0 + FT_H, g.upd_y1), g.H);
+    c.ox0 = c.x0;                c.ox1 = min(c.x0 + FT_W, g.W);
+    c.ilo = max(0, g.lr_lo);     c.ihi = min(g.h, g.lr_hi);
 
-    // ---- stage 1: stage hr (zero outside image / local band) ---------------------------------
+    // ---- stage 1: stage hr (zero outside image / local band) -----------------------------------------
     for (int t = tid; t < FH_ROWS * (FH_COLS / 4); t += F_THREADS) {
         const int ly = t / (FH_COLS / 4), q4 = t - ly * (FH_COLS / 4);
-        const int gy = y0 - 8 + ly, gx = x0 - 8 + 4 * q4;
+        const int gy = c.y0 - 8 + ly, gx = c.x0 - 8 + 4 * q4;
         float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
         if (gy >= 0 && gy < g.H && gy >= g.hr_lo && gy < g.hr_hi && gx >= 0 && gx < g.W)
             v = __ldg(reinterpret_cast<const float4*>(a.hr_in + (size_t)(gy - g.hr_lo) * g.W + gx));
-        *reinterpret_cast<float2*>(s.E + ly * FP_C + 2 * q4) = make_float2(v.x, v.z);
-        *reinterpret_cast<float2*>(s.O + ly * FP_C + 2 * q4) = make_float2(v.y, v.w);
+        *reinterpret_cast<float4*>(hs + ly * FH_COLS + 4 * q4) = v;
     }
     __syncthreads();
 
-    // site validity zone (no clamp active, LR rows local) and residual ownership of this tile
-    const int m = g.smax;
-    const int vy0 = max(m, 2 * g.lr_lo + m), vy1 = min(g.H - m, 2 * g.lr_hi - m);
-    const int vx0 = m, vx1 = g.W - m;
-    const int oi0 = max(max(g.own_i0, a.interior.y0 >> 1), y0 >> 1);
-    const int oi1 = min(min(g.own_i1, a.interior.y1 >> 1), (y0 >> 1) + FT_H / 2);
-    const int oj0 = max(a.interior.x0 >> 1, x0 >> 1);
-    const int oj1 = min(a.interior.x1 >> 1, (x0 >> 1) + FT_W / 2);
+    // a tile is "edge" when any of its lattice sites could pair with a missing LR sample, sit outside
+    // the image, or fall outside the rows this launch owns
+    const bool top = (c.y0 == 0), left = (c.x0 == 0);
+    const bool edge = (c.y0 < 8) || (c.x0 < 8) || (c.y0 + FT_H + 5 > g.H) || (c.x0 + FT_W + 5 > g.W) ||
+                      (c.y0 + FT_H > g.upd_y1) || (((c.y0 - 6) >> 1) < c.ilo) || (((c.y0 + FT_H + 4) >> 1) + 1 > c.ihi);
 
     float e2 = 0.0f;
     {
         int slot = 0;
-        if (a.phase_mask & 1) { stage_forward<R, 0, 0>(a, s, s.A + slot * FA_R * FA_C, y0, x0, vy0, vy1, vx0, vx1, oi0, oi1, oj0, oj1, e2); ++slot; }
-        if (a.phase_mask & 2) { stage_forward<R, 0, 1>(a, s, s.A + slot * FA_R * FA_C, y0, x0, vy0, vy1, vx0, vx1, oi0, oi1, oj0, oj1, e2); ++slot; }
-        if (a.phase_mask & 4) { stage_forward<R, 1, 0>(a, s, s.A + slot * FA_R * FA_C, y0, x0, vy0, vy1, vx0, vx1, oi0, oi1, oj0, oj1, e2); ++slot; }
-        if (a.phase_mask & 8) { stage_forward<R, 1, 1>(a, s, s.A + slot * FA_R * FA_C, y0, x0, vy0, vy1, vx0, vx1, oi0, oi1, oj0, oj1, e2); ++slot; }
+        if (!edge) {
+            if (a.ph_n[0]) { stage_forward<0, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[1]) { stage_forward<0, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[2]) { stage_forward<1, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[3]) { stage_forward<1, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+        } else {
+            if (a.ph_n[0]) { stage_forward<0, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[1]) { stage_forward<0, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[2]) { stage_forward<1, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[3]) { stage_forward<1, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+        }
+    }
+
+    // ---- edge fix-ups: the terms ndi_shift's clamp creates at the top / left image edges ----------------
+    if (top) {
+        // residuals deposited a second time on HR row 0 by frames with sy = -1
+        for (int t = tid; t < FT_W + 8; t += F_THREADS) {
+            const int x = c.x0 - 4 + t;
+            float v = 0.0f;
+            if (x >= 0 && x < g.W) {
+                for (int k = 0; k < g.n; ++k) {
+                    if (g.sy[k] != -1) continue;
+                    const int X = clampi2(x + g.sx[k], 0, g.W - 1);
+                    if (X & 1) continue;
+                    const int j = X >> 1;
+                    if (j >= g.w || c.ilo > 0) continue;
+                    v += __ldg(a.lr[k] + (size_t)(0 - g.lr_lo) * g.w + j) -
+                         b_direct(a, hs, c.y0, c.x0, 1, clampi2(2 * j - g.sx[k], 0, g.W - 1));
+                }
+            }
+            R0[t] = v;
+        }
+        // LR row 0 of frames with sy = +1 reads B[clamp(-1)] = B[0]: MSE only
+        if (g.upd_y0 == 0 && c.ilo == 0) {
+            for (int k = 0; k < g.n; ++k) {
+                if (g.sy[k] != 1) continue;
+                for (int j = tid; j < g.w; j += F_THREADS) {
+                    const int cx = clampi2(2 * j - g.sx[k], 0, g.W - 1);
+                    if (cx < c.ox0 || cx >= c.ox1) continue;
+                    const float e = __ldg(a.lr[k] + (size_t)(0 - g.lr_lo) * g.w + j) - b_direct(a, hs, c.y0, c.x0, 0, cx);
+                    e2 = fmaf(e, e, e2);
+                }
+            }
+        }
+    }
+    if (left) {
+        for (int t = tid; t < FT_H + 8; t += F_THREADS) {
+            const int y = c.y0 - 4 + t;
+            float v = 0.0f;
+            if (y >= 0 && y < g.H) {
+                for (int k = 0; k < g.n; ++k) {
+                    if (g.sx[k] != -1) continue;
+                    if (y + g.sy[k] < 0) continue;               // corner: already counted in R0
+                    const int Y = clampi2(y + g.sy[k], 0, g.H - 1);
+                    if (Y & 1) continue;
+                    const int i = Y >> 1;
+                    if (i >= c.ihi || i < c.ilo) continue;
+                    v += __ldg(a.lr[k] + (size_t)(i - g.lr_lo) * g.w + 0) -
+                         b_direct(a, hs, c.y0, c.x0, clampi2(2 * i - g.sy[k], 0, g.H - 1), 1);
+                }
+            }
+            C0[t] = v;
+        }
+        // LR col 0 of frames with sx = +1 reads B[., clamp(-1)] = B[., 0]: MSE only (row-virtual ones were
+        // counted by the top fix-up)
+        for (int k = 0; k < g.n; ++k) {
+            if (g.sx[k] != 1) continue;
+            for (int t = tid; t < FT_H / 2 + 2; t += F_THREADS) {
+                const int i = (c.y0 >> 1) - 1 + t;
+                if (i < c.ilo || i >= c.ihi) continue;
+                const int cy = 2 * i - g.sy[k];
+                if (cy < 0 || cy < c.oy0 || cy >= c.oy1) continue;
+                const float e = __ldg(a.lr[k] + (size_t)(i - g.lr_lo) * g.w + 0) - b_direct(a, hs, c.y0, c.x0, cy, 0);
+                e2 = fmaf(e, e, e2);
+            }
+        }
     }
     __syncthreads();
 
-    // ---- stage 3 -------------------------------------------------------------------------------
+    // ---- stage 3 -----------------------------------------------------------------------------------------
     for (int t = tid; t < (FT_H / 8) * (FT_W / 2); t += F_THREADS) {
         const int grp = t / (FT_W / 2), j = t - grp * (FT_W / 2);
         const int i0 = grp * 4;
         float o[4][2][2];
         #pragma unroll
-        for (int c = 0; c < 4; ++c) { o[c][0][0] = o[c][0][1] = o[c][1][0] = o[c][1][1] = 0.f; }
+        for (int cc = 0; cc < 4; ++cc) { o[cc][0][0] = o[cc][0][1] = o[cc][1][0] = o[cc][1][1] = 0.f; }
         int slot = 0;
-        if (a.phase_mask & 1) { stage_backward<R, 0, 0>(a, s.A + slot * FA_R * FA_C, i0, j, o); ++slot; }
-        if (a.phase_mask & 2) { stage_backward<R, 0, 1>(a, s.A + slot * FA_R * FA_C, i0, j, o); ++slot; }
-        if (a.phase_mask & 4) { stage_backward<R, 1, 0>(a, s.A + slot * FA_R * FA_C, i0, j, o); ++slot; }
-        if (a.phase_mask & 8) { stage_backward<R, 1, 1>(a, s.A + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[0]) { stage_backward<0, 0>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[1]) { stage_backward<0, 1>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[2]) { stage_backward<1, 0>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[3]) { stage_backward<1, 1>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
 
-        const int gx = x0 + 2 * j;
-        const bool xin = (gx >= a.interior.x0) && (gx < a.interior.x1);
+        const int gx = c.x0 + 2 * j;
         #pragma unroll
-        for (int c = 0; c < 4; ++c) {
+        for (int cc = 0; cc < 4; ++cc) {
             #pragma unroll
             for (int oy = 0; oy < 2; ++oy) {
-                const int ly = 2 * (i0 + c) + oy + 8;
-                const int gy = y0 + 2 * (i0 + c) + oy;
-                if (xin && gy >= a.interior.y0 && gy < a.interior.y1 && gy >= g.upd_y0 && gy < g.upd_y1) {
-                    const float h0 = s.E[ly * FP_C + j + 4], h1 = s.O[ly * FP_C + j + 4];
-                    float2 r;
-                    r.x = fminf(fmaxf(fmaf(g.alpha, o[c][oy][0], h0), g.lo), g.hi);
-                    r.y = fminf(fmaxf(fmaf(g.alpha, o[c][oy][1], h1), g.lo), g.hi);
-                    *reinterpret_cast<float2*>(a.hr_out + (size_t)(gy - g.hr_lo) * g.W + gx) = r;
+                const int ly = 2 * (i0 + cc) + oy + 8;
+                const int gy = c.y0 + 2 * (i0 + cc) + oy;
+                float o0 = o[cc][oy][0], o1 = o[cc][oy][1];
+                if (edge) {
+                    if (gy >= c.oy1 || gx >= c.ox1) continue;
+                    if (top && gy <= 3) {
+                        for (int tb = 0; tb < 7; ++tb) {
+                            const float w = a.psf[(3 - gy) * 7 + tb];
+                            o0 = fmaf(w, R0[gx + tb - 3 - (c.x0 - 4)], o0);
+                            o1 = fmaf(w, R0[gx + 1 + tb - 3 - (c.x0 - 4)], o1);
+                        }
+                    }
+                    if (left && gx <= 3) {
+                        for (int ta = 0; ta < 7; ++ta) {
+                            const float cv = C0[gy + ta - 3 - (c.y0 - 4)];
+                            if (3 - gx >= 0) o0 = fmaf(a.psf[ta * 7 + (3 - gx)], cv, o0);
+                            if (3 - (gx + 1) >= 0) o1 = fmaf(a.psf[ta * 7 + (3 - (gx + 1))], cv, o1);
+                        }
+                    }
                 }
+                const float2 hv = *reinterpret_cast<const float2*>(hs + ly * FH_COLS + 2 * j + 8);
+                float2 r;
+                r.x = fminf(fmaxf(fmaf(g.alpha, o0, hv.x), g.lo), g.hi);
+                r.y = fminf(fmaxf(fmaf(g.alpha, o1, hv.y), g.lo), g.hi);
+                *reinterpret_cast<float2*>(a.hr_out + (size_t)(gy - g.hr_lo) * g.W + gx) = r;
             }
         }
     }
 
-    // ---- residual energy of this tile ----------------------------------------------------------
-    __shared__ double red[F_THREADS / 32];
+    // ---- residual energy of this tile --------------------------------------------------------------------
     double d = (double)e2;
     #pragma unroll
     for (int off = 16; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
@@ -244,25 +367,20 @@ __global__ void __launch_bounds__(F_THREADS, 2) k_ibp_fast(const __grid_constant
     }
 }
 
-template <int R>
-static int launch_fast_r(const FastArgs& a, cudaStream_t st) {
-    int nph = __builtin_popcount(a.phase_mask & 15);
-    size_t smem = sizeof(float) * (2 * FH_ROWS * FP_C + (size_t)nph * FA_R * FA_C);
+int launch_ibp_fast(const FastArgs& a, cudaStream_t st) {
+    if (a.tiles_x <= 0 || a.tiles_y <= 0) return SR459_OK;
+    int nph = 0;
+    for (int p = 0; p < 4; ++p) nph += a.ph_n[p] > 0;
+    size_t smem = sizeof(float) * (FH_ROWS * FH_COLS + (size_t)nph * FA_R * FA_C);
     static size_t configured = 0;
     if (smem > configured) {
-        SR_CUDA(cudaFuncSetAttribute(k_ibp_fast<R>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
     dim3 grid(a.tiles_x, a.tiles_y);
-    k_ibp_fast<R><<<grid, F_THREADS, smem, st>>>(a);
+    k_ibp_fast<0><<<grid, F_THREADS, smem, st>>>(a);
     SR_LAUNCH_CHECK("k_ibp_fast");
     return SR459_OK;
-}
-
-int launch_ibp_fast(const FastArgs& a, cudaStream_t st) {
-    if (a.tiles_x <= 0 || a.tiles_y <= 0) return SR459_OK;
-    // psf is always passed as a 7x7 (smaller odd kernels are centred in it by the host)
-    return launch_fast_r<3>(a, st);
 }
 
 }  // namespace sr459

@@ -163,16 +163,16 @@ int launch_ibp_dense(const DenseArgs& a, cudaStream_t st);
 size_t ibp_dense_smem(int R, int smax, int tile_h, int tile_w, int nf, int nb);
 
 struct FastArgs {
-    IbpGeom g;
+    IbpGeom g;                      // upd_y0/upd_y1: HR rows this launch updates and whose sites it owns
     const float* lr[kMaxFrames];
     const float* hr_in;
     float* hr_out;
-    float psf[49];                  // 7x7 (R=3) row-major k[u][v]; smaller odd kernels centred & zero padded
-    Rect interior;                  // pixels this kernel may store (even bounds, x multiple of 4)
-    int phase_mask;                 // bit (p*2+q) set when some frame has shift parity (p,q)
+    float psf[49];                  // 7x7 row-major k[u][v]; smaller odd kernels centred & zero padded
+    int ph_n[4];                    // frames on lattice (P,Q), index P*2+Q
+    int ph_k[4][kMaxFrames];        // their frame ids
     int tiles_x, tiles_y;
-    int ty_origin;                  // global HR row of tile row 0 (even)
-    double* partial;
+    int ty_origin;                  // global HR row of tile row 0 (even) == g.upd_y0
+    double* partial;                // one slot per CTA
 };
 int  launch_ibp_fast(const FastArgs& a, cudaStream_t st);
 bool ibp_fast_supported(int kh, int kw, int smax);

@@ -101,25 +101,37 @@ __device__ __forceinline__ int fold_reflect(int i, int n) {     // period 2n
 }
 
 __device__ __forceinline__ float pf_fetch(const PrefilterJob& j, int Y, int X) {
+    // fold only when the (virtual) coordinate is outside the coefficient array: integer modulo is
+    // ~20 instructions and almost every fetch is inside
     if (j.mode == SRC_PLAIN) {
-        return __ldg(j.src + (size_t)fold_mirror(Y, j.ny) * j.sw + fold_mirror(X, j.nx));
+        if ((unsigned)Y >= (unsigned)j.ny) Y = fold_mirror(Y, j.ny);
+        if ((unsigned)X >= (unsigned)j.nx) X = fold_mirror(X, j.nx);
+        return __ldg(j.src + (size_t)Y * j.sw + X);
     }
-    int yy = fold_reflect(Y, j.ny) - kPad;
-    int xx = fold_reflect(X, j.nx) - kPad;
-    yy = min(max(yy, 0), j.vh - 1);
-    xx = min(max(xx, 0), j.vw - 1);
+    if ((unsigned)Y >= (unsigned)j.ny) Y = fold_reflect(Y, j.ny);
+    if ((unsigned)X >= (unsigned)j.nx) X = fold_reflect(X, j.nx);
+    const int yy = min(max(Y - kPad, 0), j.vh - 1);
+    const int xx = min(max(X - kPad, 0), j.vw - 1);
     if (j.mode == SRC_EDGEPAD) return __ldg(j.src + (size_t)yy * j.sw + xx);
     // zero-inserted residual (run_sr.py:170-175): up[::f, ::f] = err, zero elsewhere / beyond
-    int f = j.factor;
+    if (j.factor == 2) {
+        if ((yy | xx) & 1) return 0.0f;
+        const int i = yy >> 1, k = xx >> 1;
+        if (i >= j.sh || k >= j.sw) return 0.0f;
+        return __ldg(j.src + (size_t)i * j.sw + k);
+    }
+    const int f = j.factor;
     if ((yy % f) | (xx % f)) return 0.0f;
-    int i = yy / f, k = xx / f;
+    const int i = yy / f, k = xx / f;
     if (i >= j.sh || k >= j.sw) return 0.0f;
     return __ldg(j.src + (size_t)i * j.sw + k);
 }
 
-__global__ void __launch_bounds__(128) k_prefilter2d(const PrefilterJob* __restrict__ jobs) {
+struct PrefilterJobs { PrefilterJob job[8]; };
+
+__global__ void __launch_bounds__(128) k_prefilter2d(const __grid_constant__ PrefilterJobs jobs) {
     extern __shared__ float s[];
-    const PrefilterJob j = jobs[blockIdx.z];
+    const PrefilterJob& j = jobs.job[blockIdx.z];
     const int ty0 = blockIdx.y * PF_T, tx0 = blockIdx.x * PF_T;
     if (ty0 >= j.ny || tx0 >= j.nx) return;
     const int tid = threadIdx.x;
@@ -176,19 +188,25 @@ __global__ void __launch_bounds__(128) k_prefilter2d(const PrefilterJob* __restr
     }
 }
 
-// jobs are copied into a small per-stream-ordered device buffer
 int launch_prefilter2d(const PrefilterJob* h_jobs, int njobs, cudaStream_t st) {
-    if (njobs <= 0) return SR459_OK;
-    PrefilterJob* d_jobs = nullptr;
-    SR_CUDA(cudaMallocAsync((void**)&d_jobs, sizeof(PrefilterJob) * njobs, st));
-    SR_CUDA(cudaMemcpyAsync(d_jobs, h_jobs, sizeof(PrefilterJob) * njobs, cudaMemcpyHostToDevice, st));
-    int maxy = 0, maxx = 0;
-    for (int i = 0; i < njobs; ++i) { maxy = std::max(maxy, h_jobs[i].ny); maxx = std::max(maxx, h_jobs[i].nx); }
-    dim3 grid((maxx + PF_T - 1) / PF_T, (maxy + PF_T - 1) / PF_T, njobs);
+    static bool configured = false;
     size_t smem = sizeof(float) * PF_S * PF_P;
-    k_prefilter2d<<<grid, 128, smem, st>>>(d_jobs);
-    SR_LAUNCH_CHECK("k_prefilter2d");
-    SR_CUDA(cudaFreeAsync(d_jobs, st));
+    if (!configured) {
+        SR_CUDA(cudaFuncSetAttribute(k_prefilter2d, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    for (int first = 0; first < njobs; first += 8) {
+        const int cnt = std::min(8, njobs - first);
+        PrefilterJobs jobs{};
+        int maxy = 0, maxx = 0;
+        for (int i = 0; i < cnt; ++i) {
+            jobs.job[i] = h_jobs[first + i];
+            maxy = std::max(maxy, jobs.job[i].ny); maxx = std::max(maxx, jobs.job[i].nx);
+        }
+        dim3 grid((maxx + PF_T - 1) / PF_T, (maxy + PF_T - 1) / PF_T, cnt);
+        k_prefilter2d<<<grid, 128, smem, st>>>(jobs);
+        SR_LAUNCH_CHECK("k_prefilter2d");
+    }
     return SR459_OK;
 }
 

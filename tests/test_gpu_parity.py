@@ -279,6 +279,28 @@ def test_general_integer_shift_sets(sr, shifts):
         _errs_close(errs, e_o)
 
 
+@pytest.mark.parametrize("shifts", [
+    NOMINAL,
+    [(0.0, 0.0)] + NOMINAL,                                   # mono_cal_target: two lattices
+    [(0.0, 0.0), (0.5, 0.0), (0.0, 0.5), (0.5, 0.5)],         # all four lattices
+    [(0.5, -0.5)] * 3 + [(-0.5, -0.5)] * 3,                   # six frames on one lattice
+    [(0.0, 0.5), (-0.5, 0.0)],
+])
+def test_polyphase_kernel_interior_tiles_vs_oracle(sr, shifts):
+    """HR 320x640 has tiles that run the unchecked instantiation as well as all edge kinds."""
+    rng = np.random.default_rng(21)
+    h, w = 160, 320
+    lrs = [rng.uniform(0, 255, (h, w)) for _ in shifts]
+    psf = golden("g_prims")["k7"]
+    saa_o = O.shift_and_add_integer(lrs, shifts)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, saa_o, n_iter=4)
+    for path in (3, 2):
+        native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 4, path)
+        _close(saa, saa_o, what="saa")
+        _close(hr, hr_o, what=f"ibp path{path} {shifts}")
+        _errs_close(errs, e_o)
+
+
 @pytest.mark.parametrize("ksize", [3, 5, 7, 9])
 def test_psf_sizes_integer_shifts(sr, ksize):
     rng = np.random.default_rng(12)
