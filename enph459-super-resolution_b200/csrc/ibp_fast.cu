@@ -55,27 +55,27 @@ struct TileCtx {
 // ---- stage 2: B on lattice (P,Q), residuals, accumulation ------------------------------------------
 template <int P, int Q, bool CHK>
 __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __restrict__ hs,
-                                              float* __restrict__ plane, const TileCtx& c, float& e2) {
+                                              float* __restrict__ plane, const TileCtx& c, float& e2,
+                                              bool wait_stage1) {
     const IbpGeom& g = a.g;
     constexpr int ph = P * 2 + Q;
     const int m = a.ph_n[ph];
     const int mpre = m < F_PRE ? m : F_PRE;
     const int ibase = (c.y0 - 4) >> 1, jbase = (c.x0 - 4) >> 1;
 
-    for (int t = threadIdx.x; t < (FA_R / 4) * FA_C; t += F_THREADS) {
+    constexpr int NT = (FA_R / 4) * FA_C;
+    // LR samples of task t: fetched one task ahead so their global latency hides behind the FMA block
+    auto fetch_lr = [&](int t, float (&dst)[4][F_PRE]) {
         const int grp = t / FA_C, b = t - grp * FA_C;
         const int a0 = grp * 4;
-
-        // LR samples first: their global latency overlaps the shared-memory FMA block below
-        float lrv[4][F_PRE];
         #pragma unroll
         for (int f = 0; f < F_PRE; ++f) {
             #pragma unroll
-            for (int s = 0; s < 4; ++s) lrv[s][f] = 0.0f;
+            for (int s = 0; s < 4; ++s) dst[s][f] = 0.0f;
             if (f < mpre) {
                 const int k = a.ph_k[ph][f];
                 const int oy = (P + g.sy[k]) >> 1, ox = (Q + g.sx[k]) >> 1;
-                const float* p = a.lr[k] + (ptrdiff_t)(ibase + oy - g.lr_lo) * g.w + (jbase + ox);
+                const float* p = a.lr[k] + (ptrdiff_t)(ibase + oy - g.lr_lo + a0) * g.w + (jbase + ox + b);
                 const int j = jbase + ox + b;
                 #pragma unroll
                 for (int s = 0; s < 4; ++s) {
@@ -83,10 +83,30 @@ __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __
                     bool ok = true;
                     if (CHK) ok = (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) &&
                                   (c.y0 - 4 + 2 * (a0 + s) + P >= 0) && (c.x0 - 4 + 2 * b + Q >= 0);
-                    if (ok) lrv[s][f] = __ldg(p + (ptrdiff_t)(a0 + s) * g.w + b);
+                    if (ok) dst[s][f] = __ldg(p);
+                    p += g.w;
                 }
             }
         }
+    };
+
+    float lrn[4][F_PRE];
+    if (threadIdx.x < NT) fetch_lr(threadIdx.x, lrn);
+    if (wait_stage1) {                 // first lattice: the staged hr tile is needed from here on
+        asm volatile("cp.async.wait_all;\n" ::: "memory");
+        __syncthreads();
+    }
+
+    for (int t = threadIdx.x; t < NT; t += F_THREADS) {
+        const int grp = t / FA_C, b = t - grp * FA_C;
+        const int a0 = grp * 4;
+        float lrv[4][F_PRE];
+        #pragma unroll
+        for (int f = 0; f < F_PRE; ++f) {
+            #pragma unroll
+            for (int s = 0; s < 4; ++s) lrv[s][f] = lrn[s][f];
+        }
+        if (t + F_THREADS < NT) fetch_lr(t + F_THREADS, lrn);
 
         // B at the 4 sites: staged rows 8*grp+P+1 .. +12, staged cols 2b+Q+1 .. 2b+Q+7
         float B[4] = {0.f, 0.f, 0.f, 0.f};
@@ -191,7 +211,7 @@ __device__ __noinline__ float b_direct(const FastArgs& a, const float* __restric
 __device__ __forceinline__ int clampi2(int v, int lo, int hi) { return min(max(v, lo), hi); }
 
 template <int DUMMY>
-__global__ void __launch_bounds__(F_THREADS, 2) k_ibp_fast(const __grid_constant__ FastArgs a) {
+__global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant__ FastArgs a) {
     extern __shared__ __align__(16) float sm[];
     __shared__ float R0[FT_W + 8];       // duplicates deposited on HR row 0, x = x0-4 .. x0+131
     __shared__ float C0[FT_H + 8];       // duplicates deposited on HR col 0, y = y0-4 .. y0+67
@@ -207,16 +227,17 @@ __global__ void __launch_bounds__(F_THREADS, 2) k_ibp_fast(const __grid_constant
     c.ox0 = c.x0;                c.ox1 = min(c.x0 + FT_W, g.W);
     c.ilo = max(0, g.lr_lo);     c.ihi = min(g.h, g.lr_hi);
 
-    // ---- stage 1: stage hr (zero outside image / local band) -----------------------------------------
+    // ---- stage 1: stage hr (zero outside image / local band) with 16-byte cp.async -------------------
+    // (LDGSTS: no register staging, all 11-12 copies of a thread in flight at once; src-size 0 zero-fills)
     for (int t = tid; t < FH_ROWS * (FH_COLS / 4); t += F_THREADS) {
         const int ly = t / (FH_COLS / 4), q4 = t - ly * (FH_COLS / 4);
         const int gy = c.y0 - 8 + ly, gx = c.x0 - 8 + 4 * q4;
-        float4 v = make_float4(0.f, 0.f, 0.f, 0.f);
-        if (gy >= 0 && gy < g.H && gy >= g.hr_lo && gy < g.hr_hi && gx >= 0 && gx < g.W)
-            v = __ldg(reinterpret_cast<const float4*>(a.hr_in + (size_t)(gy - g.hr_lo) * g.W + gx));
-        *reinterpret_cast<float4*>(hs + ly * FH_COLS + 4 * q4) = v;
+        const bool in = (gy >= 0 && gy < g.H && gy >= g.hr_lo && gy < g.hr_hi && gx >= 0 && gx < g.W);
+        const float* src = in ? a.hr_in + (size_t)(gy - g.hr_lo) * g.W + gx : a.hr_in;
+        const unsigned dst = (unsigned)__cvta_generic_to_shared(hs + ly * FH_COLS + 4 * q4);
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r"(dst), "l"(src), "r"(in ? 16 : 0) : "memory");
     }
-    __syncthreads();
+    asm volatile("cp.async.commit_group;\n" ::: "memory");
 
     // a tile is "edge" when any of its lattice sites could pair with a missing LR sample, sit outside
     // the image, or fall outside the rows this launch owns
@@ -228,15 +249,19 @@ __global__ void __launch_bounds__(F_THREADS, 2) k_ibp_fast(const __grid_constant
     {
         int slot = 0;
         if (!edge) {
-            if (a.ph_n[0]) { stage_forward<0, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
-            if (a.ph_n[1]) { stage_forward<0, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
-            if (a.ph_n[2]) { stage_forward<1, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
-            if (a.ph_n[3]) { stage_forward<1, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[0]) { stage_forward<0, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+            if (a.ph_n[1]) { stage_forward<0, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+            if (a.ph_n[2]) { stage_forward<1, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+            if (a.ph_n[3]) { stage_forward<1, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
         } else {
-            if (a.ph_n[0]) { stage_forward<0, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
-            if (a.ph_n[1]) { stage_forward<0, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
-            if (a.ph_n[2]) { stage_forward<1, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
-            if (a.ph_n[3]) { stage_forward<1, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2); ++slot; }
+            if (a.ph_n[0]) { stage_forward<0, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+            if (a.ph_n[1]) { stage_forward<0, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+            if (a.ph_n[2]) { stage_forward<1, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+            if (a.ph_n[3]) { stage_forward<1, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
+        }
+        if (slot == 0) {                 // no frames at all: still finish stage 1
+            asm volatile("cp.async.wait_all;\n" ::: "memory");
+            __syncthreads();
         }
     }
 
