@@ -53,56 +53,67 @@ struct TileCtx {
 };
 
 // ---- stage 2: B on lattice (P,Q), residuals, accumulation ------------------------------------------
-template <int P, int Q, bool CHK>
+// M > 0: exactly M (<= 4) frames live on this lattice and the tile needs no bounds checks: everything is
+//        compile-time unrolled.  M == 0: general instantiation (edge tiles, more than 4 frames per lattice).
+template <int P, int Q, int M>
 __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __restrict__ hs,
                                               float* __restrict__ plane, const TileCtx& c, float& e2,
                                               bool wait_stage1) {
+    constexpr bool CHK = (M == 0);
+    constexpr int  NF  = CHK ? F_PRE : M;               // prefetched frames
     const IbpGeom& g = a.g;
     constexpr int ph = P * 2 + Q;
     const int m = a.ph_n[ph];
     const int mpre = m < F_PRE ? m : F_PRE;
     const int ibase = (c.y0 - 4) >> 1, jbase = (c.x0 - 4) >> 1;
-
+    const int w = g.w;
     constexpr int NT = (FA_R / 4) * FA_C;
+
+    // per-frame LR base pointers for this tile: sample of site (a,b) is pk[f][a*w + b]
+    const float* pk[NF];
+    int oyf[NF], oxf[NF];
+    #pragma unroll
+    for (int f = 0; f < NF; ++f) {
+        const int k = a.ph_k[ph][f < mpre ? f : 0];
+        oyf[f] = (P + g.sy[k]) >> 1; oxf[f] = (Q + g.sx[k]) >> 1;
+        pk[f] = a.lr[k] + (ptrdiff_t)(ibase + oyf[f] - g.lr_lo) * w + (jbase + oxf[f]);
+    }
+
     // LR samples of task t: fetched one task ahead so their global latency hides behind the FMA block
-    auto fetch_lr = [&](int t, float (&dst)[4][F_PRE]) {
+    auto fetch_lr = [&](int t, float (&dst)[4][NF]) {
         const int grp = t / FA_C, b = t - grp * FA_C;
         const int a0 = grp * 4;
+        const int off = a0 * w + b;
         #pragma unroll
-        for (int f = 0; f < F_PRE; ++f) {
+        for (int f = 0; f < NF; ++f) {
             #pragma unroll
-            for (int s = 0; s < 4; ++s) dst[s][f] = 0.0f;
-            if (f < mpre) {
-                const int k = a.ph_k[ph][f];
-                const int oy = (P + g.sy[k]) >> 1, ox = (Q + g.sx[k]) >> 1;
-                const float* p = a.lr[k] + (ptrdiff_t)(ibase + oy - g.lr_lo + a0) * g.w + (jbase + ox + b);
-                const int j = jbase + ox + b;
-                #pragma unroll
-                for (int s = 0; s < 4; ++s) {
-                    const int i = ibase + oy + a0 + s;
-                    bool ok = true;
-                    if (CHK) ok = (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) &&
-                                  (c.y0 - 4 + 2 * (a0 + s) + P >= 0) && (c.x0 - 4 + 2 * b + Q >= 0);
-                    if (ok) dst[s][f] = __ldg(p);
-                    p += g.w;
+            for (int s = 0; s < 4; ++s) {
+                if (CHK) {
+                    const int i = ibase + oyf[f] + a0 + s, j = jbase + oxf[f] + b;
+                    const bool ok = (f < mpre) && (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < w) &&
+                                    (c.y0 - 4 + 2 * (a0 + s) + P >= 0) && (c.x0 - 4 + 2 * b + Q >= 0);
+                    dst[s][f] = ok ? __ldg(pk[f] + (off + s * w)) : 0.0f;
+                } else {
+                    dst[s][f] = __ldg(pk[f] + (off + s * w));
                 }
             }
         }
     };
 
-    float lrn[4][F_PRE];
+    float lrn[4][NF];
     if (threadIdx.x < NT) fetch_lr(threadIdx.x, lrn);
     if (wait_stage1) {                 // first lattice: the staged hr tile is needed from here on
         asm volatile("cp.async.wait_all;\n" ::: "memory");
         __syncthreads();
     }
 
+    #pragma unroll 1
     for (int t = threadIdx.x; t < NT; t += F_THREADS) {
         const int grp = t / FA_C, b = t - grp * FA_C;
         const int a0 = grp * 4;
-        float lrv[4][F_PRE];
+        float lrv[4][NF];
         #pragma unroll
-        for (int f = 0; f < F_PRE; ++f) {
+        for (int f = 0; f < NF; ++f) {
             #pragma unroll
             for (int s = 0; s < 4; ++s) lrv[s][f] = lrn[s][f];
         }
@@ -130,39 +141,64 @@ __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __
             }
         }
 
-        #pragma unroll
-        for (int s = 0; s < 4; ++s) {
-            const int yg = c.y0 - 4 + 2 * (a0 + s) + P, xg = c.x0 - 4 + 2 * b + Q;
-            const bool own = (yg >= c.oy0) && (yg < c.oy1) && (xg >= c.ox0) && (xg < c.ox1);
-            float acc = 0.0f, sq = 0.0f;
+        if (!CHK) {
+            // owned sites: plane rows 2..33 and cols 2..65 (the rest is halo recomputed by neighbours)
+            const float cm = (b >= 2 && b < FA_C - 2) ? 1.0f : 0.0f;
+            const float mlo = (grp == 0) ? 0.0f : cm, mhi = (grp == FA_R / 4 - 1) ? 0.0f : cm;
             #pragma unroll
-            for (int f = 0; f < F_PRE; ++f) {
-                if (f < mpre) {
-                    bool ok = true;
-                    if (CHK) {
-                        const int k = a.ph_k[ph][f];
-                        const int i = ibase + ((P + g.sy[k]) >> 1) + a0 + s, j = jbase + ((Q + g.sx[k]) >> 1) + b;
-                        ok = (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) && (yg >= 0) && (xg >= 0);
-                    }
+            for (int s = 0; s < 4; ++s) {
+                float acc = 0.0f, sq = 0.0f;
+                #pragma unroll
+                for (int f = 0; f < NF; ++f) {
+                    const float e = lrv[s][f] - B[s];
+                    acc += e;
+                    sq = fmaf(e, e, sq);
+                }
+                e2 = fmaf(s < 2 ? mlo : mhi, sq, e2);
+                plane[(a0 + s) * FA_C + b] = acc;
+            }
+        } else {
+            #pragma unroll
+            for (int s = 0; s < 4; ++s) {
+                const int yg = c.y0 - 4 + 2 * (a0 + s) + P, xg = c.x0 - 4 + 2 * b + Q;
+                const bool own = (yg >= c.oy0) && (yg < c.oy1) && (xg >= c.ox0) && (xg < c.ox1);
+                float acc = 0.0f, sq = 0.0f;
+                #pragma unroll
+                for (int f = 0; f < NF; ++f) {
+                    const int i = ibase + oyf[f] + a0 + s, j = jbase + oxf[f] + b;
+                    const bool ok = (f < mpre) && (i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < w) && (yg >= 0) && (xg >= 0);
                     if (ok) {
                         const float e = lrv[s][f] - B[s];
                         acc += e;
                         sq = fmaf(e, e, sq);
                     }
                 }
-            }
-            for (int f = F_PRE; f < m; ++f) {            // more than 4 frames on one lattice: rare
-                const int k = a.ph_k[ph][f];
-                const int i = ibase + ((P + g.sy[k]) >> 1) + a0 + s, j = jbase + ((Q + g.sx[k]) >> 1) + b;
-                if ((i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < g.w) && (yg >= 0) && (xg >= 0)) {
-                    const float e = __ldg(a.lr[k] + (ptrdiff_t)(i - g.lr_lo) * g.w + j) - B[s];
-                    acc += e;
-                    sq = fmaf(e, e, sq);
+                for (int f = F_PRE; f < m; ++f) {            // more than 4 frames on one lattice: rare
+                    const int k = a.ph_k[ph][f];
+                    const int i = ibase + ((P + g.sy[k]) >> 1) + a0 + s, j = jbase + ((Q + g.sx[k]) >> 1) + b;
+                    if ((i >= c.ilo) && (i < c.ihi) && (j >= 0) && (j < w) && (yg >= 0) && (xg >= 0)) {
+                        const float e = __ldg(a.lr[k] + (ptrdiff_t)(i - g.lr_lo) * w + j) - B[s];
+                        acc += e;
+                        sq = fmaf(e, e, sq);
+                    }
                 }
+                if (own) e2 += sq;
+                plane[(a0 + s) * FA_C + b] = acc;
             }
-            if (own) e2 += sq;
-            plane[(a0 + s) * FA_C + b] = acc;
         }
+    }
+}
+
+template <int P, int Q>
+__device__ __forceinline__ void forward_dispatch(const FastArgs& a, const float* __restrict__ hs, float* __restrict__ plane,
+                                                 const TileCtx& c, float& e2, bool wait_stage1, bool edge) {
+    const int m = a.ph_n[P * 2 + Q];
+    if (edge || m > F_PRE) { stage_forward<P, Q, 0>(a, hs, plane, c, e2, wait_stage1); return; }
+    switch (m) {
+        case 1: stage_forward<P, Q, 1>(a, hs, plane, c, e2, wait_stage1); break;
+        case 2: stage_forward<P, Q, 2>(a, hs, plane, c, e2, wait_stage1); break;
+        case 3: stage_forward<P, Q, 3>(a, hs, plane, c, e2, wait_stage1); break;
+        default: stage_forward<P, Q, 4>(a, hs, plane, c, e2, wait_stage1); break;
     }
 }
 
@@ -215,7 +251,7 @@ __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant
     extern __shared__ __align__(16) float sm[];
     __shared__ float R0[FT_W + 8];       // duplicates deposited on HR row 0, x = x0-4 .. x0+131
     __shared__ float C0[FT_H + 8];       // duplicates deposited on HR col 0, y = y0-4 .. y0+67
-    __shared__ double red[F_THREADS / 32];
+    __shared__ float red[F_THREADS / 32];
     const IbpGeom& g = a.g;
     float* hs = sm;                                        // FH_ROWS x FH_COLS
     float* planes = sm + FH_ROWS * FH_COLS;                // one FA_R x FA_C plane per active lattice
@@ -228,16 +264,33 @@ __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant
     c.ilo = max(0, g.lr_lo);     c.ihi = min(g.h, g.lr_hi);
 
     // ---- stage 1: stage hr (zero outside image / local band) with 16-byte cp.async -------------------
-    // (LDGSTS: no register staging, all 11-12 copies of a thread in flight at once; src-size 0 zero-fills)
-    for (int t = tid; t < FH_ROWS * (FH_COLS / 4); t += F_THREADS) {
-        const int ly = t / (FH_COLS / 4), q4 = t - ly * (FH_COLS / 4);
-        const int gy = c.y0 - 8 + ly, gx = c.x0 - 8 + 4 * q4;
-        const bool in = (gy >= 0 && gy < g.H && gy >= g.hr_lo && gy < g.hr_hi && gx >= 0 && gx < g.W);
-        const float* src = in ? a.hr_in + (size_t)(gy - g.hr_lo) * g.W + gx : a.hr_in;
-        const unsigned dst = (unsigned)__cvta_generic_to_shared(hs + ly * FH_COLS + 4 * q4);
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r"(dst), "l"(src), "r"(in ? 16 : 0) : "memory");
+    // (LDGSTS: no register staging, every copy of a thread in flight at once; src-size 0 zero-fills).
+    // One warp per staged row: 32 lanes x 16 B + 4 lanes x 16 B = the 144-float row.
+    {
+        const int lane = tid & 31, warp = tid >> 5;
+        const int ylo = max(0, g.hr_lo), yhi = min(g.H, g.hr_hi);
+        const float* src0 = a.hr_in + (ptrdiff_t)(c.y0 - 8 - g.hr_lo) * g.W + (c.x0 - 8);
+        const unsigned dst0 = (unsigned)__cvta_generic_to_shared(hs);
+        const int gxa = c.x0 - 8 + 4 * lane, gxb = c.x0 - 8 + 128 + 4 * lane;
+        const bool ca = (gxa >= 0) && (gxa < g.W), cb = (lane < 4) && (gxb < g.W);
+        #pragma unroll
+        for (int r = 0; r < FH_ROWS / 8; ++r) {
+            const int ly = warp + 8 * r;
+            const int gy = c.y0 - 8 + ly;
+            const bool rok = (gy >= ylo) && (gy < yhi);
+            const float* rs = src0 + (ptrdiff_t)ly * g.W;
+            const unsigned d = dst0 + (unsigned)(ly * FH_COLS + 4 * lane) * 4u;
+            {
+                const bool in = rok && ca;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r"(d), "l"(in ? rs + 4 * lane : a.hr_in), "r"(in ? 16 : 0) : "memory");
+            }
+            if (lane < 4) {
+                const bool in = rok && cb;
+                asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;\n" :: "r"(d + 512u), "l"(in ? rs + 128 + 4 * lane : a.hr_in), "r"(in ? 16 : 0) : "memory");
+            }
+        }
+        asm volatile("cp.async.commit_group;\n" ::: "memory");
     }
-    asm volatile("cp.async.commit_group;\n" ::: "memory");
 
     // a tile is "edge" when any of its lattice sites could pair with a missing LR sample, sit outside
     // the image, or fall outside the rows this launch owns
@@ -248,17 +301,10 @@ __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant
     float e2 = 0.0f;
     {
         int slot = 0;
-        if (!edge) {
-            if (a.ph_n[0]) { stage_forward<0, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-            if (a.ph_n[1]) { stage_forward<0, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-            if (a.ph_n[2]) { stage_forward<1, 0, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-            if (a.ph_n[3]) { stage_forward<1, 1, false>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-        } else {
-            if (a.ph_n[0]) { stage_forward<0, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-            if (a.ph_n[1]) { stage_forward<0, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-            if (a.ph_n[2]) { stage_forward<1, 0, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-            if (a.ph_n[3]) { stage_forward<1, 1, true>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0); ++slot; }
-        }
+        if (a.ph_n[0]) { forward_dispatch<0, 0>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[1]) { forward_dispatch<0, 1>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[2]) { forward_dispatch<1, 0>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[3]) { forward_dispatch<1, 1>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
         if (slot == 0) {                 // no frames at all: still finish stage 1
             asm volatile("cp.async.wait_all;\n" ::: "memory");
             __syncthreads();
@@ -379,15 +425,14 @@ __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant
     }
 
     // ---- residual energy of this tile --------------------------------------------------------------------
-    double d = (double)e2;
     #pragma unroll
-    for (int off = 16; off > 0; off >>= 1) d += __shfl_xor_sync(0xffffffffu, d, off);
-    if ((tid & 31) == 0) red[tid >> 5] = d;
+    for (int off = 16; off > 0; off >>= 1) e2 += __shfl_xor_sync(0xffffffffu, e2, off);
+    if ((tid & 31) == 0) red[tid >> 5] = e2;
     __syncthreads();
     if (tid == 0) {
         double t = 0.0;
         #pragma unroll
-        for (int i = 0; i < F_THREADS / 32; ++i) t += red[i];
+        for (int i = 0; i < F_THREADS / 32; ++i) t += (double)red[i];
         a.partial[blockIdx.y * gridDim.x + blockIdx.x] = t;
     }
 }
