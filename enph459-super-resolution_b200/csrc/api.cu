@@ -89,6 +89,17 @@ struct sr459_plan {
     AxisTap *d_fwd_ty = nullptr, *d_fwd_tx = nullptr, *d_bwd_ty = nullptr, *d_bwd_tx = nullptr;
     TapList taps_f, taps_b;
     float psf7[49] = {0};
+    bool  separable = false;          // psf7[u][v] == acol[u] * brow[v]
+    float acol[7] = {0}, brow[7] = {0};
+
+    // separable fused path: pre-summed frames per parity lattice (ibp_sep.cu)
+    int   nslot = 0, slot_pq[kMaxSlots] = {0};
+    int   slot_n[kMaxSlots] = {0}, slot_k[kMaxSlots][kMaxFrames] = {{0}};
+    float mtab[kMaxSlots][4] = {{0}};
+    float* d_s1[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
+    int   s1_rows = 0, s1_pitch = 0;
+    CUtensorMap tm_s1[kMaxSlots];
+    double* d_vsum = nullptr;
 
     // scratch
     float *d_coef_lr = nullptr, *d_zoomed = nullptr, *d_coef_pad = nullptr;
@@ -153,8 +164,48 @@ static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int 
     SR_TRY(upload_taps(p->taps_b));
     if (kh == kw && (kh % 2) == 1 && kh <= 7) {
         int r = kh / 2;
+        double k7[49] = {0};
         for (int u = 0; u < kh; ++u)
-            for (int v = 0; v < kw; ++v) p->psf7[(u + 3 - r) * 7 + (v + 3 - r)] = (float)psf[u * kw + v];
+            for (int v = 0; v < kw; ++v) {
+                k7[(u + 3 - r) * 7 + (v + 3 - r)] = psf[u * kw + v];
+                p->psf7[(u + 3 - r) * 7 + (v + 3 - r)] = (float)psf[u * kw + v];
+            }
+        // rank-1 test in double: psf == column(through the peak) x row(through the peak) / peak
+        int pu = 0, pv = 0;
+        for (int i = 0; i < 49; ++i) if (fabs(k7[i]) > fabs(k7[pu * 7 + pv])) { pu = i / 7; pv = i % 7; }
+        const double peak = k7[pu * 7 + pv];
+        if (peak != 0.0) {
+            double worst = 0.0;
+            for (int u = 0; u < 7; ++u)
+                for (int v = 0; v < 7; ++v)
+                    worst = std::max(worst, fabs(k7[u * 7 + v] - k7[u * 7 + pv] * k7[pu * 7 + v] / peak));
+            if (worst <= 1e-9 * fabs(peak)) {
+                p->separable = true;
+                for (int u = 0; u < 7; ++u) { p->acol[u] = (float)k7[u * 7 + pv]; p->brow[u] = (float)(k7[pu * 7 + u] / peak); }
+            }
+        }
+    }
+    // parity lattices of the integer HR shifts (only meaningful for |shift| <= 1)
+    if (p->is_int && p->smax <= 1 && factor == 2) {
+        for (int ph = 0; ph < 4; ++ph) {
+            int cnt = 0, ks[kMaxFrames];
+            for (int k = 0; k < n_frames; ++k)
+                if ((((p->isy[k] & 1) << 1) | (p->isx[k] & 1)) == ph) ks[cnt++] = k;
+            if (!cnt) continue;
+            const int s = p->nslot++;
+            p->slot_pq[s] = ph; p->slot_n[s] = cnt;
+            for (int f = 0; f < cnt; ++f) p->slot_k[s][f] = ks[f];
+            // frames that still have a sample on the last site row / column: those with offset 0
+            for (int ra = 0; ra < 2; ++ra)
+                for (int cb = 0; cb < 2; ++cb) {
+                    int m = 0;
+                    for (int f = 0; f < cnt; ++f) {
+                        const int oy = ((ph >> 1) + p->isy[ks[f]]) >> 1, ox = ((ph & 1) + p->isx[ks[f]]) >> 1;
+                        if ((!ra || oy == 0) && (!cb || ox == 0)) ++m;
+                    }
+                    p->mtab[s][ra * 2 + cb] = (float)m;
+                }
+        }
     }
     return SR459_OK;
 }
@@ -164,7 +215,7 @@ static void plan_free(sr459_plan* p) {
     cudaSetDevice(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
-                    p->d_partial, p->d_errors};
+                    p->d_partial, p->d_errors, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum};
     for (void* q : ptrs) if (q) cudaFree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
@@ -349,6 +400,7 @@ static int dense_launch(const sr459_plan* p, const IbpGeom& g, const float* cons
 // number of partial-sum slots one fused iteration writes, and the launch recipe
 struct FusedRecipe {
     bool use_fast;
+    bool use_sep;
     int fast_tx, fast_ty;
     DensePass all;
     int n_fast, n_all, per_iter;
@@ -360,8 +412,15 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     int fth, ftw;
     ibp_fast_tile(&fth, &ftw);
     bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1;
+    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || p->path == 4);
     bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
-    if (fast_ok && (big || p->path == 3)) {
+    if (sep_ok && (big || p->path == 4)) {
+        ibp_sep_tile(&fth, &ftw);
+        r.use_sep = true;
+        r.fast_tx = (W + ftw - 1) / ftw;
+        r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
+        r.n_fast = r.fast_tx * r.fast_ty;
+    } else if (fast_ok && p->path != 4 && (big || p->path == 3)) {
         r.use_fast = true;
         r.fast_tx = (W + ftw - 1) / ftw;
         r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
@@ -375,10 +434,64 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     return r;
 }
 
+// S1 planes + sum of V for the frames of this call (ibp_sep.cu restructuring (2))
+static int sep_prepare(sr459_plan* p, const float* const* lr, cudaStream_t st) {
+    const int rows = p->lr_hi - p->lr_lo;
+    const int pitch = (p->w + 3) & ~3;
+    if (p->s1_rows != rows || p->s1_pitch != pitch) {
+        for (int s = 0; s < kMaxSlots; ++s) if (p->d_s1[s]) { cudaFree(p->d_s1[s]); p->d_s1[s] = nullptr; }
+        p->s1_rows = rows; p->s1_pitch = pitch;
+    }
+    SR_TRY(plan_alloc(p, &p->d_vsum, 1));
+    LatticeArgs a{};
+    for (int k = 0; k < p->n; ++k) a.lr[k] = lr[k];
+    a.h = p->h; a.w = p->w; a.lr_lo = p->lr_lo; a.lr_hi = p->lr_hi;
+    a.nslot = p->nslot;
+    for (int s = 0; s < p->nslot; ++s) {
+        if (!p->d_s1[s]) {
+            SR_TRY(plan_alloc(p, &p->d_s1[s], (size_t)rows * pitch));
+            SR_TRY(sep_make_s1_map(&p->tm_s1[s], p->d_s1[s], p->w, rows, pitch));
+        }
+        a.s1[s] = p->d_s1[s];
+        a.slot_n[s] = p->slot_n[s];
+        const int P = p->slot_pq[s] >> 1, Q = p->slot_pq[s] & 1;
+        for (int f = 0; f < p->slot_n[s]; ++f) {
+            const int k = p->slot_k[s][f];
+            a.slot_k[s][f] = k;
+            a.slot_oy[s][f] = (P + p->isy[k]) >> 1;
+            a.slot_ox[s][f] = (Q + p->isx[k]) >> 1;
+        }
+    }
+    a.rows = rows; a.row0 = p->lr_lo; a.pitch = pitch;
+    a.own_a0 = p->own_i0; a.own_a1 = p->own_i1;
+    a.vsum = p->d_vsum;
+    return launch_lattice_sums(a, st);
+}
+
 static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, const float* cur, float* nxt,
                          double* partial, int uy0, int uy1, cudaStream_t st) {
     IbpGeom g;
     fill_geom(p, g, uy0, uy1);
+    if (r.use_sep) {
+        SepArgs f{};
+        SR_TRY(sep_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
+        f.g = g;
+        for (int k = 0; k < p->n; ++k) f.lr[k] = lr[k];
+        f.hr_out = nxt;
+        memcpy(f.psf, p->psf7, sizeof(f.psf));
+        memcpy(f.acol, p->acol, sizeof(f.acol));
+        memcpy(f.brow, p->brow, sizeof(f.brow));
+        f.nph = p->nslot;
+        for (int s = 0; s < p->nslot; ++s) {
+            f.tm_s1[s] = p->tm_s1[s];
+            f.ph_pq[s] = p->slot_pq[s];
+            memcpy(f.mtab[s], p->mtab[s], sizeof(f.mtab[s]));
+        }
+        f.s1_row0 = p->lr_lo;
+        f.tiles_x = r.fast_tx; f.tiles_y = r.fast_ty; f.ty_origin = uy0;
+        f.partial = partial;
+        return launch_ibp_sep(f, st);
+    }
     if (r.use_fast) {
         FastArgs f{};
         f.g = g;
@@ -410,10 +523,12 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
     SR_TRY(plan_ensure_errors(p, n_iter));
     float* cur = d_hr; float* nxt = p->d_hr2;
     const double scale = 1.0 / ((double)p->n * p->h * p->w);
+    const double* d_add = nullptr;
     if (use_fused(p)) {
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
+        if (r.use_sep) { SR_TRY(sep_prepare(p, lr, st)); d_add = p->d_vsum; }
         for (int it = 0; it < n_iter; ++it) {
             SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st));
             std::swap(cur, nxt);
@@ -426,7 +541,7 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
             std::swap(cur, nxt);
         }
     }
-    SR_TRY(launch_reduce_partials(p->d_partial, p->per_iter, n_iter, scale, p->d_errors, st));
+    SR_TRY(launch_reduce_partials(p->d_partial, p->per_iter, n_iter, scale, d_add, p->d_errors, st));
     if (cur != d_hr) SR_CUDA(cudaMemcpyAsync(d_hr, cur, hpx * sizeof(float), cudaMemcpyDeviceToDevice, st));
     return SR459_OK;
 }
@@ -655,7 +770,11 @@ void sr459_plan_destroy(sr459_plan* plan) { plan_free(plan); }
 int sr459_plan_is_integer(const sr459_plan* plan) { return plan && plan->is_int ? 1 : 0; }
 
 int sr459_plan_set_path(sr459_plan* plan, int path) {
-    if (!plan || path < 0 || path > 3) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
+    if (!plan || path < 0 || path > 4) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
+    if (path == 4 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
+        set_error("separable TMA kernel not available for this plan (needs integer |shift| <= 1, a rank-1 PSF up to 7x7, W % 4 == 0)");
+        return SR459_EUNSUPPORTED;
+    }
     if ((path == 2 || path == 3) && !fused_supported(plan)) { set_error("fused integer path not available for this plan"); return SR459_EUNSUPPORTED; }
     if (path == 3 && !(ibp_fast_supported(plan->kh, plan->kw, plan->smax) && plan->W % 4 == 0)) { set_error("fast interior kernel not available for this plan"); return SR459_EUNSUPPORTED; }
     plan->path = path;

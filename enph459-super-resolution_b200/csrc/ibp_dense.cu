@@ -187,7 +187,7 @@ int launch_ibp_dense(const DenseArgs& a, cudaStream_t st) {
 }
 
 __global__ void k_reduce_partials(const double* __restrict__ partial, int per_iter, double scale,
-                                  double* __restrict__ errors) {
+                                  const double* __restrict__ add, double* __restrict__ errors) {
     __shared__ double red[32];
     const double* p = partial + (size_t)blockIdx.x * per_iter;
     double s = 0.0;
@@ -199,14 +199,15 @@ __global__ void k_reduce_partials(const double* __restrict__ partial, int per_it
     if (threadIdx.x == 0) {
         double t = 0.0;
         for (int i = 0; i < (int)(blockDim.x >> 5); ++i) t += red[i];
+        if (add) t += *add;
         errors[blockIdx.x] = t * scale;
     }
 }
 
 int launch_reduce_partials(const double* partial, int per_iter, int n_iter, double scale,
-                           double* d_errors, cudaStream_t st) {
+                           const double* d_add, double* d_errors, cudaStream_t st) {
     if (n_iter <= 0) return SR459_OK;
-    k_reduce_partials<<<n_iter, 256, 0, st>>>(partial, per_iter, scale, d_errors);
+    k_reduce_partials<<<n_iter, 256, 0, st>>>(partial, per_iter, scale, d_add, d_errors);
     SR_LAUNCH_CHECK("k_reduce_partials");
     return SR459_OK;
 }

@@ -1,0 +1,517 @@
+// ibp_sep.cu -- fused IBP iteration for integer HR shifts and a SEPARABLE PSF: the throughput path.
+//
+// The mathematics is the body of ibp() (mono_cal_target/run_sr.py:190-209) in the closed form of
+// ibp_dense.cu.  Three exact restructurings make one iteration cost ~9 bytes and ~11 FMA per HR pixel:
+//
+//  (1) polyphase lattices.  With factor 2 and |HR shift| <= 1, frame k samples the blurred image
+//      B = conv0(hr, psf) only at the sites (y, x) = (2i - sy_k, 2j - sx_k), one of the four
+//      parity lattices (P, Q) = (sy_k & 1, sx_k & 1), and its zero-inserted, back-shifted residual
+//      (:170-176) lands on the same sites.  The nominal +-0.5 px corner shifts (quirk Q3) put all
+//      four frames on lattice (1, 1).
+//  (2) co-sited frames are pre-summed.  All frames of a lattice see the same B(site), so
+//          sum_k (lr_k - B)   = S1 - m B                    S1 = sum_k lr_k(site), m = #frames
+//          sum_k (lr_k - B)^2 = V + (S1 - m B)^2 / m        V  = sum_k (lr_k - S1/m)^2
+//      S1 (one h x w plane per active lattice) and the scalar sum of V are constant over the
+//      iterations: k_lattice_sums computes them once per ibp() call, and an iteration then reads one
+//      S1 plane per lattice instead of n LR frames (1 instead of n bytes per HR pixel).
+//  (3) the Gaussian PSF of make_gaussian_psf (:104-111) is exactly rank 1, psf = acol (x) brow, so
+//      both blurs run as a column pass and a row pass that only touch lattice rows / columns.
+//
+// One CTA (512 threads) owns a 64 x 128 HR tile:
+//   stage   TMA: hr tile + 8 px halo (80 x 144, zero fill outside the image = fftconvolve's zero
+//           padding) and the 36 x 72 S1 box of every active lattice -> shared memory, one mbarrier.
+//   forward column pass  hs -> C  (lattice rows only, float4 down the columns)
+//           row pass     C  -> B at the sites; residual S1 - m B in place over the S1 box,
+//                        residual energy of the sites the tile owns
+//   backward row pass    residual plane -> W (lattice rows, all tile columns)
+//           column pass  W -> correction, hr' = clip(hr + step/n * corr), float4 stores.
+// The ndi_shift(mode='nearest') clamps only matter on the first tile row / column ("fix-ups",
+// evaluated literally from the raw LR frames as in ibp_fast.cu); tiles that touch an image or band
+// border run the bounds-checked instantiation of the two passes that need it.
+#include "internal.h"
+#include "tma.h"
+
+#include <mutex>
+
+namespace sr459 {
+
+constexpr int ST_H = 64, ST_W = 128;              // HR tile
+constexpr int SH_ROWS = ST_H + 16, SH_COLS = ST_W + 16;   // staged hr   y0-8 .. y0+71, x0-8 .. x0+135
+constexpr int SA_R = ST_H / 2 + 4;                // 36 lattice rows   ys = y0-4+2a+P
+constexpr int SA_C = ST_W / 2 + 4;                // 68 lattice cols   xs = x0-4+2b+Q
+constexpr int SA_P = SA_C + 4;                    // pitch of a lattice plane: TMA needs a 16 B aligned first column, so
+constexpr int SA_O = 2;                           //   the S1 box starts 2 sites early and site b sits at column b + SA_O
+constexpr int SC_P = 148;                         // pitch of the column-pass plane (== 20 mod 32: conflict-free LDS.128)
+constexpr int SW_P = ST_W;                        // pitch of the backward row-pass plane
+constexpr int S_THREADS = 512;
+
+constexpr int SM_HS   = SH_ROWS * SH_COLS;                        // floats
+constexpr int SM_CPL  = ((SA_R * SC_P * 4 + 127) / 128) * 32;     // floats, 128 B multiple
+constexpr int SM_ACC  = ((SA_R * SA_P * 4 + 127) / 128) * 32;
+constexpr int SM_WD   = SA_R * SW_P;
+static_assert(SM_CPL >= SM_WD, "the first backward plane aliases the column-pass plane");
+static_assert((SM_HS * 4) % 128 == 0, "TMA destinations must be 128 B aligned");
+
+void ibp_sep_tile(int* th, int* tw) { *th = ST_H; *tw = ST_W; }
+
+bool ibp_sep_supported(int kh, int kw, int smax, bool separable, int W) {
+    return separable && kh == kw && (kh == 1 || kh == 3 || kh == 5 || kh == 7) && smax <= 1 && (W % 4) == 0;
+}
+
+// ---- tensor maps ---------------------------------------------------------------------------------------
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int encode_tile_map_f32(CUtensorMap* out, const void* base, uint64_t cols, uint64_t rows, uint64_t pitch_elems,
+                        uint32_t box_c, uint32_t box_r) {
+    static EncodeTiledFn fn = nullptr;
+    static std::once_flag once;
+    std::call_once(once, [] {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess &&
+            q == cudaDriverEntryPointSuccess)
+            fn = reinterpret_cast<EncodeTiledFn>(p);
+    });
+    if (!fn) { set_error("cuTensorMapEncodeTiled is not available from this driver"); return SR459_ECUDA; }
+    if ((reinterpret_cast<uintptr_t>(base) & 15) || ((pitch_elems * 4) & 15)) {
+        set_error("TMA needs a 16-byte aligned base and row pitch (base %p, pitch %llu floats)", base, (unsigned long long)pitch_elems);
+        return SR459_EINVAL;
+    }
+    cuuint64_t gdim[2] = {cols, rows};
+    cuuint64_t gstr[1] = {pitch_elems * 4};
+    cuuint32_t box[2] = {box_c, box_r};
+    cuuint32_t estr[2] = {1, 1};
+    CUresult r = fn(out, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 2, const_cast<void*>(base), gdim, gstr, box, estr,
+                    CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_NONE, CU_TENSOR_MAP_L2_PROMOTION_L2_128B,
+                    CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+    if (r != CUDA_SUCCESS) { set_error("cuTensorMapEncodeTiled failed with CUresult %d", (int)r); return SR459_ECUDA; }
+    return SR459_OK;
+}
+
+int sep_make_hr_map(CUtensorMap* out, const float* base, int W, int rows) {
+    return encode_tile_map_f32(out, base, (uint64_t)W, (uint64_t)rows, (uint64_t)W, SH_COLS, SH_ROWS);
+}
+int sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch) {
+    return encode_tile_map_f32(out, base, (uint64_t)w, (uint64_t)rows, (uint64_t)pitch, SA_P, SA_R);
+}
+
+// ---- lattice sums (once per ibp() call) ----------------------------------------------------------------
+__global__ void __launch_bounds__(256) k_lattice_sums(const __grid_constant__ LatticeArgs a) {
+    const int slot = blockIdx.z;
+    const int b = blockIdx.x * 256 + threadIdx.x;
+    const int ar = blockIdx.y;                         // plane row; site row index a = a.row0 + ar
+    const int ag = a.row0 + ar;
+    float v = 0.0f;
+    if (b < a.w) {
+        float x[kMaxFrames];
+        int m = 0;
+        float s = 0.0f;
+        #pragma unroll
+        for (int f = 0; f < kMaxFrames; ++f) {
+            x[f] = 0.0f;
+            if (f < a.slot_n[slot]) {
+                const int k = a.slot_k[slot][f];
+                const int i = ag + a.slot_oy[slot][f], j = b + a.slot_ox[slot][f];
+                if (i >= a.lr_lo && i < a.lr_hi && i < a.h && j < a.w) {
+                    x[f] = __ldg(a.lr[k] + (size_t)(i - a.lr_lo) * a.w + j);
+                    s += x[f];
+                    m |= 1 << f;
+                }
+            }
+        }
+        a.s1[slot][(size_t)ar * a.pitch + b] = s;
+        const int cnt = __popc(m);
+        if (cnt > 0 && ag >= a.own_a0 && ag < a.own_a1) {
+            const float mu = s / (float)cnt;
+            #pragma unroll
+            for (int f = 0; f < kMaxFrames; ++f)
+                if (m & (1 << f)) { const float d = x[f] - mu; v = fmaf(d, d, v); }
+        }
+    }
+    __shared__ double red[8];
+    double d = (double)v;
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = d;
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double t = 0.0;
+        #pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i];
+        if (t != 0.0) atomicAdd(a.vsum, t);
+    }
+}
+
+int launch_lattice_sums(const LatticeArgs& a, cudaStream_t st) {
+    if (a.nslot <= 0 || a.rows <= 0) return SR459_OK;
+    SR_CUDA(cudaMemsetAsync(a.vsum, 0, sizeof(double), st));
+    dim3 grid((a.w + 255) / 256, a.rows, a.nslot);
+    k_lattice_sums<<<grid, 256, 0, st>>>(a);
+    SR_LAUNCH_CHECK("k_lattice_sums");
+    return SR459_OK;
+}
+
+// ---- the iteration kernel ------------------------------------------------------------------------------
+struct SepTile {
+    int y0, x0;                 // tile origin (global HR)
+    int oy0, oy1, ox0, ox1;     // pixels / sites this tile owns (global HR, half open)
+    int ilo, ihi;               // LR rows that exist and are local
+};
+
+// forward column pass: C[a][lx] = sum_u acol[u] * hs[4+2a+P+3-u][lx], 36 lattice rows x 144 staged columns
+template <int P>
+__device__ __forceinline__ void fwd_colpass(const SepArgs& a, const float* __restrict__ hs, float* __restrict__ cpl) {
+    const int u = threadIdx.x;
+    if (u < (SA_R / 3) * (SH_COLS / 4)) {
+        const int rg = u / (SH_COLS / 4), g = u - rg * (SH_COLS / 4);
+        const int a0 = 3 * rg;
+        const float4* src = reinterpret_cast<const float4*>(hs + (1 + 2 * a0 + P) * SH_COLS) + g;
+        float4 v[11];
+        #pragma unroll
+        for (int r = 0; r < 11; ++r) v[r] = src[r * (SH_COLS / 4)];
+        #pragma unroll
+        for (int j = 0; j < 3; ++j) {
+            float4 o = make_float4(0.f, 0.f, 0.f, 0.f);
+            #pragma unroll
+            for (int t = 0; t < 7; ++t) {
+                const float wgt = a.acol[t];
+                const float4 x = v[6 + 2 * j - t];
+                o.x = fmaf(wgt, x.x, o.x); o.y = fmaf(wgt, x.y, o.y);
+                o.z = fmaf(wgt, x.z, o.z); o.w = fmaf(wgt, x.w, o.w);
+            }
+            *reinterpret_cast<float4*>(cpl + (a0 + j) * SC_P + 4 * g) = o;
+        }
+    }
+}
+
+// forward row pass + residual: B(a,b) = sum_v brow[v] * C[a][4+2b+Q+3-v];  acc(a,b) = S1 - m B (in place)
+template <int Q, bool EDGE>
+__device__ __forceinline__ float fwd_rowpass(const SepArgs& a, const SepTile& c, int slot, int P,
+                                             const float* __restrict__ cpl, float* __restrict__ acc) {
+    const IbpGeom& g = a.g;
+    float e2 = 0.0f;
+    const float m_int = a.mtab[slot][0];
+    #pragma unroll 1
+    for (int u = threadIdx.x; u < SA_R * (SA_C / 4); u += S_THREADS) {
+        int r, cg;
+        if (u < 576) {                       // quarter-warp = 2 rows x 4 column groups: conflict-free LDS.128
+            const int su = u >> 3, l = u & 7;
+            r = 2 * (su >> 2) + (l >> 2);
+            cg = 4 * (su & 3) + (l & 3);
+        } else {
+            r = u - 576; cg = 16;
+        }
+        const float4* p = reinterpret_cast<const float4*>(cpl + r * SC_P + 8 * cg);
+        float f[16];
+        #pragma unroll
+        for (int q = 0; q < 4; ++q) { const float4 t = p[q]; f[4 * q] = t.x; f[4 * q + 1] = t.y; f[4 * q + 2] = t.z; f[4 * q + 3] = t.w; }
+        float B[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float s = 0.0f;
+            #pragma unroll
+            for (int v = 0; v < 7; ++v) s = fmaf(a.brow[v], f[7 + 2 * j + Q - v], s);
+            B[j] = s;
+        }
+        float2* sp = reinterpret_cast<float2*>(acc + r * SA_P + SA_O + 4 * cg);
+        const float2 s2a = sp[0], s2b = sp[1];
+        const float s1[4] = {s2a.x, s2a.y, s2b.x, s2b.y};
+        float res[4];
+        if (!EDGE) {
+            const bool rown = (r >= 2) && (r < SA_R - 2);
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                res[j] = fmaf(-m_int, B[j], s1[j]);
+                const int b = 4 * cg + j;
+                if (rown && b >= 2 && b < SA_C - 2) e2 = fmaf(res[j], res[j], e2);
+            }
+        } else {
+            const int ys = c.y0 - 4 + 2 * r + P;
+            const int ag = (ys - P) >> 1;
+            const bool rv = (ys >= 0) && (ys < g.H) && (ag >= c.ilo) && (ag < c.ihi);
+            const bool rown = rv && (ys >= c.oy0) && (ys < c.oy1);
+            const int ra = (ag == g.h - 1) ? 2 : 0;
+            #pragma unroll
+            for (int j = 0; j < 4; ++j) {
+                const int xs = c.x0 - 4 + 2 * (4 * cg + j) + Q;
+                const bool valid = rv && (xs >= 0) && (xs < g.W);
+                const int bg = (xs - Q) >> 1;
+                const float m = a.mtab[slot][ra + ((bg == g.w - 1) ? 1 : 0)];
+                res[j] = valid ? fmaf(-m, B[j], s1[j]) : 0.0f;
+                if (valid && rown && xs >= c.ox0 && xs < c.ox1 && m > 0.0f) e2 += res[j] * res[j] / m;
+            }
+        }
+        sp[0] = make_float2(res[0], res[1]);
+        sp[1] = make_float2(res[2], res[3]);
+    }
+    return EDGE ? e2 : e2 / m_int;
+}
+
+// backward row pass: W[a][x] (+)= sum_b brow[3 + xs_b - x] * acc[a][b], lattice rows x 128 tile columns
+template <int Q>
+__device__ __forceinline__ void bwd_rowpass(const SepArgs& a, const float* __restrict__ acc, float* __restrict__ wd, bool add) {
+    #pragma unroll 1
+    for (int u = threadIdx.x; u < SA_R * (ST_W / 4); u += S_THREADS) {
+        const int ar = u >> 5, g = u & 31;
+        const float2* p = reinterpret_cast<const float2*>(acc + ar * SA_P + SA_O + 2 * g);
+        float t[6];
+        #pragma unroll
+        for (int q = 0; q < 3; ++q) { const float2 x = p[q]; t[2 * q] = x.x; t[2 * q + 1] = x.y; }
+        float o[4] = {0.f, 0.f, 0.f, 0.f};
+        #pragma unroll
+        for (int tt = 0; tt < 6; ++tt) {
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int diff = 2 * tt + Q - 4 - i;          // xs_b - x for b = 2g + tt, x = x0 + 4g + i
+                if (diff >= -3 && diff <= 3) o[i] = fmaf(a.brow[3 + diff], t[tt], o[i]);
+            }
+        }
+        float4* d = reinterpret_cast<float4*>(wd + ar * SW_P + 4 * g);
+        if (add) { const float4 e = *d; o[0] += e.x; o[1] += e.y; o[2] += e.z; o[3] += e.w; }
+        *d = make_float4(o[0], o[1], o[2], o[3]);
+    }
+}
+
+// backward column pass contribution of the lattice rows of parity P to a 4 x 4 pixel block
+template <int P>
+__device__ __forceinline__ void bwd_colpass(const SepArgs& a, const float* __restrict__ wd, int rg, int g, float (&o)[4][4]) {
+    const float4* p = reinterpret_cast<const float4*>(wd + (2 * rg) * SW_P) + g;
+    #pragma unroll
+    for (int tt = 0; tt < 6; ++tt) {
+        bool used = false;
+        #pragma unroll
+        for (int jj = 0; jj < 4; ++jj) { const int diff = 2 * tt + P - 4 - jj; used = used || (diff >= -3 && diff <= 3); }
+        if (!used) continue;
+        const float4 x = p[tt * (SW_P / 4)];
+        #pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+            const int diff = 2 * tt + P - 4 - jj;             // ys_a - y for a = 2rg + tt, y = y0 + 4rg + jj
+            if (diff >= -3 && diff <= 3) {
+                const float wgt = a.acol[3 + diff];
+                o[jj][0] = fmaf(wgt, x.x, o[jj][0]); o[jj][1] = fmaf(wgt, x.y, o[jj][1]);
+                o[jj][2] = fmaf(wgt, x.z, o[jj][2]); o[jj][3] = fmaf(wgt, x.w, o[jj][3]);
+            }
+        }
+    }
+}
+
+// literal B = conv0(hr, psf) at one global site from the staged tile (edge fix-ups only)
+__device__ __noinline__ float sep_b_direct(const SepArgs& a, const float* __restrict__ hs, int y0, int x0, int gy, int gx) {
+    const float* c = hs + (gy - (y0 - 8)) * SH_COLS + (gx - (x0 - 8));
+    float v = 0.0f;
+    for (int u = 0; u < 7; ++u)
+        for (int w = 0; w < 7; ++w) v = fmaf(a.psf[u * 7 + w], c[(3 - u) * SH_COLS + (3 - w)], v);
+    return v;
+}
+
+__device__ __forceinline__ int sclamp(int v, int lo, int hi) { return min(max(v, lo), hi); }
+
+__global__ void __launch_bounds__(S_THREADS, 2) k_ibp_sep(const __grid_constant__ SepArgs a) {
+    extern __shared__ __align__(128) float sm[];
+    __shared__ __align__(8) uint64_t mbar;
+    __shared__ float R0[ST_W + 8];       // duplicates deposited on HR row 0, x = x0-4 .. x0+131
+    __shared__ float C0[ST_H + 8];       // duplicates deposited on HR col 0, y = y0-4 .. y0+67
+    __shared__ float red[S_THREADS / 32];
+    const IbpGeom& g = a.g;
+    float* hs   = sm;
+    float* cpl  = sm + SM_HS;
+    float* accs = cpl + SM_CPL;
+    const int tid = threadIdx.x;
+    SepTile c;
+    c.y0 = a.ty_origin + blockIdx.y * ST_H;
+    c.x0 = blockIdx.x * ST_W;
+    c.oy0 = max(c.y0, g.upd_y0); c.oy1 = min(min(c.y0 + ST_H, g.upd_y1), g.H);
+    c.ox0 = c.x0;                c.ox1 = min(c.x0 + ST_W, g.W);
+    c.ilo = max(0, g.lr_lo);     c.ihi = min(g.h, g.lr_hi);
+
+    // ---- stage: one thread arms the mbarrier and issues the TMA boxes ------------------------------------
+    if (tid == 0) {
+        mbar_init(&mbar, 1);
+        mbar_fence_init();
+        mbar_expect_tx(&mbar, (uint32_t)(4 * (SM_HS + a.nph * SA_R * SA_P)));
+        tma_load_2d(hs, &a.tm_hr, c.x0 - 8, c.y0 - 8 - g.hr_lo, &mbar);
+        for (int s = 0; s < a.nph; ++s)
+            tma_load_2d(accs + s * SM_ACC, &a.tm_s1[s], (c.x0 >> 1) - 2 - SA_O, (c.y0 >> 1) - 2 - a.s1_row0, &mbar);
+    }
+    const bool top = (c.y0 == 0), left = (c.x0 == 0);
+    const bool edge = (c.y0 < 8) || (c.x0 < 8) || (c.y0 + ST_H + 5 > g.H) || (c.x0 + ST_W + 5 > g.W) ||
+                      (c.y0 + ST_H > g.upd_y1) || (c.y0 < g.upd_y0) ||
+                      (((c.y0 - 6) >> 1) < c.ilo) || (((c.y0 + ST_H + 4) >> 1) + 1 > c.ihi);
+    __syncthreads();                                   // the barrier is initialised before anyone polls it
+    mbar_wait(&mbar, 0);
+
+    // ---- forward --------------------------------------------------------------------------------------------
+    float e2 = 0.0f;
+    int lastP = -1;
+    for (int s = 0; s < a.nph; ++s) {
+        const int P = a.ph_pq[s] >> 1, Q = a.ph_pq[s] & 1;
+        if (P != lastP) {
+            if (s) __syncthreads();                    // the previous lattice has finished reading C
+            if (P) fwd_colpass<1>(a, hs, cpl); else fwd_colpass<0>(a, hs, cpl);
+            lastP = P;
+            __syncthreads();
+        }
+        float* acc = accs + s * SM_ACC;
+        if (edge) e2 += Q ? fwd_rowpass<1, true>(a, c, s, P, cpl, acc) : fwd_rowpass<0, true>(a, c, s, P, cpl, acc);
+        else      e2 += Q ? fwd_rowpass<1, false>(a, c, s, P, cpl, acc) : fwd_rowpass<0, false>(a, c, s, P, cpl, acc);
+    }
+
+    // ---- edge fix-ups: the terms ndi_shift's clamp creates at the top / left image edges ------------------
+    if (top) {
+        // residuals deposited a second time on HR row 0 by frames with sy = -1
+        for (int t = tid; t < ST_W + 8; t += S_THREADS) {
+            const int x = c.x0 - 4 + t;
+            float v = 0.0f;
+            if (x >= 0 && x < g.W) {
+                for (int k = 0; k < g.n; ++k) {
+                    if (g.sy[k] != -1) continue;
+                    const int X = sclamp(x + g.sx[k], 0, g.W - 1);
+                    if (X & 1) continue;
+                    const int j = X >> 1;
+                    if (j >= g.w || c.ilo > 0) continue;
+                    v += __ldg(a.lr[k] + (size_t)(0 - g.lr_lo) * g.w + j) -
+                         sep_b_direct(a, hs, c.y0, c.x0, 1, sclamp(2 * j - g.sx[k], 0, g.W - 1));
+                }
+            }
+            R0[t] = v;
+        }
+        // LR row 0 of frames with sy = +1 reads B[clamp(-1)] = B[0]: MSE only
+        if (g.upd_y0 == 0 && c.ilo == 0) {
+            for (int k = 0; k < g.n; ++k) {
+                if (g.sy[k] != 1) continue;
+                for (int j = tid; j < g.w; j += S_THREADS) {
+                    const int cx = sclamp(2 * j - g.sx[k], 0, g.W - 1);
+                    if (cx < c.ox0 || cx >= c.ox1) continue;
+                    const float e = __ldg(a.lr[k] + (size_t)(0 - g.lr_lo) * g.w + j) - sep_b_direct(a, hs, c.y0, c.x0, 0, cx);
+                    e2 = fmaf(e, e, e2);
+                }
+            }
+        }
+    }
+    if (left) {
+        for (int t = tid; t < ST_H + 8; t += S_THREADS) {
+            const int y = c.y0 - 4 + t;
+            float v = 0.0f;
+            if (y >= 0 && y < g.H) {
+                for (int k = 0; k < g.n; ++k) {
+                    if (g.sx[k] != -1) continue;
+                    if (y + g.sy[k] < 0) continue;               // corner: already counted in R0
+                    const int Y = sclamp(y + g.sy[k], 0, g.H - 1);
+                    if (Y & 1) continue;
+                    const int i = Y >> 1;
+                    if (i >= c.ihi || i < c.ilo) continue;
+                    v += __ldg(a.lr[k] + (size_t)(i - g.lr_lo) * g.w + 0) -
+                         sep_b_direct(a, hs, c.y0, c.x0, sclamp(2 * i - g.sy[k], 0, g.H - 1), 1);
+                }
+            }
+            C0[t] = v;
+        }
+        // LR col 0 of frames with sx = +1 reads B[., clamp(-1)] = B[., 0]: MSE only
+        for (int k = 0; k < g.n; ++k) {
+            if (g.sx[k] != 1) continue;
+            for (int t = tid; t < ST_H / 2 + 2; t += S_THREADS) {
+                const int i = (c.y0 >> 1) - 1 + t;
+                if (i < c.ilo || i >= c.ihi) continue;
+                const int cy = 2 * i - g.sy[k];
+                if (cy < 0 || cy < c.oy0 || cy >= c.oy1) continue;
+                const float e = __ldg(a.lr[k] + (size_t)(i - g.lr_lo) * g.w + 0) - sep_b_direct(a, hs, c.y0, c.x0, cy, 0);
+                e2 = fmaf(e, e, e2);
+            }
+        }
+    }
+    __syncthreads();                                   // residual planes complete, C free
+
+    // ---- backward row pass: one W plane per active row parity ----------------------------------------------
+    int wd0o = -1, wd1o = -1;                          // offsets (floats) of the W planes of row parity 0 / 1
+    {
+        int nplanes = 0;
+        for (int s = 0; s < a.nph; ++s) {
+            const int P = a.ph_pq[s] >> 1, Q = a.ph_pq[s] & 1;
+            int wo = P ? wd1o : wd0o;
+            const bool add = wo >= 0;
+            if (!add) {
+                wo = nplanes++ ? SM_HS + SM_CPL + a.nph * SM_ACC : SM_HS;
+                if (P) wd1o = wo; else wd0o = wo;
+            }
+            if (Q) bwd_rowpass<1>(a, accs + s * SM_ACC, sm + wo, add); else bwd_rowpass<0>(a, accs + s * SM_ACC, sm + wo, add);
+        }
+    }
+    __syncthreads();
+
+    // ---- backward column pass, update, clip, store ----------------------------------------------------------
+    {
+        const int rg = tid >> 5, gq = tid & 31;
+        float o[4][4];
+        #pragma unroll
+        for (int jj = 0; jj < 4; ++jj) { o[jj][0] = o[jj][1] = o[jj][2] = o[jj][3] = 0.f; }
+        if (wd0o >= 0) bwd_colpass<0>(a, sm + wd0o, rg, gq, o);
+        if (wd1o >= 0) bwd_colpass<1>(a, sm + wd1o, rg, gq, o);
+        const int gx = c.x0 + 4 * gq;
+        #pragma unroll
+        for (int jj = 0; jj < 4; ++jj) {
+            const int ly = 4 * rg + jj;
+            const int gy = c.y0 + ly;
+            if (edge) {
+                if (gy < c.oy0 || gy >= c.oy1 || gx >= c.ox1) continue;
+                if (top && gy <= 3) {
+                    for (int tb = 0; tb < 7; ++tb) {
+                        const float w = a.psf[(3 - gy) * 7 + tb];
+                        #pragma unroll
+                        for (int i = 0; i < 4; ++i) o[jj][i] = fmaf(w, R0[gx + i + tb - 3 - (c.x0 - 4)], o[jj][i]);
+                    }
+                }
+                if (left && gx <= 3) {
+                    for (int ta = 0; ta < 7; ++ta) {
+                        const float cv = C0[gy + ta - 3 - (c.y0 - 4)];
+                        #pragma unroll
+                        for (int i = 0; i < 4; ++i)
+                            if (3 - (gx + i) >= 0) o[jj][i] = fmaf(a.psf[ta * 7 + (3 - (gx + i))], cv, o[jj][i]);
+                    }
+                }
+            }
+            const float4 hv = *reinterpret_cast<const float4*>(hs + (ly + 8) * SH_COLS + 4 * gq + 8);
+            float4 r;
+            r.x = fminf(fmaxf(fmaf(g.alpha, o[jj][0], hv.x), g.lo), g.hi);
+            r.y = fminf(fmaxf(fmaf(g.alpha, o[jj][1], hv.y), g.lo), g.hi);
+            r.z = fminf(fmaxf(fmaf(g.alpha, o[jj][2], hv.z), g.lo), g.hi);
+            r.w = fminf(fmaxf(fmaf(g.alpha, o[jj][3], hv.w), g.lo), g.hi);
+            *reinterpret_cast<float4*>(a.hr_out + (size_t)(gy - g.hr_lo) * g.W + gx) = r;
+        }
+    }
+
+    // ---- residual energy of this tile ----------------------------------------------------------------------
+    #pragma unroll
+    for (int off = 16; off > 0; off >>= 1) e2 += __shfl_xor_sync(0xffffffffu, e2, off);
+    if ((tid & 31) == 0) red[tid >> 5] = e2;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+        #pragma unroll
+        for (int i = 0; i < S_THREADS / 32; ++i) t += (double)red[i];
+        a.partial[blockIdx.y * gridDim.x + blockIdx.x] = t;
+    }
+}
+
+size_t ibp_sep_smem(int nph, int nrowpar) {
+    return sizeof(float) * ((size_t)SM_HS + SM_CPL + (size_t)nph * SM_ACC + (nrowpar > 1 ? SM_WD : 0));
+}
+
+int launch_ibp_sep(const SepArgs& a, cudaStream_t st) {
+    if (a.tiles_x <= 0 || a.tiles_y <= 0) return SR459_OK;
+    int rowpar = 0;
+    for (int s = 0; s < a.nph; ++s) rowpar |= 1 << (a.ph_pq[s] >> 1);
+    const size_t smem = ibp_sep_smem(a.nph, rowpar == 3 ? 2 : 1);
+    static size_t configured = 0;
+    if (smem > configured) {
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = smem;
+    }
+    dim3 grid(a.tiles_x, a.tiles_y);
+    k_ibp_sep<<<grid, S_THREADS, smem, st>>>(a);
+    SR_LAUNCH_CHECK("k_ibp_sep");
+    return SR459_OK;
+}
+
+}  // namespace sr459

@@ -1,5 +1,6 @@
 // internal.h -- shared declarations of the sr459 CUDA engine (not part of the public ABI).
 #pragma once
+#include <cuda.h>
 #include <cuda_runtime.h>
 #include <stdint.h>
 #include <atomic>
@@ -178,9 +179,50 @@ int  launch_ibp_fast(const FastArgs& a, cudaStream_t st);
 bool ibp_fast_supported(int kh, int kw, int smax);
 void ibp_fast_tile(int* th, int* tw);
 
-// errors[it] = sum(partials of iteration it) * scale
+// ---- separable-PSF fused iteration (ibp_sep.cu): TMA-staged tiles, pre-summed co-sited frames -------
+constexpr int kMaxSlots = 4;            // active parity lattices
+
+struct LatticeArgs {                    // k_lattice_sums: S1 planes + sum of V, once per ibp() call
+    const float* lr[kMaxFrames];
+    int h, w;                           // global LR dims
+    int lr_lo, lr_hi;                   // LR rows present in the local LR buffers
+    int nslot;
+    int slot_n[kMaxSlots];
+    int slot_k[kMaxSlots][kMaxFrames];  // frame ids on the lattice
+    int slot_oy[kMaxSlots][kMaxFrames]; // LR sample of site (a, b) is lr[a + oy][b + ox]
+    int slot_ox[kMaxSlots][kMaxFrames];
+    float* s1[kMaxSlots];               // planes: rows x pitch floats
+    int rows, row0, pitch;              // plane row r holds site row a = row0 + r
+    int own_a0, own_a1;                 // site rows whose V this launch counts
+    double* vsum;
+};
+int launch_lattice_sums(const LatticeArgs& a, cudaStream_t st);
+
+struct alignas(64) SepArgs {
+    CUtensorMap tm_hr;                  // hr_in as a {W, local rows} tensor, box 144 x 80
+    CUtensorMap tm_s1[kMaxSlots];       // S1 planes, box 72 x 36
+    IbpGeom g;
+    const float* lr[kMaxFrames];        // raw frames (edge fix-ups only)
+    float* hr_out;
+    float psf[49];                      // 7x7 row-major (fix-ups)
+    float acol[7], brow[7];             // psf[u][v] == acol[u] * brow[v]
+    int nph;
+    int ph_pq[kMaxSlots];               // P*2+Q of every active lattice, ascending
+    float mtab[kMaxSlots][4];           // frames with a sample at a site: [2*(last site row) + (last site col)]
+    int s1_row0;                        // site row held by plane row 0
+    int tiles_x, tiles_y;
+    int ty_origin;                      // global HR row of tile row 0 (even)
+    double* partial;                    // one slot per CTA
+};
+int    launch_ibp_sep(const SepArgs& a, cudaStream_t st);
+bool   ibp_sep_supported(int kh, int kw, int smax, bool separable, int W);
+void   ibp_sep_tile(int* th, int* tw);
+int    sep_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
+int    sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
+
+// errors[it] = (sum(partials of iteration it) + *d_add) * scale     (d_add may be null)
 int launch_reduce_partials(const double* partial, int per_iter, int n_iter, double scale,
-                           double* d_errors, cudaStream_t st);
+                           const double* d_add, double* d_errors, cudaStream_t st);
 
 // ---- misc kernels (misc.cu) -------------------------------------------------------
 int launch_u8_to_f32(const uint8_t* in, int64_t n, float* out, cudaStream_t st);

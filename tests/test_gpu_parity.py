@@ -160,7 +160,7 @@ def _check_against(g, native, saa, hr, errs, peak=255.0, scale=1.0, what=""):
         assert d < TOL_PSNR_DB, f"{what}: PSNR differs by {d} dB"
 
 
-@pytest.mark.parametrize("path", [0, 1, 2, 3])
+@pytest.mark.parametrize("path", [0, 1, 2, 3, 4])
 @pytest.mark.parametrize("name", ["g_int4", "g_int5", "g_real"])
 def test_integer_shift_goldens_all_paths(sr, name, path):
     g = golden(name)
@@ -240,14 +240,14 @@ def test_error_behaviour(sr):
 
 # ---------------------------------------------------------------- oracle-diff on seeded inputs, borders
 @pytest.mark.parametrize("shape", [(33, 47), (64, 96), (20, 130), (6, 6), (2, 2)])
-@pytest.mark.parametrize("path", [1, 2, 3])
+@pytest.mark.parametrize("path", [1, 2, 3, 4])
 def test_integer_paths_vs_oracle_odd_sizes(sr, shape, path):
     rng = np.random.default_rng(459)
     lrs = [rng.uniform(0, 255, shape) for _ in NOMINAL]
     psf = O.make_gaussian_psf()
     h, w = shape
-    if path == 3 and (w % 2):
-        pytest.skip("fast kernel needs W % 4 == 0")
+    if path in (3, 4) and (w % 2):
+        pytest.skip("polyphase kernels need W % 4 == 0")
     saa_o = O.shift_and_add(lrs, NOMINAL)
     hr_o, e_o = O.ibp(lrs, NOMINAL, psf, saa_o, n_iter=5)
     native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 5, path)
@@ -301,6 +301,53 @@ def test_polyphase_kernel_interior_tiles_vs_oracle(sr, shifts):
         _errs_close(errs, e_o)
 
 
+@pytest.mark.parametrize("shifts", [
+    NOMINAL,
+    [(0.0, 0.0)] + NOMINAL,                                   # mono_cal_target: two lattices, both row parities
+    [(0.0, 0.0), (0.5, 0.0), (0.0, 0.5), (0.5, 0.5)],         # all four lattices
+    [(0.5, -0.5)] * 3 + [(-0.5, -0.5)] * 3,                   # six frames on one lattice
+    [(0.0, 0.5), (-0.5, 0.0)],
+    [(0.5, 0.5), (-0.5, -0.5)],                               # frame count on the last row/col is not separable
+    [(-0.5, 0.5)],
+])
+@pytest.mark.parametrize("hw", [(160, 320), (100, 150), (33, 48)])
+def test_separable_tma_kernel_vs_oracle(sr, shifts, hw):
+    """The TMA-staged separable kernel (path 4): interior tiles, every edge kind, partial tiles,
+    images smaller than one tile; Gaussian PSF (rank 1)."""
+    rng = np.random.default_rng(22)
+    h, w = hw
+    lrs = [rng.uniform(0, 255, (h, w)) for _ in shifts]
+    psf = O.make_gaussian_psf()
+    saa_o = O.shift_and_add_integer(lrs, shifts)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, saa_o, n_iter=4)
+    native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 4, 4)
+    _close(hr, hr_o, what=f"ibp path4 {shifts} {hw}")
+    _close(hr[:8], hr_o[:8], what="top rows"); _close(hr[-8:], hr_o[-8:], what="bottom rows")
+    _close(hr[:, :8], hr_o[:, :8], what="left cols"); _close(hr[:, -8:], hr_o[:, -8:], what="right cols")
+    _errs_close(errs, e_o)
+
+
+def test_separable_kernel_small_psfs_and_anisotropic(sr):
+    rng = np.random.default_rng(23)
+    lrs = [rng.uniform(0, 255, (96, 160)) for _ in NOMINAL]
+    saa_o = O.shift_and_add_integer(lrs, NOMINAL)
+    gy = np.exp(-0.5 * (np.arange(-3, 4) / 0.7) ** 2); gx = np.exp(-0.5 * (np.arange(-3, 4) / 1.4) ** 2)
+    aniso = np.outer(gy / gy.sum(), gx / gx.sum())
+    for psf in (O.make_gaussian_psf(3, 0.6), O.make_gaussian_psf(5, 0.9), np.array([[1.0]]), aniso):
+        hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=4)
+        native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 4, 4)
+        _close(hr, hr_o, what=f"path4 psf {psf.shape}")
+        _errs_close(errs, e_o)
+
+
+def test_non_separable_psf_refuses_path4(sr):
+    plan = sr.Plan(4, 64, 64, NOMINAL, golden("g_prims")["k7"])
+    with pytest.raises(sr.Sr459Error) as ei:
+        plan.set_path(4)
+    assert ei.value.code == -4
+    plan.close()
+
+
 @pytest.mark.parametrize("ksize", [3, 5, 7, 9])
 def test_psf_sizes_integer_shifts(sr, ksize):
     rng = np.random.default_rng(12)
@@ -333,7 +380,7 @@ def test_clip_is_active_and_matches(sr):
     saa_o = O.shift_and_add(lrs, NOMINAL)
     hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=30)
     assert (hr_o == 0).any() and (hr_o == 255).any()
-    for path in (2, 3):
+    for path in (2, 3, 4):
         native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 30, path)
         _close(hr, hr_o, what=f"clip path{path}")
         _errs_close(errs, e_o)
@@ -358,8 +405,11 @@ def test_full_size_fast_equals_dense_and_properties(sr):
     assert float((mix - (2 * saa + plan.saa(other))).abs().max()) < 2e-3
     hr_fast = saa.clone(); e_fast = plan.set_path(3).ibp_(lrs, hr_fast, 6)
     hr_dense = saa.clone(); e_dense = plan.set_path(2).ibp_(lrs, hr_dense, 6)
+    hr_sep = saa.clone(); e_sep = plan.set_path(4).ibp_(lrs, hr_sep, 6)
     assert float((hr_fast - hr_dense).abs().max()) < 2e-3
+    assert float((hr_sep - hr_dense).abs().max()) < 2e-3
     np.testing.assert_allclose(e_fast, e_dense, rtol=1e-6)
+    np.testing.assert_allclose(e_sep, e_dense, rtol=1e-6)
     assert all(b < a for a, b in zip(e_fast, e_fast[1:])), "IBP residual must decrease"
     # full-size SAA against the oracle (integer shifts: zoom + clamp-gather)
     saa_o = O.shift_and_add_integer([l.cpu().numpy().astype(np.float64) for l in lrs], NOMINAL)
