@@ -36,20 +36,28 @@
 namespace sr459 {
 
 constexpr int ST_H = 64, ST_W = 128;              // HR tile
-constexpr int SH_ROWS = ST_H + 16, SH_COLS = ST_W + 16;   // staged hr   y0-8 .. y0+71, x0-8 .. x0+135
+constexpr int SH_TOP  = 7;                        // staged hr rows y0-7 .. y0+70 (the 78 rows a 7x7 PSF reaches),
+constexpr int SH_ROWS = ST_H + 14, SH_COLS = ST_W + 16;   //   cols x0-8 .. x0+135 (TMA wants a 16 B aligned first column)
 constexpr int SA_R = ST_H / 2 + 4;                // 36 lattice rows   ys = y0-4+2a+P
 constexpr int SA_C = ST_W / 2 + 4;                // 68 lattice cols   xs = x0-4+2b+Q
 constexpr int SA_P = SA_C + 4;                    // pitch of a lattice plane: TMA needs a 16 B aligned first column, so
 constexpr int SA_O = 2;                           //   the S1 box starts 2 sites early and site b sits at column b + SA_O
 constexpr int SC_P = 148;                         // pitch of the column-pass plane (== 20 mod 32: conflict-free LDS.128)
 constexpr int SW_P = ST_W;                        // pitch of the backward row-pass plane
-constexpr int S_THREADS = 512;
+#ifndef SR459_SEP_THREADS
+#define SR459_SEP_THREADS 256
+#define SR459_SEP_CTAS 3
+#endif
+constexpr int S_THREADS = SR459_SEP_THREADS;
+constexpr int S_CTAS    = SR459_SEP_CTAS;          // resident CTAs per SM the shared-memory budget is cut for
 
 constexpr int SM_HS   = SH_ROWS * SH_COLS;                        // floats
 constexpr int SM_CPL  = ((SA_R * SC_P * 4 + 127) / 128) * 32;     // floats, 128 B multiple
 constexpr int SM_ACC  = ((SA_R * SA_P * 4 + 127) / 128) * 32;
 constexpr int SM_WD   = SA_R * SW_P;
-static_assert(SM_CPL >= SM_WD, "the first backward plane aliases the column-pass plane");
+constexpr int SM_FIX  = SM_WD;                    // edge fix-up vectors live in the tail of the column-pass plane
+constexpr int FX_R0 = SM_FIX, FX_C0 = FX_R0 + ST_W + 8, FX_WR = FX_C0 + ST_H + 8, FX_WC = FX_WR + ST_W, FX_END = FX_WC + ST_H;
+static_assert(SM_CPL >= FX_END, "the first backward plane and the fix-up vectors alias the column-pass plane");
 static_assert((SM_HS * 4) % 128 == 0, "TMA destinations must be 128 B aligned");
 
 void ibp_sep_tile(int* th, int* tw) { *th = ST_H; *tw = ST_W; }
@@ -160,14 +168,14 @@ struct SepTile {
     int ilo, ihi;               // LR rows that exist and are local
 };
 
-// forward column pass: C[a][lx] = sum_u acol[u] * hs[4+2a+P+3-u][lx], 36 lattice rows x 144 staged columns
+// forward column pass: C[a][lx] = sum_u acol[u] * hs[ly_s+3-u][lx], ly_s = 4-1+2a+P, 36 lattice rows x 144 staged columns
 template <int P>
 __device__ __forceinline__ void fwd_colpass(const SepArgs& a, const float* __restrict__ hs, float* __restrict__ cpl) {
-    const int u = threadIdx.x;
-    if (u < (SA_R / 3) * (SH_COLS / 4)) {
+    #pragma unroll 1
+    for (int u = threadIdx.x; u < (SA_R / 3) * (SH_COLS / 4); u += S_THREADS) {
         const int rg = u / (SH_COLS / 4), g = u - rg * (SH_COLS / 4);
         const int a0 = 3 * rg;
-        const float4* src = reinterpret_cast<const float4*>(hs + (1 + 2 * a0 + P) * SH_COLS) + g;
+        const float4* src = reinterpret_cast<const float4*>(hs + (2 * a0 + P) * SH_COLS) + g;
         float4 v[11];
         #pragma unroll
         for (int r = 0; r < 11; ++r) v[r] = src[r * (SH_COLS / 4)];
@@ -299,7 +307,7 @@ __device__ __forceinline__ void bwd_colpass(const SepArgs& a, const float* __res
 
 // literal B = conv0(hr, psf) at one global site from the staged tile (edge fix-ups only)
 __device__ __noinline__ float sep_b_direct(const SepArgs& a, const float* __restrict__ hs, int y0, int x0, int gy, int gx) {
-    const float* c = hs + (gy - (y0 - 8)) * SH_COLS + (gx - (x0 - 8));
+    const float* c = hs + (gy - (y0 - SH_TOP)) * SH_COLS + (gx - (x0 - 8));
     float v = 0.0f;
     for (int u = 0; u < 7; ++u)
         for (int w = 0; w < 7; ++w) v = fmaf(a.psf[u * 7 + w], c[(3 - u) * SH_COLS + (3 - w)], v);
@@ -308,16 +316,18 @@ __device__ __noinline__ float sep_b_direct(const SepArgs& a, const float* __rest
 
 __device__ __forceinline__ int sclamp(int v, int lo, int hi) { return min(max(v, lo), hi); }
 
-__global__ void __launch_bounds__(S_THREADS, 2) k_ibp_sep(const __grid_constant__ SepArgs a) {
+__global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_constant__ SepArgs a) {
     extern __shared__ __align__(128) float sm[];
     __shared__ __align__(8) uint64_t mbar;
-    __shared__ float R0[ST_W + 8];       // duplicates deposited on HR row 0, x = x0-4 .. x0+131
-    __shared__ float C0[ST_H + 8];       // duplicates deposited on HR col 0, y = y0-4 .. y0+67
     __shared__ float red[S_THREADS / 32];
     const IbpGeom& g = a.g;
     float* hs   = sm;
     float* cpl  = sm + SM_HS;
     float* accs = cpl + SM_CPL;
+    float* R0 = cpl + FX_R0;             // duplicates deposited on HR row 0, x = x0-4 .. x0+131
+    float* C0 = cpl + FX_C0;             // duplicates deposited on HR col 0, y = y0-4 .. y0+67
+    float* WR = cpl + FX_WR;             // their row-passed / column-passed forms
+    float* WC = cpl + FX_WC;
     const int tid = threadIdx.x;
     SepTile c;
     c.y0 = a.ty_origin + blockIdx.y * ST_H;
@@ -331,7 +341,7 @@ __global__ void __launch_bounds__(S_THREADS, 2) k_ibp_sep(const __grid_constant_
         mbar_init(&mbar, 1);
         mbar_fence_init();
         mbar_expect_tx(&mbar, (uint32_t)(4 * (SM_HS + a.nph * SA_R * SA_P)));
-        tma_load_2d(hs, &a.tm_hr, c.x0 - 8, c.y0 - 8 - g.hr_lo, &mbar);
+        tma_load_2d(hs, &a.tm_hr, c.x0 - 8, c.y0 - SH_TOP - g.hr_lo, &mbar);
         for (int s = 0; s < a.nph; ++s)
             tma_load_2d(accs + s * SM_ACC, &a.tm_s1[s], (c.x0 >> 1) - 2 - SA_O, (c.y0 >> 1) - 2 - a.s1_row0, &mbar);
     }
@@ -359,6 +369,7 @@ __global__ void __launch_bounds__(S_THREADS, 2) k_ibp_sep(const __grid_constant_
     }
 
     // ---- edge fix-ups: the terms ndi_shift's clamp creates at the top / left image edges ------------------
+    if (top || left) __syncthreads();                  // R0 / C0 alias the column-pass plane
     if (top) {
         // residuals deposited a second time on HR row 0 by frames with sy = -1
         for (int t = tid; t < ST_W + 8; t += S_THREADS) {
@@ -438,46 +449,61 @@ __global__ void __launch_bounds__(S_THREADS, 2) k_ibp_sep(const __grid_constant_
             if (Q) bwd_rowpass<1>(a, accs + s * SM_ACC, sm + wo, add); else bwd_rowpass<0>(a, accs + s * SM_ACC, sm + wo, add);
         }
     }
+    // separable form of the duplicates: corr[y][x] += acol[3-y] * WR[x] (y <= 3) + brow[3-x] * WC[y] (x <= 3)
+    if (top) {
+        for (int t = tid; t < ST_W; t += S_THREADS) {
+            float v = 0.0f;
+            #pragma unroll
+            for (int tb = 0; tb < 7; ++tb) v = fmaf(a.brow[tb], R0[t + tb + 1], v);       // R0 index of x + tb - 3
+            WR[t] = v;
+        }
+    }
+    if (left) {
+        for (int t = tid; t < ST_H; t += S_THREADS) {
+            float v = 0.0f;
+            #pragma unroll
+            for (int ta = 0; ta < 7; ++ta) v = fmaf(a.acol[ta], C0[t + ta + 1], v);       // C0 index of y + ta - 3
+            WC[t] = v;
+        }
+    }
     __syncthreads();
 
     // ---- backward column pass, update, clip, store ----------------------------------------------------------
-    {
-        const int rg = tid >> 5, gq = tid & 31;
+    #pragma unroll 1
+    for (int u = tid; u < (ST_H / 4) * (ST_W / 4); u += S_THREADS) {
+        const int rg = u >> 5, gq = u & 31;
         float o[4][4];
         #pragma unroll
         for (int jj = 0; jj < 4; ++jj) { o[jj][0] = o[jj][1] = o[jj][2] = o[jj][3] = 0.f; }
         if (wd0o >= 0) bwd_colpass<0>(a, sm + wd0o, rg, gq, o);
         if (wd1o >= 0) bwd_colpass<1>(a, sm + wd1o, rg, gq, o);
         const int gx = c.x0 + 4 * gq;
+        float* outp = a.hr_out + (size_t)(c.y0 + 4 * rg - g.hr_lo) * g.W + gx;
+        const float* hp = hs + (4 * rg + SH_TOP) * SH_COLS + 4 * gq + 8;
         #pragma unroll
         for (int jj = 0; jj < 4; ++jj) {
-            const int ly = 4 * rg + jj;
-            const int gy = c.y0 + ly;
+            const int gy = c.y0 + 4 * rg + jj;
             if (edge) {
                 if (gy < c.oy0 || gy >= c.oy1 || gx >= c.ox1) continue;
                 if (top && gy <= 3) {
-                    for (int tb = 0; tb < 7; ++tb) {
-                        const float w = a.psf[(3 - gy) * 7 + tb];
-                        #pragma unroll
-                        for (int i = 0; i < 4; ++i) o[jj][i] = fmaf(w, R0[gx + i + tb - 3 - (c.x0 - 4)], o[jj][i]);
-                    }
+                    const float wgt = a.acol[3 - gy];
+                    const float4 wr = *reinterpret_cast<const float4*>(WR + 4 * gq);
+                    o[jj][0] = fmaf(wgt, wr.x, o[jj][0]); o[jj][1] = fmaf(wgt, wr.y, o[jj][1]);
+                    o[jj][2] = fmaf(wgt, wr.z, o[jj][2]); o[jj][3] = fmaf(wgt, wr.w, o[jj][3]);
                 }
-                if (left && gx <= 3) {
-                    for (int ta = 0; ta < 7; ++ta) {
-                        const float cv = C0[gy + ta - 3 - (c.y0 - 4)];
-                        #pragma unroll
-                        for (int i = 0; i < 4; ++i)
-                            if (3 - (gx + i) >= 0) o[jj][i] = fmaf(a.psf[ta * 7 + (3 - (gx + i))], cv, o[jj][i]);
-                    }
+                if (left && gq == 0) {
+                    const float cv = WC[4 * rg + jj];
+                    #pragma unroll
+                    for (int i = 0; i < 4; ++i) o[jj][i] = fmaf(a.brow[3 - i], cv, o[jj][i]);
                 }
             }
-            const float4 hv = *reinterpret_cast<const float4*>(hs + (ly + 8) * SH_COLS + 4 * gq + 8);
+            const float4 hv = *reinterpret_cast<const float4*>(hp + jj * SH_COLS);
             float4 r;
             r.x = fminf(fmaxf(fmaf(g.alpha, o[jj][0], hv.x), g.lo), g.hi);
             r.y = fminf(fmaxf(fmaf(g.alpha, o[jj][1], hv.y), g.lo), g.hi);
             r.z = fminf(fmaxf(fmaf(g.alpha, o[jj][2], hv.z), g.lo), g.hi);
             r.w = fminf(fmaxf(fmaf(g.alpha, o[jj][3], hv.w), g.lo), g.hi);
-            *reinterpret_cast<float4*>(a.hr_out + (size_t)(gy - g.hr_lo) * g.W + gx) = r;
+            *reinterpret_cast<float4*>(outp + (size_t)jj * g.W) = r;
         }
     }
 
