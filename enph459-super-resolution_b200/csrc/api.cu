@@ -285,7 +285,7 @@ static int run_zoom(sr459_plan* p, const float* d_lr, float* d_hr, cudaStream_t 
     ResampleSumArgs a{};
     a.coef[0] = p->d_coef_lr; a.cpitch[0] = p->w; a.n = 1;
     a.ty = p->d_zoom_y; a.tx = p->d_zoom_x; a.Hout = p->H; a.Wout = p->W; a.scale = 1.0f; a.out = d_hr;
-    return launch_resample_sum(a, st);
+    return p->factor >= 2 ? launch_resample_tile(a, st) : launch_resample_sum(a, st);
 }
 
 static int run_saa(sr459_plan* p, const float* const* lr, float* d_hr, cudaStream_t st) {
@@ -301,7 +301,7 @@ static int run_saa(sr459_plan* p, const float* const* lr, float* d_hr, cudaStrea
     a.ty = p->d_saa_ty; a.tx = p->d_saa_tx;
     if (p->is_int) {
         for (int k = 0; k < p->n; ++k) { a.coef[k] = p->d_coef_lr + k * lpx; a.cpitch[k] = p->w; }
-        return launch_resample_sum(a, st);
+        return p->factor >= 2 ? launch_resample_tile(a, st) : launch_resample_sum(a, st);
     }
     // fractional: zoom every frame, pad+prefilter the zoomed frames, evaluate the shifted splines
     SR_TRY(plan_zoom_tables(p));

@@ -87,6 +87,8 @@ struct ResampleSumArgs {
     float* out;
 };
 int launch_resample_sum(const ResampleSumArgs& a, cudaStream_t st);
+// same result for upsampling tables (factor >= 2: zoom, zoom re-indexed by integer shifts): tiled, separable
+int launch_resample_tile(const ResampleSumArgs& a, cudaStream_t st);
 
 // per frame k: sim = R_k(i,j); if lr: err = lr_k - sim stored to out_k and sum(err^2) -> partial sums
 struct ResampleErrArgs {

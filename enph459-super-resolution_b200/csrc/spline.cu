@@ -129,17 +129,36 @@ __device__ __forceinline__ float pf_fetch(const PrefilterJob& j, int Y, int X) {
 
 struct PrefilterJobs { PrefilterJob job[8]; };
 
-__global__ void __launch_bounds__(128) k_prefilter2d(const __grid_constant__ PrefilterJobs jobs) {
+// 256 threads = 8 warps.  Load / store: warp w takes tile rows w, w+8, ..., lanes run along x (coalesced).
+// Passes: one thread per line (96 columns, then the 64 interior rows); 6 CTAs are resident per SM, so
+// the serial recursions of one tile overlap the loads and stores of the others.
+__global__ void __launch_bounds__(256) k_prefilter2d(const __grid_constant__ PrefilterJobs jobs) {
     extern __shared__ float s[];
     const PrefilterJob& j = jobs.job[blockIdx.z];
     const int ty0 = blockIdx.y * PF_T, tx0 = blockIdx.x * PF_T;
     if (ty0 >= j.ny || tx0 >= j.nx) return;
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const float z = kPoleF;
 
-    for (int t = tid; t < PF_S * PF_S; t += 128) {
-        int ly = t / PF_S, lx = t - ly * PF_S;
-        s[ly * PF_P + lx] = pf_fetch(j, ty0 - PF_WARM + ly, tx0 - PF_WARM + lx);
+    // region [ty0-16, ty0+80) x [tx0-16, tx0+80) of the (virtual) coefficient array
+    const int off = (j.mode == SRC_PLAIN) ? 0 : kPad;
+    const bool fast = (j.mode != SRC_ZI_EDGEPAD) &&
+                      (ty0 - PF_WARM - off >= 0) && (ty0 + PF_T + PF_WARM - off <= j.sh) &&
+                      (tx0 - PF_WARM - off >= 0) && (tx0 + PF_T + PF_WARM - off <= j.sw);
+    if (fast) {
+        const float* src = j.src + (size_t)(ty0 - PF_WARM - off) * j.sw + (tx0 - PF_WARM - off);
+        #pragma unroll 4
+        for (int ly = warp; ly < PF_S; ly += 8) {
+            const float* row = src + (size_t)ly * j.sw;
+            float* d = s + ly * PF_P;
+            d[lane] = __ldg(row + lane); d[lane + 32] = __ldg(row + lane + 32); d[lane + 64] = __ldg(row + lane + 64);
+        }
+    } else {
+        for (int ly = warp; ly < PF_S; ly += 8) {
+            float* d = s + ly * PF_P;
+            #pragma unroll
+            for (int q = 0; q < 3; ++q) d[lane + 32 * q] = pf_fetch(j, ty0 - PF_WARM + ly, tx0 - PF_WARM + lane + 32 * q);
+        }
     }
     __syncthreads();
     // axis 0 (down the columns), all 96 columns
@@ -181,10 +200,15 @@ __global__ void __launch_bounds__(128) k_prefilter2d(const __grid_constant__ Pre
         }
     }
     __syncthreads();
-    for (int t = tid; t < PF_T * PF_T; t += 128) {
-        int ly = t / PF_T, lx = t - ly * PF_T;
-        int Y = ty0 + ly, X = tx0 + lx;
-        if (Y < j.ny && X < j.nx) j.dst[(size_t)Y * j.nx + X] = s[(PF_WARM + ly) * PF_P + PF_WARM + lx];
+    const int X0 = tx0 + lane, X1 = tx0 + lane + 32;
+    #pragma unroll 4
+    for (int ly = warp; ly < PF_T; ly += 8) {
+        const int Y = ty0 + ly;
+        if (Y >= j.ny) break;
+        const float* r = s + (PF_WARM + ly) * PF_P + PF_WARM;
+        float* d = j.dst + (size_t)Y * j.nx;
+        if (X0 < j.nx) d[X0] = r[lane];
+        if (X1 < j.nx) d[X1] = r[lane + 32];
     }
 }
 
@@ -204,7 +228,7 @@ int launch_prefilter2d(const PrefilterJob* h_jobs, int njobs, cudaStream_t st) {
             maxy = std::max(maxy, jobs.job[i].ny); maxx = std::max(maxx, jobs.job[i].nx);
         }
         dim3 grid((maxx + PF_T - 1) / PF_T, (maxy + PF_T - 1) / PF_T, cnt);
-        k_prefilter2d<<<grid, 128, smem, st>>>(jobs);
+        k_prefilter2d<<<grid, 256, smem, st>>>(jobs);
         SR_LAUNCH_CHECK("k_prefilter2d");
     }
     return SR459_OK;
@@ -252,6 +276,123 @@ int launch_resample_sum(const ResampleSumArgs& a, cudaStream_t st) {
     dim3 grid((a.Wout + 31) / 32, (a.Hout + 7) / 8), block(32, 8);
     k_resample_sum<<<grid, block, 0, st>>>(a);
     SR_LAUNCH_CHECK("k_resample_sum");
+    return SR459_OK;
+}
+
+// ------------------------------------------------------------------------------------
+// tiled separable resampling for UPSAMPLING tables (zoom, and zoom re-indexed by integer shifts)
+// ------------------------------------------------------------------------------------
+// out[y][x] = scale * sum_k sum_i wy_k[y][i] * ( sum_j wx_k[x][j] * coef_k[iy_k[y][i]][ix_k[x][j]] )
+// One CTA owns a 64 x 128 output tile.  Per frame: the coefficient rows / columns the tile's table
+// entries touch (at most 38 x 70 for a factor >= 2) are staged in shared memory, an x pass evaluates
+// every staged row at the tile's 128 columns, and a y pass accumulates 8 rows x 4 columns per thread
+// in registers.  8 FMA and ~6 shared-memory loads per output and frame instead of 16 + 16 global loads.
+constexpr int ZT_H = 64, ZT_W = 128;
+constexpr int ZR_R = ZT_H / 2 + 6, ZR_C = ZT_W / 2 + 6;     // staged coefficient region (rows x cols)
+constexpr int ZR_P = ZR_C + 1;
+
+__global__ void __launch_bounds__(256) k_resample_tile(const __grid_constant__ ResampleSumArgs a) {
+    __shared__ float R[ZR_R * ZR_P];            // staged coefficients
+    __shared__ __align__(16) float T[ZR_R * ZT_W];   // x-passed rows
+    __shared__ __align__(16) AxisTap sty[ZT_H];
+    __shared__ int bnd[4];                      // rmin, rmax, cmin, cmax
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y0 = blockIdx.y * ZT_H, x0 = blockIdx.x * ZT_W;
+    const int th = min(ZT_H, a.Hout - y0), tw = min(ZT_W, a.Wout - x0);
+    const int xq = tid & 31, yq = tid >> 5;     // y pass: columns 4xq..4xq+3, rows 8yq..8yq+7
+    float acc[8][4];
+    #pragma unroll
+    for (int i = 0; i < 8; ++i) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f; }
+
+    for (int k = 0; k < a.n; ++k) {
+        const AxisTap* ty = a.ty + (size_t)k * a.Hout + y0;
+        const AxisTap* tx = a.tx + (size_t)k * a.Wout + x0;
+        // ---- bounds of the coefficient region, table rows of the tile -> shared memory -------------------
+        if (warp == 0) {
+            int lo = 0x7fffffff, hi = -1;
+            for (int y = lane; y < th; y += 32) {
+                const AxisTap t = load_tap(ty + y);
+                sty[y] = t;
+                lo = min(lo, min(min(t.idx[0], t.idx[1]), min(t.idx[2], t.idx[3])));
+                hi = max(hi, max(max(t.idx[0], t.idx[1]), max(t.idx[2], t.idx[3])));
+            }
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+            if (lane == 0) { bnd[0] = lo; bnd[1] = hi; }
+        } else if (warp == 1) {
+            int lo = 0x7fffffff, hi = -1;
+            for (int x = lane; x < tw; x += 32) {
+                const int4 i4 = __ldg(reinterpret_cast<const int4*>(tx + x));
+                lo = min(lo, min(min(i4.x, i4.y), min(i4.z, i4.w)));
+                hi = max(hi, max(max(i4.x, i4.y), max(i4.z, i4.w)));
+            }
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+            if (lane == 0) { bnd[2] = lo; bnd[3] = hi; }
+        }
+        __syncthreads();                          // also: the previous frame's y pass is done with T
+        const int rmin = bnd[0], cmin = bnd[2];
+        const int nr = min(bnd[1] - rmin + 1, ZR_R), nc = min(bnd[3] - cmin + 1, ZR_C);
+        // ---- stage ----------------------------------------------------------------------------------------
+        {
+            const float* src = a.coef[k] + (size_t)rmin * a.cpitch[k] + cmin;
+            for (int rr = warp; rr < nr; rr += 8) {
+                const float* row = src + (size_t)rr * a.cpitch[k];
+                for (int cc = lane; cc < nc; cc += 32) R[rr * ZR_P + cc] = __ldg(row + cc);
+            }
+        }
+        __syncthreads();
+        // ---- x pass: T[rr][x] -----------------------------------------------------------------------------
+        {
+            const int x = tid & (ZT_W - 1), half = tid >> 7;
+            if (x < tw) {
+                const AxisTap t = load_tap(tx + x);
+                const int o0 = t.idx[0] - cmin, o1 = t.idx[1] - cmin, o2 = t.idx[2] - cmin, o3 = t.idx[3] - cmin;
+                #pragma unroll 2
+                for (int rr = half; rr < nr; rr += 2) {
+                    const float* r = R + rr * ZR_P;
+                    T[rr * ZT_W + x] = fmaf(t.w[3], r[o3], fmaf(t.w[2], r[o2], fmaf(t.w[1], r[o1], t.w[0] * r[o0])));
+                }
+            } else {
+                for (int rr = half; rr < nr; rr += 2) T[rr * ZT_W + x] = 0.0f;
+            }
+        }
+        __syncthreads();
+        // ---- y pass ---------------------------------------------------------------------------------------
+        #pragma unroll
+        for (int i = 0; i < 8; ++i) {
+            const int y = 8 * yq + i;
+            if (y < th) {
+                const AxisTap t = sty[y];
+                const float4* tp = reinterpret_cast<const float4*>(T) + xq;
+                #pragma unroll
+                for (int q = 0; q < 4; ++q) {
+                    const float4 v = tp[(t.idx[q] - rmin) * (ZT_W / 4)];
+                    acc[i][0] = fmaf(t.w[q], v.x, acc[i][0]); acc[i][1] = fmaf(t.w[q], v.y, acc[i][1]);
+                    acc[i][2] = fmaf(t.w[q], v.z, acc[i][2]); acc[i][3] = fmaf(t.w[q], v.w, acc[i][3]);
+                }
+            }
+        }
+    }
+    // ---- store ------------------------------------------------------------------------------------------------
+    const int gx = x0 + 4 * xq;
+    #pragma unroll
+    for (int i = 0; i < 8; ++i) {
+        const int gy = y0 + 8 * yq + i;
+        if (gy >= a.Hout || gx >= a.Wout) continue;
+        float* d = a.out + (size_t)gy * a.Wout + gx;
+        if (gx + 3 < a.Wout && (a.Wout & 3) == 0) {
+            *reinterpret_cast<float4*>(d) = make_float4(acc[i][0] * a.scale, acc[i][1] * a.scale, acc[i][2] * a.scale, acc[i][3] * a.scale);
+        } else {
+            for (int q = 0; q < 4 && gx + q < a.Wout; ++q) d[q] = acc[i][q] * a.scale;
+        }
+    }
+}
+
+int launch_resample_tile(const ResampleSumArgs& a, cudaStream_t st) {
+    dim3 grid((a.Wout + ZT_W - 1) / ZT_W, (a.Hout + ZT_H - 1) / ZT_H);
+    k_resample_tile<<<grid, 256, 0, st>>>(a);
+    SR_LAUNCH_CHECK("k_resample_tile");
     return SR459_OK;
 }
 
