@@ -4,6 +4,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 #include <algorithm>
 #include <new>
@@ -98,8 +99,11 @@ struct sr459_plan {
     float mtab[kMaxSlots][4] = {{0}};
     float* d_s1[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
     int   s1_rows = 0, s1_pitch = 0;
-    CUtensorMap tm_s1[kMaxSlots];
+    CUtensorMap tm_s1[kMaxSlots];     // box of ibp_sep.cu
+    CUtensorMap tm_s1w[kMaxSlots];    // box of ibp_ws.cu
     double* d_vsum = nullptr;
+    int*  d_counters = nullptr; int counters_cap = 0;   // per-iteration tile counters of the pipelined kernel
+    int   n_sm = 0;
 
     // scratch
     float *d_coef_lr = nullptr, *d_zoomed = nullptr, *d_coef_pad = nullptr;
@@ -215,7 +219,7 @@ static void plan_free(sr459_plan* p) {
     cudaSetDevice(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
-                    p->d_partial, p->d_errors, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum};
+                    p->d_partial, p->d_errors, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
     for (void* q : ptrs) if (q) cudaFree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
@@ -401,6 +405,7 @@ static int dense_launch(const sr459_plan* p, const IbpGeom& g, const float* cons
 struct FusedRecipe {
     bool use_fast;
     bool use_sep;
+    bool use_ws;
     int fast_tx, fast_ty;
     DensePass all;
     int n_fast, n_all, per_iter;
@@ -412,15 +417,16 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     int fth, ftw;
     ibp_fast_tile(&fth, &ftw);
     bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1;
-    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || p->path == 4);
+    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || p->path >= 4);
     bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
-    if (sep_ok && (big || p->path == 4)) {
-        ibp_sep_tile(&fth, &ftw);
+    if (sep_ok && (big || p->path >= 4)) {
+        r.use_ws = (p->path == 0 || p->path == 4);
+        if (r.use_ws) ibp_ws_tile(&fth, &ftw); else ibp_sep_tile(&fth, &ftw);
         r.use_sep = true;
         r.fast_tx = (W + ftw - 1) / ftw;
         r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
         r.n_fast = r.fast_tx * r.fast_ty;
-    } else if (fast_ok && p->path != 4 && (big || p->path == 3)) {
+    } else if (fast_ok && p->path < 4 && (big || p->path == 3)) {
         r.use_fast = true;
         r.fast_tx = (W + ftw - 1) / ftw;
         r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
@@ -451,6 +457,7 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, cudaStream_t st) {
         if (!p->d_s1[s]) {
             SR_TRY(plan_alloc(p, &p->d_s1[s], (size_t)rows * pitch));
             SR_TRY(sep_make_s1_map(&p->tm_s1[s], p->d_s1[s], p->w, rows, pitch));
+            SR_TRY(ws_make_s1_map(&p->tm_s1w[s], p->d_s1[s], p->w, rows, pitch));
         }
         a.s1[s] = p->d_s1[s];
         a.slot_n[s] = p->slot_n[s];
@@ -465,16 +472,28 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, cudaStream_t st) {
     a.rows = rows; a.row0 = p->lr_lo; a.pitch = pitch;
     a.own_a0 = p->own_i0; a.own_a1 = p->own_i1;
     a.vsum = p->d_vsum;
+    if (!p->n_sm) SR_CUDA(cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device));
     return launch_lattice_sums(a, st);
 }
 
+static int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
+    if (n_iter > p->counters_cap) {
+        if (p->d_counters) { cudaFree(p->d_counters); p->d_counters = nullptr; p->scratch -= (int64_t)p->counters_cap * 4; }
+        SR_TRY(plan_alloc(p, &p->d_counters, (size_t)n_iter));
+        p->counters_cap = n_iter;
+    }
+    SR_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(int) * (size_t)n_iter, st));
+    return SR459_OK;
+}
+
 static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, const float* cur, float* nxt,
-                         double* partial, int uy0, int uy1, cudaStream_t st) {
+                         double* partial, int uy0, int uy1, cudaStream_t st, int it = -1) {
     IbpGeom g;
     fill_geom(p, g, uy0, uy1);
     if (r.use_sep) {
         SepArgs f{};
-        SR_TRY(sep_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
+        if (r.use_ws) SR_TRY(ws_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
+        else          SR_TRY(sep_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
         f.g = g;
         for (int k = 0; k < p->n; ++k) f.lr[k] = lr[k];
         f.hr_out = nxt;
@@ -483,14 +502,17 @@ static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const
         memcpy(f.brow, p->brow, sizeof(f.brow));
         f.nph = p->nslot;
         for (int s = 0; s < p->nslot; ++s) {
-            f.tm_s1[s] = p->tm_s1[s];
+            f.tm_s1[s] = r.use_ws ? p->tm_s1w[s] : p->tm_s1[s];
             f.ph_pq[s] = p->slot_pq[s];
             memcpy(f.mtab[s], p->mtab[s], sizeof(f.mtab[s]));
         }
         f.s1_row0 = p->lr_lo;
         f.tiles_x = r.fast_tx; f.tiles_y = r.fast_ty; f.ty_origin = uy0;
         f.partial = partial;
-        return launch_ibp_sep(f, st);
+        f.tile_counter = (it >= 0 && p->d_counters && p->path == 6) ? p->d_counters + it : nullptr;
+        f.n_sm = p->n_sm;
+        { static const int dbg = getenv("SR459_DBG") ? atoi(getenv("SR459_DBG")) : 0; f.dbg = dbg; }
+        return r.use_ws ? launch_ibp_ws(f, st) : launch_ibp_sep(f, st);
     }
     if (r.use_fast) {
         FastArgs f{};
@@ -528,9 +550,9 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
-        if (r.use_sep) { SR_TRY(sep_prepare(p, lr, st)); d_add = p->d_vsum; }
+        if (r.use_sep) { SR_TRY(sep_prepare(p, lr, st)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
         for (int it = 0; it < n_iter; ++it) {
-            SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st));
+            SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st, it));
             std::swap(cur, nxt);
         }
     } else {
@@ -770,8 +792,8 @@ void sr459_plan_destroy(sr459_plan* plan) { plan_free(plan); }
 int sr459_plan_is_integer(const sr459_plan* plan) { return plan && plan->is_int ? 1 : 0; }
 
 int sr459_plan_set_path(sr459_plan* plan, int path) {
-    if (!plan || path < 0 || path > 4) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
-    if (path == 4 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
+    if (!plan || path < 0 || path > 6) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
+    if (path >= 4 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
         set_error("separable TMA kernel not available for this plan (needs integer |shift| <= 1, a rank-1 PSF up to 7x7, W % 4 == 0)");
         return SR459_EUNSUPPORTED;
     }

@@ -31,6 +31,7 @@
 #include "internal.h"
 #include "tma.h"
 
+#include <algorithm>
 #include <mutex>
 
 namespace sr459 {
@@ -161,18 +162,34 @@ int launch_lattice_sums(const LatticeArgs& a, cudaStream_t st) {
     return SR459_OK;
 }
 
-// ---- the iteration kernel ------------------------------------------------------------------------------
+// ---- the iteration kernels ------------------------------------------------------------------------------
 struct SepTile {
     int y0, x0;                 // tile origin (global HR)
     int oy0, oy1, ox0, ox1;     // pixels / sites this tile owns (global HR, half open)
     int ilo, ihi;               // LR rows that exist and are local
 };
 
-// forward column pass: C[a][lx] = sum_u acol[u] * hs[ly_s+3-u][lx], ly_s = 4-1+2a+P, 36 lattice rows x 144 staged columns
-template <int P>
-__device__ __forceinline__ void fwd_colpass(const SepArgs& a, const float* __restrict__ hs, float* __restrict__ cpl) {
+// the threads that work on one tile synchronise through this: the whole CTA (k_ibp_sep) or one
+// consumer group of the pipelined kernel (a named barrier)
+template <int NT, int BAR>
+struct GroupSync {
+    __device__ __forceinline__ static void sync() {
+        if (BAR == 0) __syncthreads();
+        else asm volatile("bar.sync %0, %1;\n" :: "r"(BAR), "n"(NT) : "memory");
+    }
+};
+
+// packed FP32 pair FMA (Blackwell FFMA2): (d0, d1) += w * (x0, x1), one issue slot instead of two
+__device__ __forceinline__ void ffma2(float& d0, float& d1, float w, float x0, float x1) {
+    asm("{\n.reg .b64 a, b, c;\nmov.b64 a, {%2, %2};\nmov.b64 b, {%3, %4};\nmov.b64 c, {%0, %1};\n"
+        "fma.rn.f32x2 c, a, b, c;\nmov.b64 {%0, %1}, c;\n}\n" : "+f"(d0), "+f"(d1) : "f"(w), "f"(x0), "f"(x1));
+}
+
+// forward column pass: C[a][lx] = sum_u acol[u] * hs[ly_s+3-u][lx], ly_s = 3+2a+P, 36 lattice rows x 144 staged columns
+template <int P, int NT>
+__device__ __forceinline__ void fwd_colpass(const SepArgs& a, int tid, const float* __restrict__ hs, float* __restrict__ cpl) {
     #pragma unroll 1
-    for (int u = threadIdx.x; u < (SA_R / 3) * (SH_COLS / 4); u += S_THREADS) {
+    for (int u = tid; u < (SA_R / 3) * (SH_COLS / 4); u += NT) {
         const int rg = u / (SH_COLS / 4), g = u - rg * (SH_COLS / 4);
         const int a0 = 3 * rg;
         const float4* src = reinterpret_cast<const float4*>(hs + (2 * a0 + P) * SH_COLS) + g;
@@ -186,8 +203,8 @@ __device__ __forceinline__ void fwd_colpass(const SepArgs& a, const float* __res
             for (int t = 0; t < 7; ++t) {
                 const float wgt = a.acol[t];
                 const float4 x = v[6 + 2 * j - t];
-                o.x = fmaf(wgt, x.x, o.x); o.y = fmaf(wgt, x.y, o.y);
-                o.z = fmaf(wgt, x.z, o.z); o.w = fmaf(wgt, x.w, o.w);
+                ffma2(o.x, o.y, wgt, x.x, x.y);
+                ffma2(o.z, o.w, wgt, x.z, x.w);
             }
             *reinterpret_cast<float4*>(cpl + (a0 + j) * SC_P + 4 * g) = o;
         }
@@ -195,14 +212,14 @@ __device__ __forceinline__ void fwd_colpass(const SepArgs& a, const float* __res
 }
 
 // forward row pass + residual: B(a,b) = sum_v brow[v] * C[a][4+2b+Q+3-v];  acc(a,b) = S1 - m B (in place)
-template <int Q, bool EDGE>
-__device__ __forceinline__ float fwd_rowpass(const SepArgs& a, const SepTile& c, int slot, int P,
+template <int Q, bool EDGE, int NT>
+__device__ __forceinline__ float fwd_rowpass(const SepArgs& a, int tid, const SepTile& c, int slot, int P,
                                              const float* __restrict__ cpl, float* __restrict__ acc) {
     const IbpGeom& g = a.g;
     float e2 = 0.0f;
     const float m_int = a.mtab[slot][0];
     #pragma unroll 1
-    for (int u = threadIdx.x; u < SA_R * (SA_C / 4); u += S_THREADS) {
+    for (int u = tid; u < SA_R * (SA_C / 4); u += NT) {
         int r, cg;
         if (u < 576) {                       // quarter-warp = 2 rows x 4 column groups: conflict-free LDS.128
             const int su = u >> 3, l = u & 7;
@@ -258,10 +275,10 @@ __device__ __forceinline__ float fwd_rowpass(const SepArgs& a, const SepTile& c,
 }
 
 // backward row pass: W[a][x] (+)= sum_b brow[3 + xs_b - x] * acc[a][b], lattice rows x 128 tile columns
-template <int Q>
-__device__ __forceinline__ void bwd_rowpass(const SepArgs& a, const float* __restrict__ acc, float* __restrict__ wd, bool add) {
+template <int Q, int NT>
+__device__ __forceinline__ void bwd_rowpass(const SepArgs& a, int tid, const float* __restrict__ acc, float* __restrict__ wd, bool add) {
     #pragma unroll 1
-    for (int u = threadIdx.x; u < SA_R * (ST_W / 4); u += S_THREADS) {
+    for (int u = tid; u < SA_R * (ST_W / 4); u += NT) {
         const int ar = u >> 5, g = u & 31;
         const float2* p = reinterpret_cast<const float2*>(acc + ar * SA_P + SA_O + 2 * g);
         float t[6];
@@ -298,8 +315,8 @@ __device__ __forceinline__ void bwd_colpass(const SepArgs& a, const float* __res
             const int diff = 2 * tt + P - 4 - jj;             // ys_a - y for a = 2rg + tt, y = y0 + 4rg + jj
             if (diff >= -3 && diff <= 3) {
                 const float wgt = a.acol[3 + diff];
-                o[jj][0] = fmaf(wgt, x.x, o[jj][0]); o[jj][1] = fmaf(wgt, x.y, o[jj][1]);
-                o[jj][2] = fmaf(wgt, x.z, o[jj][2]); o[jj][3] = fmaf(wgt, x.w, o[jj][3]);
+                ffma2(o[jj][0], o[jj][1], wgt, x.x, x.y);
+                ffma2(o[jj][2], o[jj][3], wgt, x.z, x.w);
             }
         }
     }
@@ -316,63 +333,15 @@ __device__ __noinline__ float sep_b_direct(const SepArgs& a, const float* __rest
 
 __device__ __forceinline__ int sclamp(int v, int lo, int hi) { return min(max(v, lo), hi); }
 
-__global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_constant__ SepArgs a) {
-    extern __shared__ __align__(128) float sm[];
-    __shared__ __align__(8) uint64_t mbar;
-    __shared__ float red[S_THREADS / 32];
+// the terms ndi_shift's clamp creates at the top / left image edges (first tile row / column only)
+template <int NT>
+__device__ __noinline__ float edge_fixups(const SepArgs& a, int tid, const SepTile& c, const float* __restrict__ hs,
+                                          float* __restrict__ R0, float* __restrict__ C0, bool top, bool left) {
     const IbpGeom& g = a.g;
-    float* hs   = sm;
-    float* cpl  = sm + SM_HS;
-    float* accs = cpl + SM_CPL;
-    float* R0 = cpl + FX_R0;             // duplicates deposited on HR row 0, x = x0-4 .. x0+131
-    float* C0 = cpl + FX_C0;             // duplicates deposited on HR col 0, y = y0-4 .. y0+67
-    float* WR = cpl + FX_WR;             // their row-passed / column-passed forms
-    float* WC = cpl + FX_WC;
-    const int tid = threadIdx.x;
-    SepTile c;
-    c.y0 = a.ty_origin + blockIdx.y * ST_H;
-    c.x0 = blockIdx.x * ST_W;
-    c.oy0 = max(c.y0, g.upd_y0); c.oy1 = min(min(c.y0 + ST_H, g.upd_y1), g.H);
-    c.ox0 = c.x0;                c.ox1 = min(c.x0 + ST_W, g.W);
-    c.ilo = max(0, g.lr_lo);     c.ihi = min(g.h, g.lr_hi);
-
-    // ---- stage: one thread arms the mbarrier and issues the TMA boxes ------------------------------------
-    if (tid == 0) {
-        mbar_init(&mbar, 1);
-        mbar_fence_init();
-        mbar_expect_tx(&mbar, (uint32_t)(4 * (SM_HS + a.nph * SA_R * SA_P)));
-        tma_load_2d(hs, &a.tm_hr, c.x0 - 8, c.y0 - SH_TOP - g.hr_lo, &mbar);
-        for (int s = 0; s < a.nph; ++s)
-            tma_load_2d(accs + s * SM_ACC, &a.tm_s1[s], (c.x0 >> 1) - 2 - SA_O, (c.y0 >> 1) - 2 - a.s1_row0, &mbar);
-    }
-    const bool top = (c.y0 == 0), left = (c.x0 == 0);
-    const bool edge = (c.y0 < 8) || (c.x0 < 8) || (c.y0 + ST_H + 5 > g.H) || (c.x0 + ST_W + 5 > g.W) ||
-                      (c.y0 + ST_H > g.upd_y1) || (c.y0 < g.upd_y0) ||
-                      (((c.y0 - 6) >> 1) < c.ilo) || (((c.y0 + ST_H + 4) >> 1) + 1 > c.ihi);
-    __syncthreads();                                   // the barrier is initialised before anyone polls it
-    mbar_wait(&mbar, 0);
-
-    // ---- forward --------------------------------------------------------------------------------------------
     float e2 = 0.0f;
-    int lastP = -1;
-    for (int s = 0; s < a.nph; ++s) {
-        const int P = a.ph_pq[s] >> 1, Q = a.ph_pq[s] & 1;
-        if (P != lastP) {
-            if (s) __syncthreads();                    // the previous lattice has finished reading C
-            if (P) fwd_colpass<1>(a, hs, cpl); else fwd_colpass<0>(a, hs, cpl);
-            lastP = P;
-            __syncthreads();
-        }
-        float* acc = accs + s * SM_ACC;
-        if (edge) e2 += Q ? fwd_rowpass<1, true>(a, c, s, P, cpl, acc) : fwd_rowpass<0, true>(a, c, s, P, cpl, acc);
-        else      e2 += Q ? fwd_rowpass<1, false>(a, c, s, P, cpl, acc) : fwd_rowpass<0, false>(a, c, s, P, cpl, acc);
-    }
-
-    // ---- edge fix-ups: the terms ndi_shift's clamp creates at the top / left image edges ------------------
-    if (top || left) __syncthreads();                  // R0 / C0 alias the column-pass plane
     if (top) {
         // residuals deposited a second time on HR row 0 by frames with sy = -1
-        for (int t = tid; t < ST_W + 8; t += S_THREADS) {
+        for (int t = tid; t < ST_W + 8; t += NT) {
             const int x = c.x0 - 4 + t;
             float v = 0.0f;
             if (x >= 0 && x < g.W) {
@@ -392,7 +361,7 @@ __global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_cons
         if (g.upd_y0 == 0 && c.ilo == 0) {
             for (int k = 0; k < g.n; ++k) {
                 if (g.sy[k] != 1) continue;
-                for (int j = tid; j < g.w; j += S_THREADS) {
+                for (int j = tid; j < g.w; j += NT) {
                     const int cx = sclamp(2 * j - g.sx[k], 0, g.W - 1);
                     if (cx < c.ox0 || cx >= c.ox1) continue;
                     const float e = __ldg(a.lr[k] + (size_t)(0 - g.lr_lo) * g.w + j) - sep_b_direct(a, hs, c.y0, c.x0, 0, cx);
@@ -402,7 +371,7 @@ __global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_cons
         }
     }
     if (left) {
-        for (int t = tid; t < ST_H + 8; t += S_THREADS) {
+        for (int t = tid; t < ST_H + 8; t += NT) {
             const int y = c.y0 - 4 + t;
             float v = 0.0f;
             if (y >= 0 && y < g.H) {
@@ -422,7 +391,7 @@ __global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_cons
         // LR col 0 of frames with sx = +1 reads B[., clamp(-1)] = B[., 0]: MSE only
         for (int k = 0; k < g.n; ++k) {
             if (g.sx[k] != 1) continue;
-            for (int t = tid; t < ST_H / 2 + 2; t += S_THREADS) {
+            for (int t = tid; t < ST_H / 2 + 2; t += NT) {
                 const int i = (c.y0 >> 1) - 1 + t;
                 if (i < c.ilo || i >= c.ihi) continue;
                 const int cy = 2 * i - g.sy[k];
@@ -432,26 +401,77 @@ __global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_cons
             }
         }
     }
-    __syncthreads();                                   // residual planes complete, C free
+    return e2;
+}
+
+__device__ __forceinline__ SepTile make_tile(const SepArgs& a, int by, int bx) {
+    const IbpGeom& g = a.g;
+    SepTile c;
+    c.y0 = a.ty_origin + by * ST_H;
+    c.x0 = bx * ST_W;
+    c.oy0 = max(c.y0, g.upd_y0); c.oy1 = min(min(c.y0 + ST_H, g.upd_y1), g.H);
+    c.ox0 = c.x0;                c.ox1 = min(c.x0 + ST_W, g.W);
+    c.ilo = max(0, g.lr_lo);     c.ihi = min(g.h, g.lr_hi);
+    return c;
+}
+
+// everything between "the TMA boxes have landed" and "the tile is stored"; returns this thread's share of
+// the tile's residual energy.  hs: staged hr, cpl: column-pass plane (later W plane + fix-up vectors),
+// accs: S1 boxes (in place: residual planes), wd2: second W plane (both row parities active)
+template <int NT, int BAR>
+__device__ __forceinline__ float process_tile(const SepArgs& a, int tid, const SepTile& c, const float* __restrict__ hs,
+                                              float* __restrict__ cpl, float* __restrict__ accs, float* __restrict__ wd2) {
+    using G = GroupSync<NT, BAR>;
+    const IbpGeom& g = a.g;
+    float* R0 = cpl + FX_R0;             // duplicates deposited on HR row 0, x = x0-4 .. x0+131
+    float* C0 = cpl + FX_C0;             // duplicates deposited on HR col 0, y = y0-4 .. y0+67
+    float* WR = cpl + FX_WR;             // their row-passed / column-passed forms
+    float* WC = cpl + FX_WC;
+    const bool top = (c.y0 == 0), left = (c.x0 == 0);
+    const bool edge = (c.y0 < 8) || (c.x0 < 8) || (c.y0 + ST_H + 5 > g.H) || (c.x0 + ST_W + 5 > g.W) ||
+                      (c.y0 + ST_H > g.upd_y1) || (c.y0 < g.upd_y0) ||
+                      (((c.y0 - 6) >> 1) < c.ilo) || (((c.y0 + ST_H + 4) >> 1) + 1 > c.ihi);
+
+    // ---- forward --------------------------------------------------------------------------------------------
+    float e2 = 0.0f;
+    int lastP = -1;
+    for (int s = 0; s < a.nph; ++s) {
+        const int P = a.ph_pq[s] >> 1, Q = a.ph_pq[s] & 1;
+        if (P != lastP) {
+            if (s) G::sync();                          // the previous lattice has finished reading C
+            if (P) fwd_colpass<1, NT>(a, tid, hs, cpl); else fwd_colpass<0, NT>(a, tid, hs, cpl);
+            lastP = P;
+            G::sync();
+        }
+        float* acc = accs + s * SM_ACC;
+        if (edge) e2 += Q ? fwd_rowpass<1, true, NT>(a, tid, c, s, P, cpl, acc) : fwd_rowpass<0, true, NT>(a, tid, c, s, P, cpl, acc);
+        else      e2 += Q ? fwd_rowpass<1, false, NT>(a, tid, c, s, P, cpl, acc) : fwd_rowpass<0, false, NT>(a, tid, c, s, P, cpl, acc);
+    }
+    if (top || left) {
+        G::sync();                                     // R0 / C0 alias the column-pass plane
+        e2 += edge_fixups<NT>(a, tid, c, hs, R0, C0, top, left);
+    }
+    G::sync();                                         // residual planes complete, C free
 
     // ---- backward row pass: one W plane per active row parity ----------------------------------------------
-    int wd0o = -1, wd1o = -1;                          // offsets (floats) of the W planes of row parity 0 / 1
+    int wsel0 = -1, wsel1 = -1;                        // which plane (0: cpl, 1: wd2) holds row parity 0 / 1
     {
         int nplanes = 0;
         for (int s = 0; s < a.nph; ++s) {
             const int P = a.ph_pq[s] >> 1, Q = a.ph_pq[s] & 1;
-            int wo = P ? wd1o : wd0o;
-            const bool add = wo >= 0;
+            int sel = P ? wsel1 : wsel0;
+            const bool add = sel >= 0;
             if (!add) {
-                wo = nplanes++ ? SM_HS + SM_CPL + a.nph * SM_ACC : SM_HS;
-                if (P) wd1o = wo; else wd0o = wo;
+                sel = nplanes++;
+                if (P) wsel1 = sel; else wsel0 = sel;
             }
-            if (Q) bwd_rowpass<1>(a, accs + s * SM_ACC, sm + wo, add); else bwd_rowpass<0>(a, accs + s * SM_ACC, sm + wo, add);
+            float* w = sel ? wd2 : cpl;
+            if (Q) bwd_rowpass<1, NT>(a, tid, accs + s * SM_ACC, w, add); else bwd_rowpass<0, NT>(a, tid, accs + s * SM_ACC, w, add);
         }
     }
     // separable form of the duplicates: corr[y][x] += acol[3-y] * WR[x] (y <= 3) + brow[3-x] * WC[y] (x <= 3)
     if (top) {
-        for (int t = tid; t < ST_W; t += S_THREADS) {
+        for (int t = tid; t < ST_W; t += NT) {
             float v = 0.0f;
             #pragma unroll
             for (int tb = 0; tb < 7; ++tb) v = fmaf(a.brow[tb], R0[t + tb + 1], v);       // R0 index of x + tb - 3
@@ -459,24 +479,24 @@ __global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_cons
         }
     }
     if (left) {
-        for (int t = tid; t < ST_H; t += S_THREADS) {
+        for (int t = tid; t < ST_H; t += NT) {
             float v = 0.0f;
             #pragma unroll
             for (int ta = 0; ta < 7; ++ta) v = fmaf(a.acol[ta], C0[t + ta + 1], v);       // C0 index of y + ta - 3
             WC[t] = v;
         }
     }
-    __syncthreads();
+    G::sync();
 
     // ---- backward column pass, update, clip, store ----------------------------------------------------------
     #pragma unroll 1
-    for (int u = tid; u < (ST_H / 4) * (ST_W / 4); u += S_THREADS) {
+    for (int u = tid; u < (ST_H / 4) * (ST_W / 4); u += NT) {
         const int rg = u >> 5, gq = u & 31;
         float o[4][4];
         #pragma unroll
         for (int jj = 0; jj < 4; ++jj) { o[jj][0] = o[jj][1] = o[jj][2] = o[jj][3] = 0.f; }
-        if (wd0o >= 0) bwd_colpass<0>(a, sm + wd0o, rg, gq, o);
-        if (wd1o >= 0) bwd_colpass<1>(a, sm + wd1o, rg, gq, o);
+        if (wsel0 >= 0) bwd_colpass<0>(a, wsel0 ? wd2 : cpl, rg, gq, o);
+        if (wsel1 >= 0) bwd_colpass<1>(a, wsel1 ? wd2 : cpl, rg, gq, o);
         const int gx = c.x0 + 4 * gq;
         float* outp = a.hr_out + (size_t)(c.y0 + 4 * rg - g.hr_lo) * g.W + gx;
         const float* hp = hs + (4 * rg + SH_TOP) * SH_COLS + 4 * gq + 8;
@@ -497,17 +517,43 @@ __global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_cons
                     for (int i = 0; i < 4; ++i) o[jj][i] = fmaf(a.brow[3 - i], cv, o[jj][i]);
                 }
             }
-            const float4 hv = *reinterpret_cast<const float4*>(hp + jj * SH_COLS);
-            float4 r;
-            r.x = fminf(fmaxf(fmaf(g.alpha, o[jj][0], hv.x), g.lo), g.hi);
-            r.y = fminf(fmaxf(fmaf(g.alpha, o[jj][1], hv.y), g.lo), g.hi);
-            r.z = fminf(fmaxf(fmaf(g.alpha, o[jj][2], hv.z), g.lo), g.hi);
-            r.w = fminf(fmaxf(fmaf(g.alpha, o[jj][3], hv.w), g.lo), g.hi);
+            float4 r = *reinterpret_cast<const float4*>(hp + jj * SH_COLS);
+            ffma2(r.x, r.y, g.alpha, o[jj][0], o[jj][1]);
+            ffma2(r.z, r.w, g.alpha, o[jj][2], o[jj][3]);
+            r.x = fminf(fmaxf(r.x, g.lo), g.hi);
+            r.y = fminf(fmaxf(r.y, g.lo), g.hi);
+            r.z = fminf(fmaxf(r.z, g.lo), g.hi);
+            r.w = fminf(fmaxf(r.w, g.lo), g.hi);
             *reinterpret_cast<float4*>(outp + (size_t)jj * g.W) = r;
         }
     }
+    return e2;
+}
 
-    // ---- residual energy of this tile ----------------------------------------------------------------------
+// ---- one tile per CTA (any number of active lattices) ----------------------------------------------------
+__global__ void __launch_bounds__(S_THREADS, S_CTAS) k_ibp_sep(const __grid_constant__ SepArgs a) {
+    extern __shared__ __align__(128) float sm[];
+    __shared__ __align__(8) uint64_t mbar;
+    __shared__ float red[S_THREADS / 32];
+    float* hs   = sm;
+    float* cpl  = sm + SM_HS;
+    float* accs = cpl + SM_CPL;
+    const int tid = threadIdx.x;
+    const SepTile c = make_tile(a, blockIdx.y, blockIdx.x);
+
+    if (tid == 0) {                                    // one thread arms the mbarrier and issues the TMA boxes
+        mbar_init(&mbar, 1);
+        mbar_fence_init();
+        mbar_expect_tx(&mbar, (uint32_t)(4 * (SM_HS + a.nph * SA_R * SA_P)));
+        tma_load_2d(hs, &a.tm_hr, c.x0 - 8, c.y0 - SH_TOP - a.g.hr_lo, &mbar);
+        for (int s = 0; s < a.nph; ++s)
+            tma_load_2d(accs + s * SM_ACC, &a.tm_s1[s], (c.x0 >> 1) - 2 - SA_O, (c.y0 >> 1) - 2 - a.s1_row0, &mbar);
+    }
+    __syncthreads();                                   // the barrier is initialised before anyone polls it
+    mbar_wait(&mbar, 0);
+
+    float e2 = process_tile<S_THREADS, 0>(a, tid, c, hs, cpl, accs, accs + a.nph * SM_ACC);
+
     #pragma unroll
     for (int off = 16; off > 0; off >>= 1) e2 += __shfl_xor_sync(0xffffffffu, e2, off);
     if ((tid & 31) == 0) red[tid >> 5] = e2;
@@ -524,8 +570,106 @@ size_t ibp_sep_smem(int nph, int nrowpar) {
     return sizeof(float) * ((size_t)SM_HS + SM_CPL + (size_t)nph * SM_ACC + (nrowpar > 1 ? SM_WD : 0));
 }
 
+// ---- persistent, pipelined variant (one active lattice): the headline configuration -----------------------
+// One CTA per SM: a producer warp streams tiles through a 3-stage ring of {hr tile, S1 box} buffers with
+// TMA; two consumer groups of PG_T threads each take every other tile.  While both groups compute, the
+// third stage is already in flight, so no warp ever waits for HBM; tiles are handed out dynamically
+// (one global counter per iteration), which also removes the wave-quantisation tail of a plain grid.
+constexpr int PG_T = 384;                         // threads per consumer group
+constexpr int PG_N = 2;                           // consumer groups
+constexpr int PG_STAGES = 3;
+constexpr int PG_THREADS = PG_N * PG_T + 32;      // + producer warp
+constexpr int SM_STAGE = SM_HS + SM_ACC;          // floats per stage
+static_assert((SM_STAGE * 4) % 128 == 0, "stage size must keep TMA destinations 128 B aligned");
+
+__global__ void __launch_bounds__(PG_THREADS, 1) k_ibp_sep_pipe(const __grid_constant__ SepArgs a) {
+    extern __shared__ __align__(128) float sm[];
+    __shared__ __align__(8) uint64_t full[PG_STAGES];
+    __shared__ __align__(8) uint64_t empty[PG_STAGES];
+    __shared__ int tile_of[PG_STAGES];
+    __shared__ float red[PG_N][PG_T / 32];
+    const int tid = threadIdx.x;
+    const int ntiles = a.tiles_x * a.tiles_y;
+
+    if (tid == 0) {
+        for (int s = 0; s < PG_STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+        mbar_fence_init();
+    }
+    __syncthreads();
+
+    if (tid >= PG_N * PG_T) {
+        // ===== producer warp (one elected lane) =====
+        if (tid == PG_N * PG_T) {
+            int ended = 0;
+            for (int k = 0; ended < PG_N; ++k) {
+                const int s = k % PG_STAGES;
+                if (k >= PG_STAGES) mbar_wait(&empty[s], ((k / PG_STAGES) - 1) & 1);
+                int t = -1;
+                if (!ended) {
+                    t = atomicAdd(a.tile_counter, 1);
+                    if (t >= ntiles) t = -1;
+                }
+                tile_of[s] = t;
+                if (t >= 0) {
+                    const int by = t / a.tiles_x, bx = t - by * a.tiles_x;
+                    const int y0 = a.ty_origin + by * ST_H, x0 = bx * ST_W;
+                    float* st = sm + s * SM_STAGE;
+                    mbar_expect_tx(&full[s], (uint32_t)(4 * (SM_HS + SA_R * SA_P)));
+                    tma_load_2d(st, &a.tm_hr, x0 - 8, y0 - SH_TOP - a.g.hr_lo, &full[s]);
+                    tma_load_2d(st + SM_HS, &a.tm_s1[0], (x0 >> 1) - 2 - SA_O, (y0 >> 1) - 2 - a.s1_row0, &full[s]);
+                } else {
+                    ++ended;
+                    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" :: "r"(smem_u32(&full[s])) : "memory");
+                }
+            }
+        }
+        return;
+    }
+
+    // ===== consumer groups =====
+    const int grp = tid / PG_T, gt = tid - grp * PG_T;
+    float* cpl = sm + PG_STAGES * SM_STAGE + grp * SM_CPL;
+    for (int k = grp; ; k += PG_N) {
+        const int s = k % PG_STAGES;
+        mbar_wait(&full[s], (k / PG_STAGES) & 1);
+        const int t = tile_of[s];
+        if (t < 0) break;
+        const int by = t / a.tiles_x, bx = t - by * a.tiles_x;
+        const SepTile c = make_tile(a, by, bx);
+        float* st = sm + s * SM_STAGE;
+        float e2 = grp == 0 ? process_tile<PG_T, 1>(a, gt, c, st, cpl, st + SM_HS, nullptr)
+                            : process_tile<PG_T, 2>(a, gt, c, st, cpl, st + SM_HS, nullptr);
+        #pragma unroll
+        for (int off = 16; off > 0; off >>= 1) e2 += __shfl_xor_sync(0xffffffffu, e2, off);
+        if ((gt & 31) == 0) red[grp][gt >> 5] = e2;
+        if (grp == 0) GroupSync<PG_T, 1>::sync(); else GroupSync<PG_T, 2>::sync();     // stage and red[] are done with
+        if (gt == 0) {
+            double sum = 0.0;
+            #pragma unroll
+            for (int i = 0; i < PG_T / 32; ++i) sum += (double)red[grp][i];
+            a.partial[t] = sum;
+            asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];\n" :: "r"(smem_u32(&empty[s])) : "memory");
+        }
+    }
+}
+
+size_t ibp_sep_pipe_smem() { return sizeof(float) * ((size_t)PG_STAGES * SM_STAGE + (size_t)PG_N * SM_CPL); }
+
 int launch_ibp_sep(const SepArgs& a, cudaStream_t st) {
     if (a.tiles_x <= 0 || a.tiles_y <= 0) return SR459_OK;
+    if (a.nph == 1 && a.tile_counter && a.n_sm > 0) {
+        const size_t smem = ibp_sep_pipe_smem();
+        static bool configured = false;
+        if (!configured) {
+            SR_CUDA(cudaFuncSetAttribute(k_ibp_sep_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+            configured = true;
+        }
+        const int ntiles = a.tiles_x * a.tiles_y;
+        const int grid = std::min(a.n_sm, (ntiles + PG_N - 1) / PG_N);
+        k_ibp_sep_pipe<<<grid, PG_THREADS, smem, st>>>(a);
+        SR_LAUNCH_CHECK("k_ibp_sep_pipe");
+        return SR459_OK;
+    }
     int rowpar = 0;
     for (int s = 0; s < a.nph; ++s) rowpar |= 1 << (a.ph_pq[s] >> 1);
     const size_t smem = ibp_sep_smem(a.nph, rowpar == 3 ? 2 : 1);

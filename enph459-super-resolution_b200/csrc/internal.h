@@ -214,11 +214,19 @@ struct alignas(64) SepArgs {
     int s1_row0;                        // site row held by plane row 0
     int tiles_x, tiles_y;
     int ty_origin;                      // global HR row of tile row 0 (even)
-    double* partial;                    // one slot per CTA
+    double* partial;                    // one slot per tile
+    int* tile_counter;                  // pipelined kernel: zeroed counter of this iteration (null: one CTA per tile)
+    int n_sm;                           // SMs of the device (grid of the pipelined kernel)
+    int dbg;                            // development probes (SR459_DBG): 1 = no arithmetic, 2 = no TMA loads
 };
 int    launch_ibp_sep(const SepArgs& a, cudaStream_t st);
 bool   ibp_sep_supported(int kh, int kw, int smax, bool separable, int W);
 void   ibp_sep_tile(int* th, int* tw);
+// warp-synchronous form of the same iteration (ibp_ws.cu): tile 64 x 112, own TMA box shapes
+int    launch_ibp_ws(const SepArgs& a, cudaStream_t st);
+void   ibp_ws_tile(int* th, int* tw);
+int    ws_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
+int    ws_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
 int    sep_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
 int    sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
 

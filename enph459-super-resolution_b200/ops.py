@@ -325,7 +325,7 @@ class Plan:
         return bool(self._lib.sr459_plan_is_integer(self._h))
 
     def set_path(self, path: int):
-        """0 auto, 1 generic stage-by-stage, 2 dense fused, 3 polyphase fused, 4 TMA separable fused."""
+        """0 auto, 1 generic stage-by-stage, 2 dense fused, 3 polyphase fused, 4 TMA separable fused (warp-synchronous), 5 four-phase form, 6 persistent pipelined form."""
         _lib.check(self._lib.sr459_plan_set_path(self._h, int(path)))
         return self
 

@@ -115,8 +115,10 @@ void sr459_plan_destroy(sr459_plan* plan);
 int sr459_plan_is_integer(const sr459_plan* plan);
 /* Force a code path, for tests: 0 = automatic, 1 = generic stage-by-stage path,
  * 2 = dense fused integer kernel, 3 = polyphase fused kernel (any 7x7 PSF),
- * 4 = TMA-staged separable-PSF fused kernel.  SR459_EUNSUPPORTED if the plan's
- * geometry cannot run the requested path.                                     */
+ * 4 = TMA-staged separable-PSF fused kernel, warp-synchronous form (the default
+ * for rank-1 PSFs), 5 = its four-phase shared-memory form, 6 = the persistent
+ * pipelined variant of 5 (single parity lattice only).
+ * SR459_EUNSUPPORTED if the plan's geometry cannot run the requested path.    */
 int sr459_plan_set_path(sr459_plan* plan, int path);
 /* Bytes of device scratch the plan holds.                                     */
 int64_t sr459_plan_scratch_bytes(const sr459_plan* plan);
