@@ -272,7 +272,7 @@ def run_b200_arm(args):
     traffic = None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("k_ibp_ws_bytes_per_launch")
+            traffic = json.load(f).get("k_ibp_stream_bytes_per_launch")
     except Exception:
         pass
     alg_job = ((n + 4) + iters * (8 + n)) * H * W
@@ -289,7 +289,7 @@ def run_b200_arm(args):
                    "parallelism": f"batch-dp{world}"},
         "stage_ms": {"saa": saa_ms, "ibp": ibp_ms, "ibp_per_iteration": k_ms},
         "job_hbm_frac": alg_job / (total_ms / args.steps * 1e-3) / 1e9 / peak,
-        "roofline": {"bound": "hbm", "kernel": "k_ibp_ws (fused IBP iteration, separable PSF, integer HR shifts)",
+        "roofline": {"bound": "hbm", "kernel": "k_ibp_stream (fused IBP iteration: register-streaming warps, TMA row ring; rank-1 PSF, integer HR shifts)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "algorithmic_bytes_per_launch": alg_iter, "peak_source": peak_src, "launch_ms": k_ms},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,

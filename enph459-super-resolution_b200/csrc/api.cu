@@ -102,6 +102,8 @@ struct sr459_plan {
     CUtensorMap tm_s1[kMaxSlots];     // box of ibp_sep.cu
     CUtensorMap tm_s1w[kMaxSlots];    // box of ibp_ws.cu
     double* d_vsum = nullptr;
+    float* d_edge = nullptr;          // ibp_stream.cu edge vectors: colS1[h], leftS1[h], rowS1[w], topS1[w], scal[4]
+    CUtensorMap tm_s1s;               // box of ibp_stream.cu (single lattice)
     int*  d_counters = nullptr; int counters_cap = 0;   // per-iteration tile counters of the pipelined kernel
     int   n_sm = 0;
 
@@ -219,7 +221,7 @@ static void plan_free(sr459_plan* p) {
     cudaSetDevice(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
-                    p->d_partial, p->d_errors, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
+                    p->d_partial, p->d_errors, p->d_edge, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
     for (void* q : ptrs) if (q) cudaFree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
@@ -406,6 +408,8 @@ struct FusedRecipe {
     bool use_fast;
     bool use_sep;
     bool use_ws;
+    bool use_stream;
+    int st_nit, st_seg, st_nseg, st_nstrip;
     int fast_tx, fast_ty;
     DensePass all;
     int n_fast, n_all, per_iter;
@@ -419,7 +423,15 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1;
     bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || p->path >= 4);
     bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
-    if (sep_ok && (big || p->path >= 4)) {
+    const bool stream_ok = sep_ok && !p->band && uy0 == 0 && uy1 == p->H && (p->path == 0 || p->path == 7) &&
+                           ibp_stream_supported(p->kh, p->kw, p->smax, p->separable, W, p->nslot);
+    if (stream_ok && (big || p->path == 7)) {
+        r.use_stream = true;
+        int n_sm = p->n_sm;
+        if (!n_sm) { cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, p->device); }
+        stream_geometry(p->H, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
+        r.n_fast = r.st_nseg * r.st_nstrip;
+    } else if (sep_ok && p->path != 7 && (big || p->path >= 4)) {
         r.use_ws = (p->path == 0 || p->path == 4);
         if (r.use_ws) ibp_ws_tile(&fth, &ftw); else ibp_sep_tile(&fth, &ftw);
         r.use_sep = true;
@@ -473,7 +485,14 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, cudaStream_t st) {
     a.own_a0 = p->own_i0; a.own_a1 = p->own_i1;
     a.vsum = p->d_vsum;
     if (!p->n_sm) SR_CUDA(cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device));
-    return launch_lattice_sums(a, st);
+    SR_TRY(launch_lattice_sums(a, st));
+    if (!p->band && p->nslot == 1) {                  // the streaming kernel's map and edge vectors
+        SR_TRY(stream_make_s1_map(&p->tm_s1s, p->d_s1[0], p->w, rows, pitch));
+        SR_TRY(plan_alloc(p, &p->d_edge, (size_t)2 * p->h + 2 * p->w + 4));
+        SR_TRY(launch_stream_edge_sums(lr, p->n, p->h, p->w, p->isy, p->isx, p->slot_pq[0] >> 1, p->slot_pq[0] & 1,
+                                       p->d_edge, p->d_vsum, st));
+    }
+    return SR459_OK;
 }
 
 static int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
@@ -490,6 +509,33 @@ static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const
                          double* partial, int uy0, int uy1, cudaStream_t st, int it = -1) {
     IbpGeom g;
     fill_geom(p, g, uy0, uy1);
+    if (r.use_stream) {
+        StreamArgs f{};
+        SR_TRY(stream_make_hr_map(&f.tm_hr, cur, p->W, p->H));
+        f.tm_s1 = p->tm_s1s;
+        f.hr_out = nxt;
+        f.H = p->H; f.W = p->W; f.h = p->h; f.w = p->w;
+        f.nit = r.st_nit; f.seg_rows = r.st_seg; f.nseg = r.st_nseg; f.nstrip = r.st_nstrip;
+        f.alpha = g.alpha; f.lo = g.lo; f.hi = g.hi;
+        memcpy(f.acol, p->acol, sizeof(f.acol));
+        memcpy(f.brow, p->brow, sizeof(f.brow));
+        memcpy(f.mtab, p->mtab[0], sizeof(f.mtab));
+        const int P = p->slot_pq[0] >> 1, Q = p->slot_pq[0] & 1;
+        f.has_left = (Q == 1);
+        f.colS1 = p->d_edge; f.leftS1 = p->d_edge + p->h; f.rowS1 = p->d_edge + 2 * p->h;
+        f.topS1 = p->d_edge + 2 * p->h + p->w; f.scal = p->d_edge + 2 * p->h + 2 * p->w;
+        for (int k = 0; k < p->n; ++k) {
+            const int oy = (P + p->isy[k]) >> 1, ox = (Q + p->isx[k]) >> 1;
+            if (p->isx[k] == -1) { f.mc[0] += 1.f; if (oy == 0) f.mc[1] += 1.f; }
+            if (p->isx[k] == +1) { f.ml[0] += 1.f; if (oy == 0) f.ml[1] += 1.f; }
+            if (p->isy[k] == -1) { f.mr[0] += 1.f; if (ox == 0) f.mr[1] += 1.f; }
+            if (p->isy[k] == +1) { f.mt[0] += 1.f; if (ox == 0) f.mt[1] += 1.f; }
+            if (p->isy[k] == -1 && p->isx[k] == -1) f.m_dupc += 1.f;
+            if (p->isy[k] == +1 && p->isx[k] == +1) f.m_msec += 1.f;
+        }
+        f.partial = partial;
+        return launch_ibp_stream(f, P, Q, st);
+    }
     if (r.use_sep) {
         SepArgs f{};
         if (r.use_ws) SR_TRY(ws_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
@@ -550,7 +596,7 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
-        if (r.use_sep) { SR_TRY(sep_prepare(p, lr, st)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
+        if (r.use_sep || r.use_stream) { SR_TRY(sep_prepare(p, lr, st)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
         for (int it = 0; it < n_iter; ++it) {
             SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st, it));
             std::swap(cur, nxt);
@@ -792,9 +838,13 @@ void sr459_plan_destroy(sr459_plan* plan) { plan_free(plan); }
 int sr459_plan_is_integer(const sr459_plan* plan) { return plan && plan->is_int ? 1 : 0; }
 
 int sr459_plan_set_path(sr459_plan* plan, int path) {
-    if (!plan || path < 0 || path > 6) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
+    if (!plan || path < 0 || path > 7) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
     if (path >= 4 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
         set_error("separable TMA kernel not available for this plan (needs integer |shift| <= 1, a rank-1 PSF up to 7x7, W % 4 == 0)");
+        return SR459_EUNSUPPORTED;
+    }
+    if (path == 7 && (plan->band || !ibp_stream_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W, plan->nslot))) {
+        set_error("streaming kernel not available for this plan (needs a single parity lattice and a whole-image plan)");
         return SR459_EUNSUPPORTED;
     }
     if ((path == 2 || path == 3) && !fused_supported(plan)) { set_error("fused integer path not available for this plan"); return SR459_EUNSUPPORTED; }

@@ -230,6 +230,35 @@ int    ws_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int 
 int    sep_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
 int    sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
 
+// ---- register-streaming fused iteration (ibp_stream.cu): one lattice, rank-1 PSF, whole image ---------
+struct alignas(64) StreamArgs {
+    CUtensorMap tm_hr;                  // hr_in as a {W, H} tensor, box 128 x 8
+    CUtensorMap tm_s1;                  // the lattice's S1 plane {w, h}, box 64 x 4
+    float* hr_out;
+    int H, W, h, w;
+    int nit;                            // loop iterations (4 lattice rows each) per warp
+    int seg_rows;                       // HR rows a warp updates = 8 nit - 6
+    int nseg, nstrip;                   // warps = nseg * nstrip
+    float alpha, lo, hi;
+    float acol[7], brow[7];
+    float mtab[4];                      // frames with a sample at a site: [2*(last site row) + (last site col)]
+    int has_left;                       // lattice column parity 1: column-0 clamp terms exist
+    const float* colS1; const float* leftS1; const float* rowS1; const float* topS1; const float* scal;
+    float mc[2], ml[2];                 // frames with sx = -1 / +1 valid at a site row: [last site row]
+    float mr[2], mt[2];                 // frames with sy = -1 / +1 valid at a site col: [last site col]
+    float m_dupc, m_msec;               // frames (-1,-1) / (+1,+1)
+    double* partial;                    // one slot per warp
+};
+struct EdgeSumArgs;
+int  launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st);
+bool ibp_stream_supported(int kh, int kw, int smax, bool separable, int W, int nslot);
+int  stream_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
+int  stream_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
+void stream_geometry(int H, int W, int n_sm, int* nit, int* seg_rows, int* nseg, int* nstrip);
+// edge vectors + their variances (added to *vsum); buf holds 2h + 2w + 4 floats: colS1, leftS1, rowS1, topS1, scal
+int  launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const int* sy, const int* sx, int P, int Q,
+                             float* buf, double* vsum, cudaStream_t st);
+
 // errors[it] = (sum(partials of iteration it) + *d_add) * scale     (d_add may be null)
 int launch_reduce_partials(const double* partial, int per_iter, int n_iter, double scale,
                            const double* d_add, double* d_errors, cudaStream_t st);

@@ -117,7 +117,9 @@ int sr459_plan_is_integer(const sr459_plan* plan);
  * 2 = dense fused integer kernel, 3 = polyphase fused kernel (any 7x7 PSF),
  * 4 = TMA-staged separable-PSF fused kernel, warp-synchronous form (the default
  * for rank-1 PSFs), 5 = its four-phase shared-memory form, 6 = the persistent
- * pipelined variant of 5 (single parity lattice only).
+ * pipelined variant of 5 (single parity lattice only), 7 = the register-streaming
+ * kernel (one warp per strip, TMA row ring; rank-1 PSF and a single parity lattice;
+ * the default when it applies).
  * SR459_EUNSUPPORTED if the plan's geometry cannot run the requested path.    */
 int sr459_plan_set_path(sr459_plan* plan, int path);
 /* Bytes of device scratch the plan holds.                                     */

@@ -160,7 +160,7 @@ def _check_against(g, native, saa, hr, errs, peak=255.0, scale=1.0, what=""):
         assert d < TOL_PSNR_DB, f"{what}: PSNR differs by {d} dB"
 
 
-@pytest.mark.parametrize("path", [0, 1, 2, 3, 4])
+@pytest.mark.parametrize("path", [0, 1, 2, 3, 4, 7])
 @pytest.mark.parametrize("name", ["g_int4", "g_int5", "g_real"])
 def test_integer_shift_goldens_all_paths(sr, name, path):
     g = golden(name)
@@ -340,6 +340,64 @@ def test_separable_kernel_small_psfs_and_anisotropic(sr):
         native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 4, 4)
         _close(hr, hr_o, what=f"path4 psf {psf.shape}")
         _errs_close(errs, e_o)
+
+
+
+# ---------------------------------------------------------------- the register-streaming kernel (path 7)
+SINGLE_LATTICE_SETS = [
+    NOMINAL,                                                  # (1,1): all four corner frames
+    [(0.5, -0.5)] * 3 + [(-0.5, -0.5)] * 3,                   # six frames, only sx = -1
+    [(0.5, 0.5), (-0.5, -0.5)],                               # frame count on the last row/col is not separable
+    [(-0.5, 0.5)],                                            # one frame
+    [(0.5, 0.5)],
+    [(0.0, 0.0)],                                             # (0,0): centre frame only
+    [(0.0, 0.0)] * 3,
+    [(0.0, 0.5), (0.0, -0.5)],                                # (0,1): column clamp terms only
+    [(0.5, 0.0), (-0.5, 0.0), (-0.5, 0.0)],                   # (1,0): row clamp terms only
+    [(0.5, -0.5)] * 8,
+]
+
+
+@pytest.mark.parametrize("shifts", SINGLE_LATTICE_SETS)
+@pytest.mark.parametrize("hw", [(160, 320), (100, 150), (33, 48), (7, 60), (2, 2), (231, 58)])
+def test_streaming_kernel_vs_oracle(sr, shifts, hw):
+    """k_ibp_stream (path 7): interior and general iterations, top segment, left strip, last site
+    row / column, partial last segment and strip, images smaller than one strip."""
+    rng = np.random.default_rng(24)
+    h, w = hw
+    lrs = [rng.uniform(0, 255, (h, w)) for _ in shifts]
+    psf = O.make_gaussian_psf()
+    saa_o = O.shift_and_add_integer(lrs, shifts)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, saa_o, n_iter=4)
+    native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 4, 7)
+    _close(hr, hr_o, what=f"ibp path7 {shifts} {hw}")
+    _close(hr[:8], hr_o[:8], what="top rows"); _close(hr[-8:], hr_o[-8:], what="bottom rows")
+    _close(hr[:, :8], hr_o[:, :8], what="left cols"); _close(hr[:, -8:], hr_o[:, -8:], what="right cols")
+    _errs_close(errs, e_o)
+
+
+def test_streaming_kernel_small_psfs_anisotropic_and_unit_range(sr):
+    rng = np.random.default_rng(25)
+    lrs = [rng.uniform(0, 255, (96, 160)) for _ in NOMINAL]
+    saa_o = O.shift_and_add_integer(lrs, NOMINAL)
+    gy = np.exp(-0.5 * (np.arange(-3, 4) / 0.7) ** 2); gx = np.exp(-0.5 * (np.arange(-3, 4) / 1.4) ** 2)
+    aniso = np.outer(gy / gy.sum(), gx / gx.sum())
+    for psf in (O.make_gaussian_psf(3, 0.6), O.make_gaussian_psf(5, 0.9), np.array([[1.0]]), aniso):
+        hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=4)
+        native, saa, hr, errs = _run_pipeline(sr, lrs, NOMINAL, psf, 4, 7)
+        _close(hr, hr_o, what=f"path7 psf {psf.shape}")
+        _errs_close(errs, e_o)
+    g = golden("g_unit")                                      # [0,1] images: tolerance 1e-4 absolute
+    res = _run_pipeline(sr, list(g["lr"]), g["shifts"], g["psf"], len(g["errors"]), 7)
+    _check_against(g, *res, peak=1.0, scale=1.0 / 255.0, what="g_unit path7")
+
+
+def test_streaming_kernel_refuses_two_lattices(sr):
+    plan = sr.Plan(5, 32, 32, [(0.0, 0.0)] + NOMINAL, O.make_gaussian_psf())
+    with pytest.raises(sr.Sr459Error) as ei:
+        plan.set_path(7)
+    assert ei.value.code == -4
+    plan.close()
 
 
 def test_non_separable_psf_refuses_path4(sr):
