@@ -453,7 +453,7 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
 }
 
 // S1 planes + sum of V for the frames of this call (ibp_sep.cu restructuring (2))
-static int sep_prepare(sr459_plan* p, const float* const* lr, cudaStream_t st) {
+static int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaStream_t st) {
     const int rows = p->lr_hi - p->lr_lo;
     const int pitch = (p->w + 3) & ~3;
     if (p->s1_rows != rows || p->s1_pitch != pitch) {
@@ -486,7 +486,7 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, cudaStream_t st) {
     a.vsum = p->d_vsum;
     if (!p->n_sm) SR_CUDA(cudaDeviceGetAttribute(&p->n_sm, cudaDevAttrMultiProcessorCount, p->device));
     SR_TRY(launch_lattice_sums(a, st));
-    if (!p->band && p->nslot == 1) {                  // the streaming kernel's map and edge vectors
+    if (stream_kernel) {                              // the streaming kernel's map and edge vectors (+ their variances)
         SR_TRY(stream_make_s1_map(&p->tm_s1s, p->d_s1[0], p->w, rows, pitch));
         SR_TRY(plan_alloc(p, &p->d_edge, (size_t)2 * p->h + 2 * p->w + 4));
         SR_TRY(launch_stream_edge_sums(lr, p->n, p->h, p->w, p->isy, p->isx, p->slot_pq[0] >> 1, p->slot_pq[0] & 1,
@@ -596,7 +596,7 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
-        if (r.use_sep || r.use_stream) { SR_TRY(sep_prepare(p, lr, st)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
+        if (r.use_sep || r.use_stream) { SR_TRY(sep_prepare(p, lr, r.use_stream, st)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
         for (int it = 0; it < n_iter; ++it) {
             SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st, it));
             std::swap(cur, nxt);

@@ -218,7 +218,11 @@ struct WarpCtx {
 // One lattice row.  T = step mod 4 fixes every register slot at compile time:
 //   hr window   row (ys + 3 - u) sits in slot (2T + 1 - u) mod 8; this step's new rows are slots 2T, 2T+1
 //   W ring      this step writes slot T; W of step j-d sits in slot (T - d) mod 4
-template <int T, int P, int Q, bool GEN, bool LEFT>
+// MODE: M_GEN = every row / ownership / store decision at run time (segment ends, image borders);
+// otherwise the site row is a valid interior one and MODE says whether the warp owns it for the MSE
+// (M_OWN) and whether this step's two HR rows are stored (M_ST).
+constexpr int M_OWN = 1, M_ST = 2, M_GEN = 4;
+template <int T, int P, int Q, int MODE, bool LEFT>
 __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const WarpCtx& c, const StreamArgs& a,
                                             const int aj, const float* __restrict__ s1row, const float* __restrict__ pf,
                                             float*& outp, const float cS, const float lS, const int lane) {
@@ -232,11 +236,14 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
     Dlo = fma2(k.A[5], WIN(5).lo, Dlo); Dhi = fma2(k.A[5], WIN(5).hi, Dhi);
     Clo = fma2(k.A[6], WIN(6).lo, Clo); Chi = fma2(k.A[6], WIN(6).hi, Chi);
     Clo = add2(Clo, Dlo); Chi = add2(Chi, Dhi);
+    constexpr bool GEN = (MODE & M_GEN) != 0;
+    constexpr bool OWN = GEN || (MODE & M_OWN) != 0;     // the residual energy is accumulated
+    constexpr bool ST  = GEN || (MODE & M_ST) != 0;      // the transposed column pass / update / stores run
     const Row h1 = WIN(6), h2 = WIN(5);                 // hr rows ys-3, ys-2: updated at the end of this step
 
     // top segments, site row ys = 1: B on HR row 0 (LR row 0 of the frames with sy = +1 reads it)
     u64 C0lo = 0, C0hi = 0;
-    const bool top_step = GEN && (P == 1) && c.top && (aj == 0);
+    const bool top_step = GEN && (P == 1) && (T == 2) && c.top && (aj == 0);   // a0 = -2 in a top segment: always step 2
     if (top_step) {
         C0lo = mul2(k.A[0], WIN(1).lo); C0hi = mul2(k.A[0], WIN(1).hi);
         C0lo = fma2(k.A[1], WIN(2).lo, C0lo); C0hi = fma2(k.A[1], WIN(2).hi, C0hi);
@@ -266,8 +273,10 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
         w2 = own ? (last ? k.wL2 : k.wI2) : 0.0f;
     }
     const float r1 = fmaf(-m1, B1, s1.x), r2 = fmaf(-m2, B2, s1.y);
-    s.e2 = fmaf(r1 * w1, r1, s.e2);
-    s.e2 = fmaf(r2 * w2, r2, s.e2);
+    if (OWN) {
+        s.e2 = fmaf(r1 * w1, r1, s.e2);
+        s.e2 = fmaf(r2 * w2, r2, s.e2);
+    }
 
     // ---- transposed row pass ------------------------------------------------------------------------------------
     float Wx, Wy, Wz, Ww;
@@ -282,7 +291,7 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
         const float Bc0 = fmaf(k.b[0], Cw, fmaf(k.b[1], Cz, fmaf(k.b[2], Cy, k.b[3] * Cx)));
         const float rl = fmaf(-ml, Bc0, lS);
         const float wl = GEN ? (own ? (last ? k.wlL : k.wlI) : 0.0f) : k.wlI;
-        s.e2 = fmaf(rl * wl, rl, s.e2);
+        if (OWN) s.e2 = fmaf(rl * wl, rl, s.e2);
     }
     s.wr[T].lo = pk(Wx, Wy); s.wr[T].hi = pk(Wz, Ww);
 
@@ -316,31 +325,34 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
         s.w0.lo = pk(Vx, Vy); s.w0.hi = pk(Vz, Vw);
     }
 
-    // ---- transposed column pass: HR rows y1 = ys - 3 (sites ys-6, ys-4, ys-2, ys) and y2 = ys - 2 ----------------
-    const Row& wa = s.wr[(T + 1) & 3]; const Row& wb = s.wr[(T + 2) & 3]; const Row& wc = s.wr[(T + 3) & 3]; const Row& wd = s.wr[T];
-    u64 o1lo = add2(fma2(k.A[2], wb.lo, mul2(k.A[0], wa.lo)), fma2(k.A[6], wd.lo, mul2(k.A[4], wc.lo)));
-    u64 o1hi = add2(fma2(k.A[2], wb.hi, mul2(k.A[0], wa.hi)), fma2(k.A[6], wd.hi, mul2(k.A[4], wc.hi)));
-    u64 o2lo = fma2(k.A[5], wd.lo, fma2(k.A[3], wc.lo, mul2(k.A[1], wb.lo)));
-    u64 o2hi = fma2(k.A[5], wd.hi, fma2(k.A[3], wc.hi, mul2(k.A[1], wb.hi)));
-    const int y1 = 2 * aj + P - 3;
-    if (GEN && c.top) {                                 // HR rows 0..3 also see the duplicate site row ys = 0
-        if (y1 >= 0 && y1 < 4) { const float g = a.acol[3 - y1]; const u64 g2 = pk(g, g); o1lo = fma2(g2, s.w0.lo, o1lo); o1hi = fma2(g2, s.w0.hi, o1hi); }
-        if (y1 + 1 >= 0 && y1 + 1 < 4) { const float g = a.acol[2 - y1]; const u64 g2 = pk(g, g); o2lo = fma2(g2, s.w0.lo, o2lo); o2hi = fma2(g2, s.w0.hi, o2hi); }
+    if (ST) {
+        // ---- transposed column pass: HR rows y1 = ys - 3 (sites ys-6, ys-4, ys-2, ys) and y2 = ys - 2 ----------------
+        const Row& wa = s.wr[(T + 1) & 3]; const Row& wb = s.wr[(T + 2) & 3]; const Row& wc = s.wr[(T + 3) & 3]; const Row& wd = s.wr[T];
+        u64 o1lo = add2(fma2(k.A[2], wb.lo, mul2(k.A[0], wa.lo)), fma2(k.A[6], wd.lo, mul2(k.A[4], wc.lo)));
+        u64 o1hi = add2(fma2(k.A[2], wb.hi, mul2(k.A[0], wa.hi)), fma2(k.A[6], wd.hi, mul2(k.A[4], wc.hi)));
+        u64 o2lo = fma2(k.A[5], wd.lo, fma2(k.A[3], wc.lo, mul2(k.A[1], wb.lo)));
+        u64 o2hi = fma2(k.A[5], wd.hi, fma2(k.A[3], wc.hi, mul2(k.A[1], wb.hi)));
+        const int y1 = 2 * aj + P - 3;
+        if (GEN && c.top) {                                 // HR rows 0..3 also see the duplicate site row ys = 0
+            if (y1 >= 0 && y1 < 4) { const float g = a.acol[3 - y1]; const u64 g2 = pk(g, g); o1lo = fma2(g2, s.w0.lo, o1lo); o1hi = fma2(g2, s.w0.hi, o1hi); }
+            if (y1 + 1 >= 0 && y1 + 1 < 4) { const float g = a.acol[2 - y1]; const u64 g2 = pk(g, g); o2lo = fma2(g2, s.w0.lo, o2lo); o2hi = fma2(g2, s.w0.hi, o2hi); }
+        }
+        // ---- update, clip, store ----------------------------------------------------------------------------------------
+        float4 q1, q2;
+        upk(fma2(k.alpha2, o1lo, h1.lo), q1.x, q1.y); upk(fma2(k.alpha2, o1hi, h1.hi), q1.z, q1.w);
+        upk(fma2(k.alpha2, o2lo, h2.lo), q2.x, q2.y); upk(fma2(k.alpha2, o2hi, h2.hi), q2.z, q2.w);
+        q1.x = clipf(q1.x, k.lo, k.hi); q1.y = clipf(q1.y, k.lo, k.hi); q1.z = clipf(q1.z, k.lo, k.hi); q1.w = clipf(q1.w, k.lo, k.hi);
+        q2.x = clipf(q2.x, k.lo, k.hi); q2.y = clipf(q2.y, k.lo, k.hi); q2.z = clipf(q2.z, k.lo, k.hi); q2.w = clipf(q2.w, k.lo, k.hi);
+        bool st1 = k.st_ok, st2 = k.st_ok;
+        if (GEN) { st1 = st1 && (y1 >= c.ya) && (y1 < c.yb); st2 = st2 && (y1 + 1 >= c.ya) && (y1 + 1 < c.yb); }
+        if (st1) *reinterpret_cast<float4*>(outp) = q1;
+        if (st2) *reinterpret_cast<float4*>(outp + a.W) = q2;
     }
-    // ---- update, clip, store ----------------------------------------------------------------------------------------
-    float4 q1, q2;
-    upk(fma2(k.alpha2, o1lo, h1.lo), q1.x, q1.y); upk(fma2(k.alpha2, o1hi, h1.hi), q1.z, q1.w);
-    upk(fma2(k.alpha2, o2lo, h2.lo), q2.x, q2.y); upk(fma2(k.alpha2, o2hi, h2.hi), q2.z, q2.w);
-    q1.x = clipf(q1.x, k.lo, k.hi); q1.y = clipf(q1.y, k.lo, k.hi); q1.z = clipf(q1.z, k.lo, k.hi); q1.w = clipf(q1.w, k.lo, k.hi);
-    q2.x = clipf(q2.x, k.lo, k.hi); q2.y = clipf(q2.y, k.lo, k.hi); q2.z = clipf(q2.z, k.lo, k.hi); q2.w = clipf(q2.w, k.lo, k.hi);
-    bool st1 = k.st_ok, st2 = k.st_ok;
-    if (GEN) { st1 = st1 && (y1 >= c.ya) && (y1 < c.yb); st2 = st2 && (y1 + 1 >= c.ya) && (y1 + 1 < c.yb); }
-    if (st1) *reinterpret_cast<float4*>(outp) = q1;
-    if (st2) *reinterpret_cast<float4*>(outp + a.W) = q2;
     outp += 2 * a.W;
 }
 
-template <int P, int Q, bool GEN, bool LEFT>
+// Four steps; M0..M3 are the steps' MODEs (see stream_step)
+template <int P, int Q, int M0, int M1, int M2, int M3, bool LEFT>
 __device__ __forceinline__ void stream_iteration(State& s, const LaneConst& k, const WarpCtx& c, const StreamArgs& a,
                                                  const int it, const float* __restrict__ ring, uint64_t* bars,
                                                  float*& outp, float& curC, float& curL, const int lane) {
@@ -356,11 +368,11 @@ __device__ __forceinline__ void stream_iteration(State& s, const LaneConst& k, c
     }
     const unsigned FULL = 0xffffffffu;
     #define EDGE(t) (LEFT ? __shfl_sync(FULL, curC, t) : 0.0f), (LEFT ? __shfl_sync(FULL, curL, t) : 0.0f)
-    stream_step<0, P, Q, GEN, LEFT>(s, k, c, a, aj + 0, s1s + 0 * 64, hrs + 2 * SS_COLS, outp, EDGE(0), lane);
-    stream_step<1, P, Q, GEN, LEFT>(s, k, c, a, aj + 1, s1s + 1 * 64, hrs + 4 * SS_COLS, outp, EDGE(1), lane);
-    stream_step<2, P, Q, GEN, LEFT>(s, k, c, a, aj + 2, s1s + 2 * 64, hrs + 6 * SS_COLS, outp, EDGE(2), lane);
+    stream_step<0, P, Q, M0, LEFT>(s, k, c, a, aj + 0, s1s + 0 * 64, hrs + 2 * SS_COLS, outp, EDGE(0), lane);
+    stream_step<1, P, Q, M1, LEFT>(s, k, c, a, aj + 1, s1s + 1 * 64, hrs + 4 * SS_COLS, outp, EDGE(1), lane);
+    stream_step<2, P, Q, M2, LEFT>(s, k, c, a, aj + 2, s1s + 2 * 64, hrs + 6 * SS_COLS, outp, EDGE(2), lane);
     mbar_wait(&bars[nslot], (uint32_t)(((it + 2) / SS_STAGES) & 1));          // the next stage: its first two rows are prefetched now
-    stream_step<3, P, Q, GEN, LEFT>(s, k, c, a, aj + 3, s1s + 3 * 64, nxt, outp, EDGE(3), lane);
+    stream_step<3, P, Q, M3, LEFT>(s, k, c, a, aj + 3, s1s + 3 * 64, nxt, outp, EDGE(3), lane);
     #undef EDGE
     curC = nC; curL = nL;
 }
@@ -457,14 +469,41 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     if (lane == 0 && SS_STAGES <= nit + 1) stream_issue(a, ring, bars, SS_STAGES, xs0, sb, c.a0);
 
     for (int it = 0; it < nit; ++it) {
-        const int ysf = 2 * (c.a0 + 4 * it) + P, ysl = ysf + 6;             // first / last site row of the iteration
-        const bool fast = (ysf - 3 >= c.ya) && (ysl < c.yb) && (c.a0 + 4 * it + 3 < c.h - 1) && !(c.top && ysf - 3 < 4);
+        // classify the four steps: interior site row? owned (MSE)? both HR rows stored, or none?
+        int kind = 0;                                    // 0 all fast, 1 first (warm-up), 2 last, 3 general
+        {
+            int nf = 0, pat = 0;
+            #pragma unroll
+            for (int t = 0; t < 4; ++t) {
+                const int aj = c.a0 + 4 * it + t, ys = 2 * aj + P, y1 = ys - 3;
+                const bool interior = (aj >= 0) && (aj < c.h - 1);
+                const bool own = (ys >= c.ya) && (ys < c.yb);
+                const bool both = (y1 >= c.ya) && (y1 + 1 < c.yb) && !(c.top && y1 < 4);
+                const bool none = (y1 + 1 < c.ya);
+                int m = -1;
+                if (interior && both) m = own ? (M_OWN | M_ST) : M_ST;
+                else if (interior && none) m = own ? M_OWN : 0;
+                if (m < 0) nf = 1;
+                pat |= (m & 3) << (2 * t);
+            }
+            const int FAST = M_OWN | M_ST;
+            if (nf) kind = 3;
+            else if (pat == (FAST | FAST << 2 | FAST << 4 | FAST << 6)) kind = 0;
+            else if (pat == (0 | 0 << 2 | M_OWN << 4 | FAST << 6)) kind = 1;
+            else if (pat == (FAST | FAST << 2 | FAST << 4 | M_ST << 6)) kind = 2;
+            else kind = 3;
+        }
+        constexpr int F = M_OWN | M_ST;
         if (left) {
-            if (fast) stream_iteration<P, Q, false, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else      stream_iteration<P, Q, true,  true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            if (kind == 0)      stream_iteration<P, Q, F, F, F, F, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 1) stream_iteration<P, Q, 0, 0, M_OWN, F, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 2) stream_iteration<P, Q, F, F, F, M_ST, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else                stream_iteration<P, Q, M_GEN, M_GEN, M_GEN, M_GEN, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
         } else {
-            if (fast) stream_iteration<P, Q, false, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else      stream_iteration<P, Q, true,  false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            if (kind == 0)      stream_iteration<P, Q, F, F, F, F, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 1) stream_iteration<P, Q, 0, 0, M_OWN, F, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 2) stream_iteration<P, Q, F, F, F, M_ST, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else                stream_iteration<P, Q, M_GEN, M_GEN, M_GEN, M_GEN, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
         }
         // stage it+1 is consumed: refill its slot with stage it+4
         __syncwarp();
