@@ -5,6 +5,7 @@ all arithmetic runs in hand-written sm_100a CUDA kernels behind the C ABI declar
 include/sr459.h (libsr459.so, bound with ctypes).  Import as ``import sr459``.
 """
 from . import _lib
+from . import bands
 from ._lib import Sr459Error
 from .ops import (CLIP_HI, CLIP_LO, IBP_ITERATIONS, IBP_STEP_SIZE, PSF_HALFWIDTH, PSF_SIGMA, PSF_SIZE,
                   UPSAMPLE_FACTOR, Plan, back_project, blur, clear_plan_cache, extract_red, forward_model,

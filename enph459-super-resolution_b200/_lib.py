@@ -65,12 +65,9 @@ _SIGNATURES = {
     "sr459_saa_ibp": (_I, [_P, _PP, _P, _P, _I, _PD, _P]),
     "sr459_band_plan_create": (_I, [_PP, _I, _I, _I, _I, _I, _PD, _PD, _I, _I, _D, _D, _D, _I, _I]),
     "sr459_band_layout": (_I, [_P, _PI]),
+    "sr459_band_begin": (_I, [_P, _PP, _I, _P]),
     "sr459_band_iterate": (_I, [_P, _PP, _P, _P, _I, _P]),
     "sr459_band_errors": (_I, [_P, _I, _PD, _P]),
-    "sr459_band_exchange": (_I, [_P, _P, _P, _I, _I, _P]),
-    "sr459_nccl_unique_id": (_I, [_P]),
-    "sr459_nccl_comm_init": (_I, [_PP, _P, _I, _I]),
-    "sr459_nccl_comm_destroy": (_I, [_P]),
 }
 
 

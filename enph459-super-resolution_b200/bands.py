@@ -1,0 +1,206 @@
+"""Row-band IBP of ONE large HR image across the GPUs of a node (BASELINE config 4).
+
+The reference has no multi-device path: `ibp()` (mono_cal_target/run_sr.py:190-209) walks one
+image on one CPU thread.  Here rank g owns the HR rows [2a_g, 2a_{g+1}) (LR rows [a_g, a_{g+1}) =
+an even split of h) and keeps `halo = 2*reach + 2` further hr rows on each side.  One iteration
+= the fused kernel over the owned rows (sr459_band_iterate) followed by ONE neighbour exchange
+of the freshly written boundary rows (torch.distributed send/recv: NCCL over NVLink on the GPU
+box, gloo in the CPU tests); the per-iteration squared-error sums are all-reduced once per call.
+Image borders keep the reference's boundary rules on the first / last band only.
+
+`BandLayout`, `exchange_halos` and `band_loop` are device-agnostic host logic (the world_size-2
+gloo tests run them on CPU tensors); `BandPlan` binds the CUDA side through the C ABI.
+"""
+from __future__ import annotations
+
+import ctypes as C
+from typing import Callable, List, Optional, Sequence
+
+import numpy as np
+
+from . import _lib
+
+
+class BandLayout:
+    """Row ranges of one rank; the same arithmetic as sr459_band_plan_create (checked in the tests)."""
+
+    def __init__(self, h: int, w: int, reach: int, rank: int, world: int, factor: int = 2):
+        if factor != 2:
+            raise ValueError("row bands are implemented for factor 2")
+        if not (0 <= rank < world):
+            raise ValueError(f"bad rank {rank} of {world}")
+        if h < world:
+            raise ValueError(f"{h} LR rows cannot be split into {world} bands")
+        self.h, self.w, self.H, self.W = h, w, 2 * h, 2 * w
+        self.rank, self.world, self.reach = rank, world, reach
+        self.halo = 2 * reach + 2
+        self.own_i0 = (rank * h) // world
+        self.own_i1 = ((rank + 1) * h) // world
+        self.own_y0, self.own_y1 = 2 * self.own_i0, 2 * self.own_i1
+        self.hr_lo = max(0, self.own_y0 - self.halo)
+        self.hr_hi = min(self.H, self.own_y1 + self.halo)
+        self.lr_lo = max(0, (self.own_y0 - self.halo) // 2)
+        self.lr_hi = min(h, (self.own_y1 + self.halo) // 2 + 1)
+        if world > 1 and min(((r + 1) * h) // world - (r * h) // world for r in range(world)) * 2 < self.halo:
+            raise ValueError(f"bands of {2 * (h // world)} HR rows are thinner than the {self.halo}-row halo; use fewer ranks")
+
+    def as_tuple(self):
+        return (self.own_y0, self.own_y1, self.hr_lo, self.hr_hi, self.lr_lo, self.lr_hi, self.halo, self.world)
+
+    # local row slices of the band's hr buffer (rows hr_lo .. hr_hi)
+    @property
+    def owned(self) -> slice:
+        return slice(self.own_y0 - self.hr_lo, self.own_y1 - self.hr_lo)
+
+    def split_hr(self, hr_full):
+        return hr_full[self.hr_lo:self.hr_hi]
+
+    def split_frames(self, lr_full: Sequence):
+        return [f[self.lr_lo:self.lr_hi] for f in lr_full]
+
+
+def exchange_halos(hr_local, lay: BandLayout, group=None) -> None:
+    """Refresh the halo rows of hr_local from the neighbours' owned boundary rows (in place).
+    Works on CPU tensors (gloo) and CUDA tensors (NCCL send/recv over NVLink, stream-ordered)."""
+    import torch.distributed as dist
+    if lay.world == 1:
+        return
+    R, o0, o1 = lay.halo, lay.own_y0 - lay.hr_lo, lay.own_y1 - lay.hr_lo
+    ops = []
+    if lay.rank > 0:                                   # upper neighbour: my first R owned rows <-> my upper halo
+        ops.append(dist.P2POp(dist.isend, hr_local[o0:o0 + R], lay.rank - 1, group))
+        ops.append(dist.P2POp(dist.irecv, hr_local[o0 - R:o0], lay.rank - 1, group))
+    if lay.rank < lay.world - 1:                       # lower neighbour
+        ops.append(dist.P2POp(dist.isend, hr_local[o1 - R:o1], lay.rank + 1, group))
+        ops.append(dist.P2POp(dist.irecv, hr_local[o1:o1 + R], lay.rank + 1, group))
+    for req in dist.batch_isend_irecv(ops):
+        req.wait()
+
+
+def band_loop(lay: BandLayout, hr_local, scratch, n_iter: int, iterate: Callable, exchange: Callable = exchange_halos,
+              group=None):
+    """The K-iteration loop of ibp() (run_sr.py:197-208) on one band: iterate(cur, nxt, it) updates
+    nxt's owned rows from cur; the exchange refreshes nxt's halo rows; buffers swap.  Returns the
+    buffer that holds the result (hr_local or scratch)."""
+    cur, nxt = hr_local, scratch
+    for it in range(n_iter):
+        iterate(cur, nxt, it)
+        exchange(nxt, lay, group)
+        cur, nxt = nxt, cur
+    return cur
+
+
+def reduce_errors(local_sums, n_frames: int, lay: BandLayout, group=None, device=None) -> List[float]:
+    """errors[it] = (1/n) sum_k mean(err_k^2) (run_sr.py:202,206) from the per-rank squared-error sums."""
+    import torch
+    import torch.distributed as dist
+    t = torch.as_tensor(np.asarray(local_sums, dtype=np.float64), device=device)
+    if lay.world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.SUM, group=group)
+    return (t / float(n_frames * lay.h * lay.w)).tolist()
+
+
+class BandPlan:
+    """CUDA side of one rank's band (sr459_band_* in include/sr459.h)."""
+
+    def __init__(self, n_frames, h, w, shifts_yx, kernel, rank, world, factor=2, step=0.5, clip_lo=0.0, clip_hi=255.0,
+                 device=None):
+        from . import ops
+        torch = ops._torch()
+        self._lib = _lib.load()
+        self.device = torch.cuda.current_device() if device is None else int(device)
+        self.n, self.h, self.w = int(n_frames), int(h), int(w)
+        sh = np.ascontiguousarray(np.asarray(shifts_yx, dtype=np.float64).reshape(-1))
+        if sh.size != 2 * self.n:
+            raise ValueError(f"need {self.n} (dy, dx) shifts, got {sh.size // 2}")
+        k, kp, kh, kw = ops._psf_arg(kernel)
+        handle = C.c_void_p()
+        _lib.check(self._lib.sr459_band_plan_create(C.byref(handle), self.device, self.n, self.h, self.w, int(factor),
+                                                    sh.ctypes.data_as(C.POINTER(C.c_double)), kp, kh, kw,
+                                                    float(step), float(clip_lo), float(clip_hi), int(rank), int(world)))
+        self._h = handle
+        out = (C.c_int * 8)()
+        _lib.check(self._lib.sr459_band_layout(self._h, out))
+        self.layout = BandLayout(self.h, self.w, (int(out[6]) - 2) // 2, int(rank), int(world), int(factor))
+        if tuple(out) != self.layout.as_tuple():
+            raise RuntimeError(f"band layout mismatch: library {tuple(out)} vs host {self.layout.as_tuple()}")
+
+    def close(self):
+        if getattr(self, "_h", None):
+            self._lib.sr459_plan_destroy(self._h)
+            self._h = None
+
+    __del__ = close
+
+    def set_path(self, path: int):
+        _lib.check(self._lib.sr459_plan_set_path(self._h, int(path)))
+        return self
+
+    def run(self, lr_local: Sequence, hr_local, n_iter: int, group=None, exchange: Optional[Callable] = exchange_halos):
+        """IBP on this rank's band.  lr_local: the n frames' rows [lr_lo, lr_hi); hr_local: float32 CUDA
+        tensor with HR rows [hr_lo, hr_hi) (halos filled).  Returns (hr_local_result, errors)."""
+        from . import ops
+        torch = ops._torch()
+        lay = self.layout
+        ts = [ops._dev(f) for f in lr_local]
+        for t in ts:
+            if tuple(t.shape) != (lay.lr_hi - lay.lr_lo, self.w):
+                raise ValueError(f"local frame shape {tuple(t.shape)} != {(lay.lr_hi - lay.lr_lo, self.w)}")
+        if tuple(hr_local.shape) != (lay.hr_hi - lay.hr_lo, lay.W) or not hr_local.is_contiguous():
+            raise ValueError(f"local hr shape {tuple(hr_local.shape)} != {(lay.hr_hi - lay.hr_lo, lay.W)} (contiguous)")
+        arr = (C.c_void_p * self.n)(*[t.data_ptr() for t in ts])
+        _lib.check(self._lib.sr459_band_begin(self._h, arr, int(n_iter), ops._stream_ptr()))
+        scratch = hr_local.clone()
+
+        def iterate(cur, nxt, it):
+            _lib.check(self._lib.sr459_band_iterate(self._h, arr, ops._ptr(cur), ops._ptr(nxt), int(it), ops._stream_ptr()))
+
+        res = band_loop(lay, hr_local, scratch, int(n_iter), iterate, exchange or (lambda *a: None), group)
+        sums = np.zeros(max(int(n_iter), 0), dtype=np.float64)
+        if n_iter > 0:
+            _lib.check(self._lib.sr459_band_errors(self._h, int(n_iter), sums.ctypes.data_as(C.POINTER(C.c_double)),
+                                                   ops._stream_ptr()))
+        errors = reduce_errors(sums, self.n, lay, group, device=hr_local.device)
+        return res, errors
+
+
+def run_emulated(plans: Sequence[BandPlan], lr_full: Sequence, hr_full, n_iter: int):
+    """All ranks of a band decomposition inside ONE process on one GPU (tests; a single-GPU check of
+    the multi-GPU path): the bands iterate in lock step and the halo exchange is a row copy."""
+    from . import ops
+    torch = ops._torch()
+    world = len(plans)
+    lays = [p.layout for p in plans]
+    hr_full = ops._dev(hr_full)
+    frames = [ops._dev(f) for f in lr_full]
+    cur = [lay.split_hr(hr_full).clone() for lay in lays]
+    nxt = [c.clone() for c in cur]
+    arrs, keep = [], []
+    for p, lay in zip(plans, lays):
+        ts = [f[lay.lr_lo:lay.lr_hi].contiguous() for f in frames]
+        keep.append(ts)
+        arr = (C.c_void_p * p.n)(*[t.data_ptr() for t in ts])
+        arrs.append(arr)
+        _lib.check(p._lib.sr459_band_begin(p._h, arr, int(n_iter), ops._stream_ptr()))
+    for it in range(n_iter):
+        for g, p in enumerate(plans):
+            _lib.check(p._lib.sr459_band_iterate(p._h, arrs[g], ops._ptr(cur[g]), ops._ptr(nxt[g]), it, ops._stream_ptr()))
+        for g, lay in enumerate(lays):                  # what exchange_halos does, as copies
+            R, o0, o1 = lay.halo, lay.own_y0 - lay.hr_lo, lay.own_y1 - lay.hr_lo
+            if g > 0:
+                up = lays[g - 1]
+                nxt[g][o0 - R:o0].copy_(nxt[g - 1][up.own_y1 - up.hr_lo - R:up.own_y1 - up.hr_lo])
+            if g < world - 1:
+                dn = lays[g + 1]
+                nxt[g][o1:o1 + R].copy_(nxt[g + 1][dn.own_y0 - dn.hr_lo:dn.own_y0 - dn.hr_lo + R])
+        cur, nxt = nxt, cur
+    out = torch.empty_like(hr_full)
+    total = np.zeros(max(n_iter, 0), dtype=np.float64)
+    for g, (p, lay) in enumerate(zip(plans, lays)):
+        out[lay.own_y0:lay.own_y1] = cur[g][lay.owned]
+        if n_iter > 0:
+            sums = np.zeros(n_iter, dtype=np.float64)
+            _lib.check(p._lib.sr459_band_errors(p._h, int(n_iter), sums.ctypes.data_as(C.POINTER(C.c_double)), ops._stream_ptr()))
+            total += sums
+    errors = (total / float(plans[0].n * lays[0].h * lays[0].w)).tolist()
+    return out, errors

@@ -83,6 +83,8 @@ struct sr459_plan {
     bool band = false;
     int own_i0 = 0, own_i1 = 0;       // owned LR rows
     int hr_lo = 0, hr_hi = 0, lr_lo = 0, lr_hi = 0, halo = 0;
+    int rank = 0, nranks = 1;
+    bool band_recipe_valid = false, band_uses_vsum = false; int band_iters = 0;
 
     // tables
     AxisTap *d_zoom_y = nullptr, *d_zoom_x = nullptr;
@@ -892,6 +894,87 @@ int sr459_saa_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, flo
     if (d_saa)
         SR_CUDA(cudaMemcpyAsync(d_saa, d_hr, sizeof(float) * (size_t)plan->H * plan->W, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return sr459_ibp(plan, h_d_lr, d_hr, n_iter, h_errors, stream);
+}
+
+// ---- row bands (one HR image split across GPUs; halo rows are exchanged by the host layer) -------------
+int sr459_band_plan_create(sr459_plan** out, int device, int n_frames, int h, int w, int factor, const double* h_shifts_yx,
+                           const double* h_psf, int kh, int kw, double step, double clip_lo, double clip_hi,
+                           int rank, int nranks) {
+    if (!out) { set_error("band_plan_create: null output"); return SR459_EINVAL; }
+    *out = nullptr;
+    if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("band_plan_create: bad rank %d of %d", rank, nranks); return SR459_EINVAL; }
+    if (h < nranks) { set_error("band_plan_create: %d LR rows cannot be split into %d bands", h, nranks); return SR459_EINVAL; }
+    sr459_plan* p = new (std::nothrow) sr459_plan();
+    if (!p) { set_error("out of host memory"); return SR459_ENOMEM; }
+    int rc = plan_common_init(p, device, n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw, step, clip_lo, clip_hi);
+    if (rc != SR459_OK) { plan_free(p); return rc; }
+    if (!fused_supported(p)) {
+        plan_free(p);
+        set_error("band plans need integer HR shifts (|shift| <= %d), factor 2 and a PSF reach <= 16", kMaxIntShift);
+        return SR459_EUNSUPPORTED;
+    }
+    p->band = true;
+    p->rank = rank; p->nranks = nranks;
+    const int reach = std::max(p->taps_f.reach, p->taps_b.reach);
+    p->halo = 2 * reach + 2;                              // hr' depends on hr within 2 r rows; +2 keeps it even with slack
+    p->own_i0 = (int)(((long long)rank * h) / nranks);
+    p->own_i1 = (int)(((long long)(rank + 1) * h) / nranks);
+    const int oy0 = 2 * p->own_i0, oy1 = 2 * p->own_i1;
+    p->hr_lo = std::max(0, oy0 - p->halo); p->hr_hi = std::min(p->H, oy1 + p->halo);
+    p->lr_lo = std::max(0, (oy0 - p->halo) / 2); p->lr_hi = std::min(h, (oy1 + p->halo) / 2 + 1);
+    *out = p;
+    return SR459_OK;
+}
+
+int sr459_band_layout(const sr459_plan* plan, int* h_out8) {
+    if (!plan || !h_out8 || !plan->band) { set_error("band_layout: not a band plan"); return SR459_EINVAL; }
+    h_out8[0] = 2 * plan->own_i0; h_out8[1] = 2 * plan->own_i1;
+    h_out8[2] = plan->hr_lo; h_out8[3] = plan->hr_hi;
+    h_out8[4] = plan->lr_lo; h_out8[5] = plan->lr_hi;
+    h_out8[6] = plan->halo;  h_out8[7] = plan->nranks;
+    return SR459_OK;
+}
+
+int sr459_band_begin(sr459_plan* plan, const float* const* h_d_lr_local, int n_iter, void* stream) {
+    SR_TRY(check_lr(plan, h_d_lr_local));
+    if (!plan->band || n_iter < 0) { set_error("band_begin: not a band plan or n_iter < 0"); return SR459_EINVAL; }
+    SR_CUDA(cudaSetDevice(plan->device));
+    cudaStream_t st = (cudaStream_t)stream;
+    plan->band_recipe_valid = false;
+    if (n_iter == 0) return SR459_OK;
+    FusedRecipe r = fused_recipe(plan, 2 * plan->own_i0, 2 * plan->own_i1);
+    plan->per_iter = r.per_iter;
+    SR_TRY(plan_ensure_errors(plan, n_iter));
+    SR_TRY(plan_ensure_partial(plan, (size_t)n_iter * r.per_iter));
+    plan->band_uses_vsum = false;
+    if (r.use_sep) { SR_TRY(sep_prepare(plan, h_d_lr_local, false, st)); SR_TRY(sep_counters(plan, n_iter, st)); plan->band_uses_vsum = true; }
+    plan->band_recipe_valid = true;
+    plan->band_iters = n_iter;
+    return SR459_OK;
+}
+
+int sr459_band_iterate(sr459_plan* plan, const float* const* h_d_lr_local, const float* d_cur, float* d_nxt, int it, void* stream) {
+    SR_TRY(check_lr(plan, h_d_lr_local));
+    if (!plan->band || !plan->band_recipe_valid || !d_cur || !d_nxt || it < 0 || it >= plan->band_iters) {
+        set_error("band_iterate: call sr459_band_begin first; it must be in [0, n_iter)"); return SR459_EINVAL;
+    }
+    SR_CUDA(cudaSetDevice(plan->device));
+    const int uy0 = 2 * plan->own_i0, uy1 = 2 * plan->own_i1;
+    FusedRecipe r = fused_recipe(plan, uy0, uy1);
+    return iterate_fused(plan, r, h_d_lr_local, d_cur, d_nxt, plan->d_partial + (size_t)it * r.per_iter, uy0, uy1,
+                         (cudaStream_t)stream, it);
+}
+
+int sr459_band_errors(sr459_plan* plan, int n_iter, double* h_sums, void* stream) {
+    if (!plan || !plan->band || !h_sums || n_iter < 0 || n_iter > plan->errors_cap) { set_error("band_errors: bad arguments"); return SR459_EINVAL; }
+    if (n_iter == 0) return SR459_OK;
+    cudaStream_t st = (cudaStream_t)stream;
+    SR_CUDA(cudaSetDevice(plan->device));
+    SR_TRY(launch_reduce_partials(plan->d_partial, plan->per_iter, n_iter, 1.0, plan->band_uses_vsum ? plan->d_vsum : nullptr,
+                                  plan->d_errors, st));
+    SR_CUDA(cudaMemcpyAsync(h_sums, plan->d_errors, sizeof(double) * n_iter, cudaMemcpyDeviceToHost, st));
+    SR_CUDA(cudaStreamSynchronize(st));
+    return SR459_OK;
 }
 
 }  // extern "C"

@@ -144,6 +144,27 @@ int sr459_ibp_errors(sr459_plan* plan, int n_iter, double* h_errors, void* strea
 int sr459_saa_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, float* d_saa,
                   int n_iter, double* h_errors, void* stream);
 
+/* ---- row bands: ONE large HR image split across GPUs (BASELINE config 4) ---- */
+/* The reference has no multi-device path; a band plan runs ibp()'s iteration (run_sr.py:197-205)
+ * on the HR rows [2a, 2b) that rank `rank` of `nranks` owns (LR rows [a, b) = an even split of h),
+ * reading halo = 2*reach+2 further hr rows on each side that the host layer refreshes from the
+ * neighbouring ranks after every iteration (bands.py: NCCL send/recv between the rank processes).
+ * Needs integer HR shifts and factor 2 (SR459_EUNSUPPORTED otherwise).  All band buffers are LOCAL:
+ * hr buffers hold global HR rows [hr_lo, hr_hi), frame buffers global LR rows [lr_lo, lr_hi).        */
+int sr459_band_plan_create(sr459_plan** out, int device, int n_frames, int h, int w, int factor,
+                           const double* h_shifts_yx, const double* h_psf, int kh, int kw,
+                           double step, double clip_lo, double clip_hi, int rank, int nranks);
+/* h_out8 = { own_y0, own_y1, hr_lo, hr_hi, lr_lo, lr_hi, halo_rows, nranks } (global row numbers)   */
+int sr459_band_layout(const sr459_plan* plan, int* h_out8);
+/* once per ibp() call: per-call sums of the local frames, partial-sum storage for n_iter iterations */
+int sr459_band_begin(sr459_plan* plan, const float* const* h_d_lr_local, int n_iter, void* stream);
+/* iteration `it`: d_nxt[owned rows] = update(d_cur); halo rows of d_nxt are NOT written             */
+int sr459_band_iterate(sr459_plan* plan, const float* const* h_d_lr_local, const float* d_cur,
+                       float* d_nxt, int it, void* stream);
+/* h_sums[it] = sum over the frames and the LR rows this rank owns of err^2 (un-normalised; the host
+ * layer all-reduces and divides by n*h*w as run_sr.py:202,206 do).  Synchronises the stream.          */
+int sr459_band_errors(sr459_plan* plan, int n_iter, double* h_sums, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -492,3 +492,40 @@ def test_full_size_fast_equals_dense_and_properties(sr):
         else:
             _close(got[-160:, -224:], hr_c[-160:, -224:], what="ibp bottom-right window")
     plan.close()
+
+
+# ---------------------------------------------------------------- row bands (multi-GPU path, emulated on one GPU)
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("case", ["gauss7", "gauss5", "measured31", "two_lattices"])
+def test_row_bands_emulated_vs_oracle(sr, world, case):
+    """All ranks of a band decomposition in one process: band kernels + halo copies == full-image oracle.
+    The halo exchange itself (torch.distributed) is covered by tests/test_bands_host.py over gloo."""
+    from sr459.bands import BandPlan, run_emulated
+    rng = np.random.default_rng(31)
+    shifts = NOMINAL if case != "two_lattices" else [(0.0, 0.0)] + NOMINAL
+    if case == "measured31":
+        h, w, psf = 144, 80, golden("g_psf")["k31"]
+    else:
+        h, w = 150, 168
+        psf = O.make_gaussian_psf(5, 0.9) if case == "gauss5" else O.make_gaussian_psf()
+    lrs = [rng.uniform(0, 255, (h, w)) for _ in shifts]
+    hr0 = O.shift_and_add_integer(lrs, shifts)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, hr0, n_iter=4)
+    plans = [BandPlan(len(shifts), h, w, shifts, psf, r, world) for r in range(world)]
+    hr, errs = run_emulated(plans, lrs, hr0, 4)
+    for p in plans:
+        p.close()
+    hr = hr.cpu().numpy()
+    _close(hr, hr_o, what=f"bands {case} world {world}")
+    for p in plans:                                            # band seams
+        y = p.layout.own_y0
+        if y:
+            _close(hr[y - 8:y + 8], hr_o[y - 8:y + 8], what=f"seam at row {y}")
+    _errs_close(errs, e_o)
+
+
+def test_band_plan_refuses_fractional_shifts(sr):
+    from sr459.bands import BandPlan
+    with pytest.raises(sr.Sr459Error) as ei:
+        BandPlan(4, 64, 64, CALIBRATED, O.make_gaussian_psf(), 0, 2)
+    assert ei.value.code == -4
