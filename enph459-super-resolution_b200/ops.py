@@ -169,6 +169,16 @@ def load_measured_psf(psf_dir: str, halfwidth: Optional[int] = None) -> np.ndarr
 # --------------------------------------------------------------------------------------
 # ingest helpers
 # --------------------------------------------------------------------------------------
+def u8_to_f32(img):
+    """uint8 frame -> float32 on the device (the numeric half of load_gray, run_sr.py:73-75)."""
+    torch = _torch()
+    lib = _lib.load()
+    t = _dev(img, torch.uint8)
+    out = torch.empty(t.shape, dtype=torch.float32, device=t.device)
+    _lib.check(lib.sr459_u8_to_f32(_ptr(t), t.numel(), _ptr(out), _stream_ptr()))
+    return out
+
+
 def extract_red(img):
     """Red Bayer sites img[0::2, 0::2] -- rgb_cal_target/run_sr.py:73-75."""
     torch = _torch()

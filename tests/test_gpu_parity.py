@@ -529,3 +529,90 @@ def test_band_plan_refuses_fractional_shifts(sr):
     with pytest.raises(sr.Sr459Error) as ei:
         BandPlan(4, 64, 64, CALIBRATED, O.make_gaussian_psf(), 0, 2)
     assert ei.value.code == -4
+
+
+# ---------------------------------------------------------------- run_sr.py-compatible CLI on synthetic session folders
+def _png(path, arr):
+    from PIL import Image
+    Image.fromarray(arr).save(path)
+
+
+def _read_png(path):
+    from PIL import Image
+    return np.array(Image.open(path))
+
+
+def _u8_close(got, want_f64, what):
+    want = O.to_uint8(want_f64)
+    assert got.shape == want.shape and got.dtype == np.uint8, what
+    d = np.abs(got.astype(int) - want.astype(int))
+    assert d.max() <= 1 and (d > 0).mean() < 1e-3, f"{what}: {int((d > 0).sum())} pixels differ, max {d.max()}"
+
+
+@pytest.mark.parametrize("experiment", ["mono_cal_target", "rgb_cal_target", "mono_barcodes", "rgb_barcodes"])
+def test_run_sr_cli_writes_reference_outputs(sr, tmp_path, experiment):
+    """Same directory walk, file names and pixel values as the reference's four run_sr.py scripts
+    (main/process_session/load_session, mono_cal_target/run_sr.py:78-99, :262-366 and siblings)."""
+    import json
+    from sr459 import run_sr
+    rng = np.random.default_rng(41)
+    data, out = tmp_path / "data", tmp_path / "results"
+    sess = data / "session_a"
+    sess.mkdir(parents=True)
+    (data / "not_a_session.txt").write_text("x")
+    red = experiment.startswith("rgb")
+    H0, W0 = (72, 104) if red else (36, 52)
+    n_iter = 6
+    jobs = []                                                 # (out_dir, frames f64, shifts, lr-mean name)
+    if experiment == "mono_cal_target":
+        names = ["center.png", "shift_0.png", "shift_1.png", "shift_2.png", "shift_3.png"]
+        raws = [rng.integers(0, 256, (H0, W0), dtype=np.uint8) for _ in names]
+        for nme, r in zip(names, raws):
+            _png(sess / nme, r)
+        jobs.append((out / "session_a", [r.astype(np.float64) for r in raws], [(0.0, 0.0)] + NOMINAL, "LR_mean.png"))
+    elif experiment == "rgb_cal_target":
+        meta = {"expected_shifts": {lab: {"dy_px": 2 * s[0], "dx_px": 2 * s[1]} for lab, s in zip(run_sr.CORNER_ORDER, CALIBRATED)}}
+        (sess / "metadata.json").write_text(json.dumps(meta))
+        frames = []
+        for c in range(4):
+            reps = [rng.integers(0, 256, (H0, W0), dtype=np.uint8) for _ in range(3)]
+            for r, raw in enumerate(reps):
+                _png(sess / f"corner{c}_rep{r:02d}.png", raw)
+            frames.append(np.stack([O.extract_red(x.astype(np.float64)) for x in reps]).mean(axis=0))
+        jobs.append((out / "session_a", frames, CALIBRATED, "LR_red_mean.png"))
+    else:
+        for r in range(2):
+            raws = [rng.integers(0, 256, (H0, W0), dtype=np.uint8) for _ in range(4)]
+            for c, raw in enumerate(raws):
+                _png(sess / f"corner{c}_rep{r:02d}.png", raw)
+            fr = [O.extract_red(x.astype(np.float64)) if red else x.astype(np.float64) for x in raws]
+            jobs.append((out / "session_a" / f"rep{r}", fr, NOMINAL, "LR_red_mean.png" if red else "LR_mean.png"))
+    argv = ["--experiment", experiment, "--data-dir", str(data), "--output-dir", str(out), "--iterations", str(n_iter)]
+    assert run_sr.main(argv) == 0
+    psf = O.make_gaussian_psf()
+    for out_dir, frames, shifts, lr_name in jobs:
+        assert (out_dir / "done.flag").exists()
+        native_o = O.native_2x(np.mean(frames, axis=0))
+        saa_o = O.shift_and_add(frames, shifts)
+        hr_o, e_o = O.ibp(frames, shifts, psf, saa_o, n_iter=n_iter)
+        _u8_close(_read_png(out_dir / "native_2x.png"), native_o, "native_2x.png")
+        _u8_close(_read_png(out_dir / "SAA.png"), saa_o, "SAA.png")
+        _u8_close(_read_png(out_dir / "SAA_IBP.png"), hr_o, "SAA_IBP.png")
+        _u8_close(_read_png(out_dir / lr_name), np.mean(frames, axis=0), lr_name)
+        _errs_close(json.loads((out_dir / "errors.json").read_text())["mse_per_iteration"], e_o)
+        if experiment == "rgb_cal_target":
+            sj = json.loads((out_dir / "shifts.json").read_text())
+            assert sj["corner_labels"] == run_sr.CORNER_ORDER and np.allclose(sj["shifts_lr_yx"], CALIBRATED)
+    # second run: everything is skipped (done.flag), nothing is rewritten
+    stamp = {p: p.stat().st_mtime_ns for p in out.rglob("SAA_IBP.png")}
+    assert run_sr.main(argv) == 0
+    assert stamp == {p: p.stat().st_mtime_ns for p in out.rglob("SAA_IBP.png")}
+
+
+def test_run_sr_cli_errors(sr, tmp_path):
+    from sr459 import run_sr
+    (tmp_path / "data" / "empty").mkdir(parents=True)
+    with pytest.raises(FileNotFoundError):
+        run_sr.main(["--experiment", "mono_cal_target", "--data-dir", str(tmp_path / "data"), "--output-dir", str(tmp_path / "o")])
+    with pytest.raises(FileNotFoundError):
+        run_sr.main(["--experiment", "mono_barcodes", "--data-dir", str(tmp_path / "data"), "--output-dir", str(tmp_path / "o")])
