@@ -47,6 +47,7 @@ _SIGNATURES = {
     "sr459_u8_to_f32": (_I, [_P, _L, _P, _P]),
     "sr459_extract_red": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "sr459_mean_frames": (_I, [_PP, _I, _L, _P, _P]),
+    "sr459_ingest_groups": (_I, [_PP, _I, _I, _I, _I, _I, _I, _I, _PP, _P, _P, _P]),
     "sr459_f32_to_u8": (_I, [_P, _L, _P, _P]),
     "sr459_blur": (_I, [_P, _I, _I, _PD, _I, _I, _P, _P]),
     "sr459_zoom": (_I, [_P, _I, _I, _I, _P, _P]),

@@ -719,6 +719,14 @@ int sr459_mean_frames(const float* const* h_d_frames, int n_frames, int64_t n_px
     return launch_mean_frames(h_d_frames, n_frames, n_px, d_out, (cudaStream_t)stream);
 }
 
+int sr459_ingest_groups(const uint8_t* const* h_d_imgs, int n_groups, int reps, int H, int W, int step, int row_off, int col_off,
+                        float* const* h_d_frames, float* d_mean_f32, uint8_t* d_mean_u8, void* stream) {
+    if (!h_d_imgs || !h_d_frames) { set_error("ingest_groups: null pointer arrays"); return SR459_EINVAL; }
+    for (int k = 0; k < n_groups * reps && k < 32; ++k) if (!h_d_imgs[k]) { set_error("ingest_groups: image %d is null", k); return SR459_EINVAL; }
+    for (int g = 0; g < n_groups && g < 8; ++g) if (!h_d_frames[g]) { set_error("ingest_groups: frame %d is null", g); return SR459_EINVAL; }
+    return launch_ingest_groups(h_d_imgs, n_groups, reps, H, W, step, row_off, col_off, h_d_frames, d_mean_f32, d_mean_u8, (cudaStream_t)stream);
+}
+
 int sr459_blur(const float* d_img, int H, int W, const double* h_psf, int kh, int kw, float* d_out, void* stream) {
     if (!d_img || !d_out || !h_psf || H < 1 || W < 1 || kh < 1 || kw < 1) { set_error("blur: bad arguments"); return SR459_EINVAL; }
     if (d_img == d_out) { set_error("blur: in-place operation is not supported"); return SR459_EINVAL; }

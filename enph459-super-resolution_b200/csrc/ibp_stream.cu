@@ -408,11 +408,17 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     const int xs0 = c.x0 - 8;
     const int nit = a.nit;
 
+    // programmatic dependent launch: the next iteration's grid may start (and run everything above and the
+    // barrier set-up below) while this one drains; nothing written by the previous grid is touched before the wait
+    asm volatile("griddepcontrol.launch_dependents;\n" ::: "memory");
     if (lane == 0) {
         #pragma unroll
         for (int i = 0; i < SS_STAGES; ++i) mbar_init(&bars[i], 1);
         mbar_fence_init();
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    }
+    asm volatile("griddepcontrol.wait;\n" ::: "memory");
+    if (lane == 0) {
         #pragma unroll
         for (int st = 0; st < SS_STAGES; ++st) stream_issue(a, ring, bars, st, xs0, sb, c.a0);
     }
@@ -559,12 +565,20 @@ int launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st) {
         configured = true;
     }
     const int grid = (warps + SS_WARPS - 1) / SS_WARPS;
+    cudaLaunchConfig_t cfg{};
+    cfg.gridDim = dim3(grid); cfg.blockDim = dim3(SS_THREADS); cfg.dynamicSmemBytes = smem; cfg.stream = st;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    cfg.attrs = attr; cfg.numAttrs = 1;
+    cudaError_t le;
     switch (P * 2 + Q) {
-        case 0: k_ibp_stream<0, 0><<<grid, SS_THREADS, smem, st>>>(a); break;
-        case 1: k_ibp_stream<0, 1><<<grid, SS_THREADS, smem, st>>>(a); break;
-        case 2: k_ibp_stream<1, 0><<<grid, SS_THREADS, smem, st>>>(a); break;
-        default: k_ibp_stream<1, 1><<<grid, SS_THREADS, smem, st>>>(a); break;
+        case 0: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 0>, a); break;
+        case 1: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 1>, a); break;
+        case 2: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 0>, a); break;
+        default: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 1>, a); break;
     }
+    if (le != cudaSuccess) { set_error("launch of k_ibp_stream failed: %s", cudaGetErrorString(le)); return SR459_ECUDA; }
     SR_LAUNCH_CHECK("k_ibp_stream");
     return SR459_OK;
 }

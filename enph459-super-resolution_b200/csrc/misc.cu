@@ -80,6 +80,49 @@ int launch_mean_frames(const float* const* h_frames, int n, int64_t npx, float* 
     return SR459_OK;
 }
 
+// ---- fused frame-set ingest ----------------------------------------------------------------------------
+// load_gray + extract_red + the per-corner repetition mean (rgb_cal_target/run_sr.py:107-108) + np.mean over
+// the frames (run_sr.py:274) in ONE pass over the uint8 files, in float64 and in numpy's order of operations
+// (sequential sums along axis 0, one division each), so LR_mean.png truncates exactly as the reference's does.
+struct IngestPtrs { const uint8_t* img[32]; float* frame[8]; };
+
+__global__ void __launch_bounds__(256) k_ingest_groups(const __grid_constant__ IngestPtrs p, int n_groups, int reps, int W,
+                                                       int step, int ro, int co, int oh, int ow,
+                                                       float* __restrict__ mean_f32, uint8_t* __restrict__ mean_u8) {
+    const int j = blockIdx.x * 32 + (threadIdx.x & 31);
+    const int i = blockIdx.y * 8 + (threadIdx.x >> 5);
+    if (i >= oh || j >= ow) return;
+    const size_t src = (size_t)(step * i + ro) * W + (size_t)(step * j + co), dst = (size_t)i * ow + j;
+    double total = 0.0;
+    for (int g = 0; g < n_groups; ++g) {
+        double s = 0.0;
+        for (int r = 0; r < reps; ++r) s += (double)p.img[g * reps + r][src];
+        const double m = (reps > 1) ? s / (double)reps : s;
+        p.frame[g][dst] = (float)m;
+        total += m;
+    }
+    const double mean = total / (double)n_groups;
+    if (mean_f32) mean_f32[dst] = (float)mean;
+    if (mean_u8) mean_u8[dst] = (uint8_t)(int)fmin(fmax(mean, 0.0), 255.0);
+}
+
+int launch_ingest_groups(const uint8_t* const* h_imgs, int n_groups, int reps, int H, int W, int step, int ro, int co,
+                         float* const* h_frames, float* mean_f32, uint8_t* mean_u8, cudaStream_t st) {
+    if (n_groups < 1 || n_groups > 8 || reps < 1 || n_groups * reps > 32) {
+        set_error("ingest_groups: 1..8 frames of 1..%d repetitions (at most 32 images), got %d x %d", 32, n_groups, reps);
+        return SR459_EINVAL;
+    }
+    if (step < 1 || ro < 0 || co < 0 || ro >= H || co >= W) { set_error("ingest_groups: bad lattice"); return SR459_EINVAL; }
+    const int oh = (H - ro + step - 1) / step, ow = (W - co + step - 1) / step;
+    IngestPtrs p{};
+    for (int k = 0; k < n_groups * reps; ++k) p.img[k] = h_imgs[k];
+    for (int g = 0; g < n_groups; ++g) p.frame[g] = h_frames[g];
+    dim3 grid((ow + 31) / 32, (oh + 7) / 8);
+    k_ingest_groups<<<grid, 256, 0, st>>>(p, n_groups, reps, W, step, ro, co, oh, ow, mean_f32, mean_u8);
+    SR_LAUNCH_CHECK("k_ingest_groups");
+    return SR459_OK;
+}
+
 // ---- argmax: first maximum in row-major order (np.argmax) -------------------------------------
 // key = (value-bits << 32) | (0xffffffff - index): a max over keys picks the largest value and,
 // among equals, the smallest index.  Pixel values are non-negative so float bits order correctly.

@@ -179,6 +179,34 @@ def u8_to_f32(img):
     return out
 
 
+def ingest_groups(groups, red: bool = False):
+    """Frame-set ingest in one kernel: `groups` is a list of n frames, each a list of `reps` uint8
+    images (H x W, numpy or CUDA uint8 tensors).  Returns (frames, mean_lr, mean_u8): the n float32
+    LR frames (Bayer-red sites if `red`, mean over the repetitions), their mean and its uint8 cast --
+    load_gray / extract_red / stack.mean(axis=0) / np.mean(lr_frames, axis=0) of the reference
+    (rgb_cal_target/run_sr.py:73-75, :107-108; mono_cal_target/run_sr.py:274, :308)."""
+    torch = _torch()
+    lib = _lib.load()
+    n, reps = len(groups), len(groups[0])
+    if any(len(g) != reps for g in groups):
+        raise ValueError("every frame needs the same number of repetitions")
+    imgs = [_dev(i, torch.uint8) for g in groups for i in g]
+    H, W = imgs[0].shape
+    for t in imgs:
+        _check2d(t, "image")
+        if tuple(t.shape) != (H, W):
+            raise ValueError("all images of a frame set must have the same shape")
+    step = 2 if red else 1
+    oh, ow = (H + step - 1) // step, (W + step - 1) // step
+    frames = torch.empty((n, oh, ow), dtype=torch.float32, device=imgs[0].device)
+    mean = torch.empty((oh, ow), dtype=torch.float32, device=imgs[0].device)
+    mean_u8 = torch.empty((oh, ow), dtype=torch.uint8, device=imgs[0].device)
+    ip = (C.c_void_p * len(imgs))(*[t.data_ptr() for t in imgs])
+    fp = (C.c_void_p * n)(*[frames[k].data_ptr() for k in range(n)])
+    _lib.check(lib.sr459_ingest_groups(ip, n, reps, H, W, step, 0, 0, fp, _ptr(mean), _ptr(mean_u8), _stream_ptr()))
+    return [frames[k] for k in range(n)], mean, mean_u8
+
+
 def extract_red(img):
     """Red Bayer sites img[0::2, 0::2] -- rgb_cal_target/run_sr.py:73-75."""
     torch = _torch()

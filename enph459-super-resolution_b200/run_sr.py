@@ -52,24 +52,32 @@ def _load_png(path: str):
     return torch.from_numpy(np.ascontiguousarray(img)).cuda()
 
 
-def _load_u8(path: str):
-    t = _load_png(path)
-    return ops.u8_to_f32(t) if t.dtype == ops._torch().uint8 else t
+def _ingest(groups, red: bool):
+    """groups[k] = the repetitions of frame k as device tensors -> (frames, mean_lr, mean_u8 | None)."""
+    torch = ops._torch()
+    if all(t.dtype == torch.uint8 for g in groups for t in g):
+        return ops.ingest_groups(groups, red=red)                      # one fused kernel, float64 means
+    frames = []                                                        # RGB / 16-bit files: stage by stage
+    for g in groups:
+        fs = [t if t.dtype == torch.float32 else ops.u8_to_f32(t) for t in g]
+        fs = [ops.extract_red(f) for f in fs] if red else fs
+        frames.append(ops.mean_frames(fs) if len(fs) > 1 else fs[0])
+    return frames, ops.mean_frames(frames), None
 
 
 def load_session(session_dir: str):
     """mono_cal_target loader (run_sr.py:78-99): centre + four shifted frames, nominal shifts."""
-    frames, shifts = [], []
+    groups, shifts = [], []
     for fname, s in IMAGE_SHIFTS:
         path = os.path.join(session_dir, fname)
         if not os.path.exists(path):
             print(f"  WARNING: {fname} not found, skipping")
             continue
-        frames.append(_load_u8(path))
+        groups.append([_load_png(path)])
         shifts.append(s)
-    if len(frames) < 2:
+    if len(groups) < 2:
         raise FileNotFoundError(f"Need at least 2 images in {session_dir}")
-    return frames, shifts
+    return groups, shifts
 
 
 def load_combo(combo_dir: str):
@@ -87,18 +95,17 @@ def load_combo(combo_dir: str):
             return c["expected_dy_px"] / 2.0, c["expected_dx_px"] / 2.0
         raise KeyError(f"Cannot find shift for {label} in metadata")
 
-    frames, shifts = [], []
+    groups, shifts = [], []
     for idx, label in enumerate(CORNER_ORDER):
         reps = sorted(f for f in os.listdir(combo_dir) if f.startswith(f"corner{idx}_rep") and f.endswith(".png"))
         if not reps:
             raise FileNotFoundError(f"No images for corner{idx} in {combo_dir}")
-        reds = [ops.extract_red(_load_png(os.path.join(combo_dir, r))) for r in reps]
-        frames.append(ops.mean_frames(reds))
+        groups.append([_load_png(os.path.join(combo_dir, r)) for r in reps])
         shifts.append(get_shift(label))
-    return frames, shifts
+    return groups, shifts
 
 
-def load_reps(session_dir: str, red: bool):
+def load_reps(session_dir: str):
     """*_barcodes loader (mono_barcodes/run_sr.py:89-130, rgb_barcodes/run_sr.py:102-145): every
     repetition index is an independent four-frame job."""
     rep_indices = sorted({int(m.group(1)) for f in os.listdir(session_dir)
@@ -107,13 +114,13 @@ def load_reps(session_dir: str, red: bool):
         raise FileNotFoundError(f"No corner*_rep*.png files in {session_dir}")
     all_reps = []
     for ri in rep_indices:
-        frames = []
+        groups = []
         for ci in range(4):
             path = os.path.join(session_dir, f"corner{ci}_rep{ri:02d}.png")
             if not os.path.exists(path):
                 raise FileNotFoundError(f"Missing {path}")
-            frames.append(ops.extract_red(_load_png(path)) if red else _load_u8(path))
-        all_reps.append(frames)
+            groups.append([_load_png(path)])
+        all_reps.append(groups)
     return all_reps, list(CORNER_SHIFTS)
 
 
@@ -122,15 +129,15 @@ def _save_u8(img, path: str):
     Image.fromarray(ops.to_uint8(img).cpu().numpy()).save(path)        # clip + truncating cast on the device (:303)
 
 
-def run_job(frames: Sequence, shifts: Sequence[Tuple[float, float]], psf, n_iter: int, out_dir: str, lr_name: str,
-            extra_json=None) -> dict:
+def run_job(groups: Sequence, red: bool, shifts: Sequence[Tuple[float, float]], psf, n_iter: int, out_dir: str,
+            lr_name: str, extra_json=None) -> dict:
     """process_session's numeric body and outputs (run_sr.py:272-314)."""
     torch = ops._torch()
     os.makedirs(out_dir, exist_ok=True)
+    t0 = time.time()
+    frames, mean_lr, mean_u8 = _ingest(groups, red)
     n, (h, w) = len(frames), frames[0].shape
     plan = ops.get_plan(n, h, w, shifts, psf)
-    t0 = time.time()
-    mean_lr = ops.mean_frames(list(frames))
     native = plan.native_2x(mean_lr)
     saa = plan.saa(list(frames))
     hr = saa.clone()
@@ -139,7 +146,11 @@ def run_job(frames: Sequence, shifts: Sequence[Tuple[float, float]], psf, n_iter
     dt = time.time() - t0
     for name, img in (("native_2x", native), ("SAA", saa), ("SAA_IBP", hr)):
         _save_u8(img, os.path.join(out_dir, f"{name}.png"))
-    _save_u8(mean_lr, os.path.join(out_dir, lr_name))
+    if mean_u8 is not None:
+        from PIL import Image
+        Image.fromarray(mean_u8.cpu().numpy()).save(os.path.join(out_dir, lr_name))
+    else:
+        _save_u8(mean_lr, os.path.join(out_dir, lr_name))
     if extra_json:
         for fname, obj in extra_json.items():
             with open(os.path.join(out_dir, fname), "w") as fp:
@@ -162,20 +173,20 @@ def process_session(experiment: str, session_dir: str, psf, output_base: str, n_
             print(f"  [skip] {name} - already done")
             return 0
         if experiment == "mono_cal_target":
-            frames, shifts = load_session(session_dir)
+            groups, shifts = load_session(session_dir)
             extra = None
         else:
-            frames, shifts = load_combo(session_dir)
+            groups, shifts = load_combo(session_dir)
             extra = {"shifts.json": {"shifts_lr_yx": [list(s) for s in shifts], "corner_labels": CORNER_ORDER}}
-        run_job(frames, shifts, psf, n_iter, out_dir, lr_name, extra)
+        run_job(groups, red, shifts, psf, n_iter, out_dir, lr_name, extra)
         return 1
-    all_reps, shifts = load_reps(session_dir, red)
-    for rep_idx, frames in enumerate(all_reps):
+    all_reps, shifts = load_reps(session_dir)
+    for rep_idx, groups in enumerate(all_reps):
         out_dir = os.path.join(output_base, name, f"rep{rep_idx}")
         if os.path.exists(os.path.join(out_dir, "done.flag")):
             print(f"  [skip] rep {rep_idx} - already done")
             continue
-        run_job(frames, shifts, psf, n_iter, out_dir, lr_name)
+        run_job(groups, red, shifts, psf, n_iter, out_dir, lr_name)
         jobs += 1
     return jobs
 

@@ -78,6 +78,16 @@ int sr459_extract_red(const void* d_in, int is_f32, int H, int W, int row_off, i
 /* np.mean(frames, axis=0) over n_frames device images  run_sr.py:274, rgb_cal_target/run_sr.py:107-108 */
 int sr459_mean_frames(const float* const* h_d_frames, int n_frames, int64_t n_px,
                       float* d_out, void* stream);
+/* One-pass ingest of a frame set from its uint8 files: load_gray (run_sr.py:73-75), optional Bayer
+ * lattice gather in[step*i+row_off, step*j+col_off] (extract_red, rgb_cal_target/run_sr.py:73-75;
+ * step 1 = every pixel), mean over the `reps` repetitions of each of the n_groups frames
+ * (rgb_cal_target/run_sr.py:107-108) and np.mean over the frames (run_sr.py:274), in float64 and in
+ * numpy's order of operations.  h_d_imgs: n_groups*reps device images (H x W uint8), group-major.
+ * h_d_frames: n_groups outputs (float32, ceil((H-row_off)/step) x ceil((W-col_off)/step)).
+ * d_mean_f32 / d_mean_u8 (either may be NULL): the frame mean and its clip+truncate uint8 cast (:308). */
+int sr459_ingest_groups(const uint8_t* const* h_d_imgs, int n_groups, int reps, int H, int W,
+                        int step, int row_off, int col_off, float* const* h_d_frames,
+                        float* d_mean_f32, uint8_t* d_mean_u8, void* stream);
 /* np.clip(img,0,255).astype(np.uint8)  (truncation)    run_sr.py:303          */
 int sr459_f32_to_u8(const float* d_in, int64_t n, uint8_t* d_out, void* stream);
 

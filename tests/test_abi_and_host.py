@@ -123,3 +123,23 @@ def test_shard_indices_cover_every_frame_set_once():
         seen = sorted(i for r in range(world) for i in shard_indices(n_items, r, world))
         assert seen == list(range(n_items))
     assert shard_indices(10, 1, 4) == [1, 5, 9]
+
+
+def test_run_sr_cli_session_discovery(tmp_path):
+    """The directory walks of the four reference main()s (mono_cal_target/run_sr.py:338-343,
+    rgb_cal_target/run_sr.py:352-356, mono_barcodes/run_sr.py:375-378): pure host logic."""
+    from sr459 import run_sr
+    d = tmp_path / "data"
+    for name in ("b_sess", "a_sess", "c_other"):
+        (d / name).mkdir(parents=True)
+    (d / "a_sess" / "center.png").write_bytes(b"")
+    (d / "b_sess" / "metadata.json").write_text("{}")
+    (d / "file.txt").write_text("x")
+    base = lambda ps: [os.path.basename(p) for p in ps]
+    assert base(run_sr.find_sessions("mono_cal_target", str(d))) == ["a_sess"]
+    assert base(run_sr.find_sessions("rgb_cal_target", str(d))) == ["b_sess"]
+    assert base(run_sr.find_sessions("mono_barcodes", str(d))) == ["a_sess", "b_sess", "c_other"]
+    (tmp_path / "empty").mkdir()
+    with pytest.raises(FileNotFoundError):
+        run_sr.find_sessions("rgb_barcodes", str(tmp_path / "empty"))
+    assert run_sr.EXPERIMENTS["rgb_cal_target"][0] == 50 and run_sr.EXPERIMENTS["mono_barcodes"][0] == 80

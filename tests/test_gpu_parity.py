@@ -598,7 +598,7 @@ def test_run_sr_cli_writes_reference_outputs(sr, tmp_path, experiment):
         _u8_close(_read_png(out_dir / "native_2x.png"), native_o, "native_2x.png")
         _u8_close(_read_png(out_dir / "SAA.png"), saa_o, "SAA.png")
         _u8_close(_read_png(out_dir / "SAA_IBP.png"), hr_o, "SAA_IBP.png")
-        _u8_close(_read_png(out_dir / lr_name), np.mean(frames, axis=0), lr_name)
+        assert np.array_equal(_read_png(out_dir / lr_name), O.to_uint8(np.mean(frames, axis=0))), lr_name   # exact: float64 means
         _errs_close(json.loads((out_dir / "errors.json").read_text())["mse_per_iteration"], e_o)
         if experiment == "rgb_cal_target":
             sj = json.loads((out_dir / "shifts.json").read_text())
@@ -607,6 +607,24 @@ def test_run_sr_cli_writes_reference_outputs(sr, tmp_path, experiment):
     stamp = {p: p.stat().st_mtime_ns for p in out.rglob("SAA_IBP.png")}
     assert run_sr.main(argv) == 0
     assert stamp == {p: p.stat().st_mtime_ns for p in out.rglob("SAA_IBP.png")}
+
+
+def test_fused_ingest_matches_numpy_order_of_operations(sr):
+    """sr459_ingest_groups == load_gray + extract_red + stack.mean(axis=0) + np.mean(frames, axis=0) in float64."""
+    rng = np.random.default_rng(43)
+    for (H0, W0, n, reps, red) in [(37, 53, 4, 5, True), (36, 52, 5, 1, False), (8, 8, 1, 3, True), (33, 47, 8, 4, False)]:
+        groups = [[rng.integers(0, 256, (H0, W0), dtype=np.uint8) for _ in range(reps)] for _ in range(n)]
+        frames, mean, mean_u8 = sr.ingest_groups(groups, red=red)
+        ref = [np.stack([(O.extract_red(x.astype(np.float64)) if red else x.astype(np.float64)) for x in g]).mean(axis=0) for g in groups]
+        ref_mean = np.mean(ref, axis=0)
+        for f, r in zip(frames, ref):
+            assert np.array_equal(f.cpu().numpy(), r.astype(np.float32))
+        assert np.array_equal(mean.cpu().numpy(), ref_mean.astype(np.float32))
+        assert np.array_equal(mean_u8.cpu().numpy(), O.to_uint8(ref_mean))
+    with pytest.raises(ValueError):
+        sr.ingest_groups([[np.zeros((4, 4), np.uint8)], [np.zeros((4, 4), np.uint8)] * 2])
+    with pytest.raises(sr.Sr459Error):
+        sr.ingest_groups([[np.zeros((4, 4), np.uint8)] * 5] * 8)
 
 
 def test_run_sr_cli_errors(sr, tmp_path):
