@@ -1,12 +1,17 @@
 #!/bin/bash
-# one GPU-box visit: parity tests, bench, ncu launch list, one full ncu capture of the IBP kernel
+# one GPU-box visit: parity tests, bench (both arms), per-config timings, ncu launch list, one full ncu capture of the IBP kernel
 tag=${1:-r01x}
 mkdir -p gpurun_out
-python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${tag}_pytest.log
+nvidia-smi --query-gpu=name,clocks.sm,clocks.max.sm,power.draw --format=csv > gpurun_out/${tag}_smi.txt 2>&1
+timeout 1500 python -m pytest tests -m gpu -x -q > gpurun_out/${tag}_pytest.log 2>&1; echo "pytest rc=$?" >> gpurun_out/${tag}_pytest.log
 tail -3 gpurun_out/${tag}_pytest.log
-python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
+timeout 600 python bench.py --steps 10 --warmup 3 > gpurun_out/${tag}_bench.json 2> gpurun_out/${tag}_bench.err; echo "bench rc=$?"
 cat gpurun_out/${tag}_bench.json
-ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
+timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/${tag}_bench_ref.json 2> gpurun_out/${tag}_bench_ref.err; echo "bench ref rc=$?"
+cat gpurun_out/${tag}_bench_ref.json
+timeout 300 python tools/time_configs.py > gpurun_out/${tag}_configs.txt 2>&1; echo "configs rc=$?"
+cat gpurun_out/${tag}_configs.txt
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file gpurun_out/${tag}_launches.csv \
     python bench.py --steps 2 --warmup 3 --no-cpu > gpurun_out/${tag}_ncu1.log 2>&1; echo "ncu list rc=$?"
-ncu --set full --clock-control none --import-source on -k regex:k_ibp -s 20 -c 1 -f -o gpurun_out/${tag}_k_ibp \
+timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_ibp -s 20 -c 1 -f -o gpurun_out/${tag}_k_ibp \
     python bench.py --steps 1 --warmup 3 --no-cpu > gpurun_out/${tag}_ncu2.log 2>&1; echo "ncu full rc=$?"
