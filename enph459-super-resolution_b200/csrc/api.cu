@@ -107,6 +107,7 @@ struct sr459_plan {
     float* d_edge = nullptr;          // ibp_stream.cu edge vectors: colS1[h], leftS1[h], rowS1[w], topS1[w], scal[4]
     CUtensorMap tm_s1s;               // box of ibp_stream.cu (single lattice)
     int*  d_counters = nullptr; int counters_cap = 0;   // per-iteration tile counters of the pipelined kernel
+    LatPlan* lat = nullptr;           // ibp_lat.cu: large / non-separable PSFs
     int   n_sm = 0;
 
     // scratch
@@ -142,6 +143,8 @@ static int plan_ensure_errors(sr459_plan* p, int n_iter) {
     p->errors_cap = n_iter;
     return SR459_OK;
 }
+
+static bool fused_supported(const sr459_plan* p);
 
 static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int w, int factor,
                             const double* shifts, const double* psf, int kh, int kw, double step,
@@ -193,6 +196,7 @@ static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int 
             }
         }
     }
+    if (fused_supported(p) && lat_supported(kh, kw, p->smax, p->W)) SR_TRY(lat_create(&p->lat, psf, kh, kw));
     // parity lattices of the integer HR shifts (only meaningful for |shift| <= 1)
     if (p->is_int && p->smax <= 1 && factor == 2) {
         for (int ph = 0; ph < 4; ++ph) {
@@ -227,6 +231,7 @@ static void plan_free(sr459_plan* p) {
     for (void* q : ptrs) if (q) cudaFree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
+    lat_destroy(p->lat);
     delete p;
 }
 
@@ -405,12 +410,21 @@ static int dense_launch(const sr459_plan* p, const IbpGeom& g, const float* cons
     return launch_ibp_dense(a, st);
 }
 
+static void fill_lat_call(const sr459_plan* p, LatCall& c, int uy0, int uy1) {
+    c.H = p->H; c.W = p->W; c.h = p->h; c.w = p->w; c.n = p->n;
+    for (int k = 0; k < p->n; ++k) { c.sy[k] = p->isy[k]; c.sx[k] = p->isx[k]; }
+    c.hr_lo = p->hr_lo; c.hr_hi = p->hr_hi; c.lr_lo = p->lr_lo; c.lr_hi = p->lr_hi;
+    c.own_i0 = p->own_i0; c.own_i1 = p->own_i1; c.upd_y0 = uy0; c.upd_y1 = uy1;
+    c.alpha = (float)(p->step / p->n); c.lo = (float)p->lo; c.hi = (float)p->hi;
+}
+
 // number of partial-sum slots one fused iteration writes, and the launch recipe
 struct FusedRecipe {
     bool use_fast;
     bool use_sep;
     bool use_ws;
     bool use_stream;
+    bool use_lat;
     int st_nit, st_seg, st_nseg, st_nstrip;
     int fast_tx, fast_ty;
     DensePass all;
@@ -422,9 +436,10 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     const int W = p->W;
     int fth, ftw;
     ibp_fast_tile(&fth, &ftw);
-    bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1;
-    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || p->path >= 4);
+    bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1 && p->path != 8;
+    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || (p->path >= 4 && p->path <= 7));
     bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
+    const bool lat_ok = p->lat != nullptr && (p->path == 0 || p->path == 8);
     const bool stream_ok = sep_ok && !p->band && uy0 == 0 && uy1 == p->H && (p->path == 0 || p->path == 7) &&
                            ibp_stream_supported(p->kh, p->kw, p->smax, p->separable, W, p->nslot);
     if (stream_ok && (big || p->path == 7)) {
@@ -440,6 +455,10 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
         r.fast_tx = (W + ftw - 1) / ftw;
         r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
         r.n_fast = r.fast_tx * r.fast_ty;
+    } else if (lat_ok && (p->path == 8 || (p->path == 0 && !fast_ok && big))) {
+        r.use_lat = true;
+        LatCall c{}; fill_lat_call(p, c, uy0, uy1);
+        r.n_fast = lat_per_iter(p->lat, c);
     } else if (fast_ok && p->path < 4 && (big || p->path == 3)) {
         r.use_fast = true;
         r.fast_tx = (W + ftw - 1) / ftw;
@@ -537,6 +556,13 @@ static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const
         }
         f.partial = partial;
         return launch_ibp_stream(f, P, Q, st);
+    }
+    if (r.use_lat) {
+        LatCall c{};
+        fill_lat_call(p, c, uy0, uy1);
+        for (int k = 0; k < p->n; ++k) c.lr[k] = lr[k];
+        c.hr_in = cur; c.hr_out = nxt; c.partial = partial;
+        return lat_iterate(p->lat, c, st);
     }
     if (r.use_sep) {
         SepArgs f{};
@@ -848,8 +874,9 @@ void sr459_plan_destroy(sr459_plan* plan) { plan_free(plan); }
 int sr459_plan_is_integer(const sr459_plan* plan) { return plan && plan->is_int ? 1 : 0; }
 
 int sr459_plan_set_path(sr459_plan* plan, int path) {
-    if (!plan || path < 0 || path > 7) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
-    if (path >= 4 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
+    if (!plan || path < 0 || path > 8) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
+    if (path == 8 && !plan->lat) { set_error("lattice kernel not available for this plan (needs integer |shift| <= 1, factor 2, PSF reach <= 15, W % 4 == 0)"); return SR459_EUNSUPPORTED; }
+    if (path >= 4 && path <= 7 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
         set_error("separable TMA kernel not available for this plan (needs integer |shift| <= 1, a rank-1 PSF up to 7x7, W % 4 == 0)");
         return SR459_EUNSUPPORTED;
     }
@@ -863,7 +890,7 @@ int sr459_plan_set_path(sr459_plan* plan, int path) {
     return SR459_OK;
 }
 
-int64_t sr459_plan_scratch_bytes(const sr459_plan* plan) { return plan ? plan->scratch : 0; }
+int64_t sr459_plan_scratch_bytes(const sr459_plan* plan) { return plan ? plan->scratch + lat_scratch_bytes(plan->lat) : 0; }
 
 int sr459_native2x(sr459_plan* plan, const float* d_mean_lr, float* d_hr, void* stream) {
     if (!plan || !d_mean_lr || !d_hr) { set_error("native2x: bad arguments"); return SR459_EINVAL; }

@@ -259,6 +259,24 @@ void stream_geometry(int H, int W, int n_sm, int* nit, int* seg_rows, int* nseg,
 int  launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const int* sy, const int* sx, int P, int Q,
                              float* buf, double* vsum, cudaStream_t st);
 
+// ---- lattice form for large / non-separable PSFs (ibp_lat.cu): reach <= 15, |integer HR shift| <= 1 ---------
+struct LatPlan;                         // tables + site planes, owned by the plan
+struct LatCall {
+    int H, W, h, w, n;
+    int sy[kMaxFrames], sx[kMaxFrames];
+    int hr_lo, hr_hi, lr_lo, lr_hi, own_i0, own_i1, upd_y0, upd_y1;
+    float alpha, lo, hi;
+    const float* lr[kMaxFrames];
+    const float* hr_in; float* hr_out;
+    double* partial;                    // lat_per_iter() slots
+};
+bool    lat_supported(int kh, int kw, int smax, int W);
+int     lat_create(LatPlan** out, const double* psf, int kh, int kw);
+void    lat_destroy(LatPlan* L);
+int     lat_per_iter(const LatPlan* L, const LatCall& c);
+int     lat_iterate(LatPlan* L, const LatCall& c, cudaStream_t st);
+int64_t lat_scratch_bytes(const LatPlan* L);
+
 // errors[it] = (sum(partials of iteration it) + *d_add) * scale     (d_add may be null)
 int launch_reduce_partials(const double* partial, int per_iter, int n_iter, double scale,
                            const double* d_add, double* d_errors, cudaStream_t st);

@@ -432,6 +432,58 @@ def test_measured_psf_31_integer_and_fractional(sr):
         _errs_close(errs, e_o)
 
 
+LATTICE_SHIFT_SETS = [
+    NOMINAL,
+    [(0.0, 0.0)] + NOMINAL,                                   # two lattices (mono_cal_target)
+    [(0.0, 0.0), (0.5, 0.0), (0.0, 0.5), (0.5, 0.5)],         # all four lattices, no clamp terms
+    [(0.0, 0.0), (-0.5, 0.0), (0.0, -0.5), (-0.5, -0.5)],     # all four lattices, row-0 / column-0 duplicates
+    [(0.5, 0.5)] * 2 + [(-0.5, -0.5)] * 3,                    # MSE-only rows and duplicate rows on one lattice
+    [(-0.5, 0.5), (0.5, 0.0)],
+]
+
+
+def _nonseparable_psf(size, seed):
+    rng = np.random.default_rng(seed)
+    r = size // 2
+    y, x = np.mgrid[-r:r + 1, -r:r + 1].astype(np.float64)
+    k = np.exp(-(x * x / (0.5 * r + 1.0) + y * y / (0.3 * r + 0.7) + 0.2 * x * y / (r + 1.0))) * (1.0 + 0.3 * rng.uniform(size=(size, size)))
+    return k / k.sum()
+
+
+@pytest.mark.parametrize("shifts", LATTICE_SHIFT_SETS)
+@pytest.mark.parametrize("hw,ksize", [((40, 56), 31), ((70, 130), 31), ((33, 48), 19), ((36, 72), 9), ((64, 66), 7), ((2, 2), 31), ((5, 34), 15)])
+def test_lattice_kernel_vs_oracle(sr, shifts, hw, ksize):
+    """Path 8 (ibp_lat.cu): large / non-separable PSFs, integer shifts |2d| <= 1, every lattice mix and border kind."""
+    rng = np.random.default_rng(81)
+    h, w = hw
+    lrs = [rng.uniform(0, 255, (h, w)) for _ in shifts]
+    psf = _nonseparable_psf(ksize, ksize)
+    saa_o = O.shift_and_add_integer(lrs, shifts)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, saa_o, n_iter=4)
+    native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 4, 8)
+    _close(hr, hr_o, what=f"lattice ibp {hw} k{ksize} {shifts}")
+    _close(hr[:16], hr_o[:16], what="top rows"); _close(hr[:, :16], hr_o[:, :16], what="left cols")
+    _close(hr[-16:], hr_o[-16:], what="bottom rows"); _close(hr[:, -16:], hr_o[:, -16:], what="right cols")
+    _errs_close(errs, e_o)
+
+
+def test_lattice_kernel_matches_dense_kernel_and_reference_golden(sr):
+    import torch
+    g = golden("g_psf")
+    rng = np.random.default_rng(82)
+    h, w = 96, 160
+    lrs = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in NOMINAL]
+    plan = sr.Plan(4, h, w, NOMINAL, g["k31"])
+    saa = plan.saa(lrs)
+    a = saa.clone(); ea = plan.set_path(8).ibp_(lrs, a, 6)
+    b = saa.clone(); eb = plan.set_path(2).ibp_(lrs, b, 6)
+    plan.close()
+    assert float((a - b).abs().max()) <= 2e-3
+    _errs_close(ea, eb)
+    with pytest.raises(sr.Sr459Error):
+        sr.Plan(4, 32, 33, NOMINAL, g["k31"]).set_path(8)       # W % 4 != 0: dense path only
+
+
 def test_clip_is_active_and_matches(sr):
     """S1 noise drives hr to both clip bounds (quirk Q5: literals 0 and 255)."""
     rng = np.random.default_rng(14)

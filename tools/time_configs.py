@@ -22,6 +22,14 @@ def measured7():
     return k / k.sum()
 
 
+def measured31():
+    """The non-separable 31x31 stand-in of tools/bench_bands.py (the pinhole PNGs do not travel)."""
+    y, x = np.mgrid[-15:16, -15:16].astype(np.float64)
+    k = np.exp(-(x * x / 18.0 + y * y / 8.0 + 0.05 * x * y)) + 0.15 * np.exp(-((x - 4) ** 2 + (y + 3) ** 2) / 6.0)
+    k[np.abs(k) < 1e-4 * k.max()] = 0.0
+    return k / k.sum()
+
+
 CONFIGS = {
     # name: (h, w, shifts, psf, iters)
     "c1": (1536, 2048, NOMINAL, "gauss", 50),
@@ -30,6 +38,7 @@ CONFIGS = {
     "c2gauss": (768, 1024, CALIBRATED, "gauss", 50),
     "c2int": (768, 1024, NOMINAL, "gauss", 50),
     "monocal": (1536, 2048, [(0.0, 0.0)] + NOMINAL, "gauss", 80),
+    "c4": (1536, 2048, NOMINAL, "meas31", 20),
 }
 
 
@@ -40,7 +49,7 @@ def main():
     rng = np.random.default_rng(459)
     for name in names:
         h, w, shifts, psfname, iters = CONFIGS[name]
-        psf = sr459.make_gaussian_psf() if psfname == "gauss" else measured7()
+        psf = sr459.make_gaussian_psf() if psfname == "gauss" else (measured31() if psfname == "meas31" else measured7())
         n = len(shifts)
         frames = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in range(n)]
         plan = sr459.Plan(n, h, w, shifts, psf)
