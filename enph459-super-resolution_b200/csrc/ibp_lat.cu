@@ -51,9 +51,8 @@ constexpr int LT_COLS = LT_WARPS * LT_NB;   // 64
 // taps (+ one zero).  e[][][tu][m] = (w[2m], w[2m+1]); o[][][tu][m] = (w[2m-1], w[2m]) with w[-1] = w[NT] = 0:
 // the two packings a lane needs for outputs at even / odd offsets from its 8-byte aligned window.
 template <int NT>
-struct LatTab {
-    u64 e[2][2][NT][NT / 2];
-    u64 o[2][2][NT][NT / 2 + 1];
+struct alignas(16) LatTab {
+    u64 w[2][2][NT][NT + 2];            // [0, NT/2): e pairs; [NT/2, NT+1): o pairs; one pad (16-byte rows)
 };
 
 struct LatGeom {
@@ -65,28 +64,64 @@ struct LatGeom {
     int slot_pq[kMaxSlots];             // P*2+Q
 };
 
-// out[b] += sum_t w[t] * x[b + DELTA + t], b = 0..15; x = 32 floats as 16 aligned pairs; acc = (lo, hi) halves
-template <int NT, int DELTA>
-__device__ __forceinline__ void lat_conv_row(const u64 (&xp)[(LT_NB + NT) / 2], const u64* __restrict__ we,
-                                             const u64* __restrict__ wo, u64 (&acc)[LT_NB]) {
-    #pragma unroll
-    for (int b = 0; b < LT_NB; ++b) {
-        if (((b + DELTA) & 1) == 0) {
-            #pragma unroll
-            for (int m = 0; m < NT / 2; ++m) acc[b] = lat_fma2(xp[(b + DELTA) / 2 + m], we[m], acc[b]);
-        } else {
-            #pragma unroll
-            for (int m = 0; m <= NT / 2; ++m) acc[b] = lat_fma2(xp[(b + DELTA - 1) / 2 + m], wo[m], acc[b]);
-        }
-    }
-}
-
 template <int NT>
 __device__ __forceinline__ void lat_load_window(const float* p, u64 (&xp)[(LT_NB + NT) / 2]) {
     const ulonglong2* q = reinterpret_cast<const ulonglong2*>(p);
     #pragma unroll
     for (int i = 0; i < (LT_NB + NT) / 4; ++i) { const ulonglong2 t = q[i]; xp[2 * i] = t.x; xp[2 * i + 1] = t.y; }
 }
+
+// out[b] += sum_t w[t] * x[b + DELTA + t], b = 0..15; x = 32 floats as 16 aligned pairs; acc = (lo, hi) halves.
+// Split by the parity of b + DELTA so that one weight packing is in use while the other one is being fetched.
+template <int NT, int DELTA>
+__device__ __forceinline__ void lat_conv_even(const u64 (&xp)[(LT_NB + NT) / 2], const u64 (&we)[NT / 2], u64 (&acc)[LT_NB]) {
+    #pragma unroll
+    for (int m = 0; m < NT / 2; ++m) {
+        #pragma unroll
+        for (int b = DELTA; b < LT_NB; b += 2) acc[b] = lat_fma2(xp[(b + DELTA) / 2 + m], we[m], acc[b]);
+    }
+}
+template <int NT, int DELTA>
+__device__ __forceinline__ void lat_conv_odd(const u64 (&xp)[(LT_NB + NT) / 2], const u64 (&wo)[NT / 2 + 2], u64 (&acc)[LT_NB]) {
+    #pragma unroll
+    for (int m = 0; m <= NT / 2; ++m) {
+        #pragma unroll
+        for (int b = 1 - DELTA; b < LT_NB; b += 2) acc[b] = lat_fma2(xp[(b + DELTA - 1) / 2 + m], wo[m], acc[b]);
+    }
+}
+template <int NT>
+__device__ __forceinline__ void lat_load_we(const u64* row, u64 (&we)[NT / 2]) {
+    const ulonglong2* q = reinterpret_cast<const ulonglong2*>(row);
+    #pragma unroll
+    for (int i = 0; i < NT / 4; ++i) { const ulonglong2 t = q[i]; we[2 * i] = t.x; we[2 * i + 1] = t.y; }
+}
+template <int NT>
+__device__ __forceinline__ void lat_load_wo(const u64* row, u64 (&wo)[NT / 2 + 2]) {
+    const ulonglong2* q = reinterpret_cast<const ulonglong2*>(row + NT / 2);
+    #pragma unroll
+    for (int i = 0; i < NT / 4 + 1; ++i) { const ulonglong2 t = q[i]; wo[2 * i] = t.x; wo[2 * i + 1] = t.y; }
+}
+
+// one parity phase of a 2-D correlation: acc[b] += sum_{tu < ntu} sum_tv w[tu][tv] * x[row tu][b + DELTA + tv];
+// software-pipelined: next window and next weight packing are fetched under the FFMA2 of the current ones
+template <int NT, int DELTA>
+__device__ __forceinline__ void lat_conv_phase(const float* base, int pitch, const u64 (*wt)[NT + 2], int ntu, u64 (&acc)[LT_NB]) {
+    u64 x[(LT_NB + NT) / 2], xn[(LT_NB + NT) / 2], we[NT / 2], wo[NT / 2 + 2];
+    lat_load_window<NT>(base, x);
+    lat_load_we<NT>(wt[0], we);
+    #pragma unroll 2
+    for (int tu = 0; tu < ntu; ++tu) {
+        const int t1 = min(tu + 1, ntu - 1);
+        lat_load_wo<NT>(wt[tu], wo);
+        lat_load_window<NT>(base + t1 * pitch, xn);
+        lat_conv_even<NT, DELTA>(x, we, acc);
+        lat_load_we<NT>(wt[t1], we);
+        lat_conv_odd<NT, DELTA>(x, wo, acc);
+        #pragma unroll
+        for (int i = 0; i < (LT_NB + NT) / 2; ++i) x[i] = xn[i];
+    }
+}
+
 
 template <int NT> struct LatDims {
     static constexpr int RT = NT - 1;               // padded PSF reach (odd)
@@ -110,10 +145,12 @@ struct alignas(16) LatFwdArgs {
 template <int NT>
 __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_constant__ LatFwdArgs<NT> a) {
     typedef LatDims<NT> D;
-    extern __shared__ __align__(16) float sm[];             // [4 phases][SR][SP]
+    extern __shared__ __align__(16) float sm[];             // [4 phases][SR][SP] + weight table
     const LatGeom& g = a.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int s = blockIdx.z;
+    u64 (*wsm)[2][NT][NT + 2] = reinterpret_cast<u64 (*)[2][NT][NT + 2]>(sm + 4 * D::SR * D::SP);
+    for (int i = tid; i < 4 * NT * (NT + 2); i += LT_WARPS * 32) (&wsm[0][0][0][0])[i] = (&a.tab.w[0][0][0][0])[i];
     const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
     const int A0 = g.sa_lo + blockIdx.y * LT_ROWS, B0 = blockIdx.x * LT_COLS;
     int du0[2], dv0[2];
@@ -122,22 +159,37 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_const
 
     // ---- stage the four parity planes of hr around the tile (zero outside the image / the local rows) ----
     {
+        // one warp per hr row, four rows (12 independent 8-byte loads per lane) in flight before the scatter
         const int rbase = 2 * (A0 - D::HB), cbase = B0 - D::HB;
-        for (int rr2 = warp; rr2 < 2 * D::SR; rr2 += LT_WARPS) {
-            const int r = rbase + rr2, pr = r & 1;
-            const int rr = ((rr2 - pr) >> 1) - D::HB - du0[pr];
-            if (rr < 0 || rr >= D::SR) continue;
-            const bool rowok = r >= 0 && r < g.H && r >= g.hr_lo && r < g.hr_hi;
-            const float* src = a.hr + (size_t)(r - g.hr_lo) * g.W;
-            float* d0 = sm + ((pr * 2 + 0) * D::SR + rr) * D::SP;
-            float* d1 = sm + ((pr * 2 + 1) * D::SR + rr) * D::SP;
-            for (int cc2 = lane; cc2 <= D::SC; cc2 += 32) {
-                const int c = cbase + cc2;
-                float2 v = make_float2(0.f, 0.f);
-                if (rowok && c >= 0 && c < g.w) v = __ldg(reinterpret_cast<const float2*>(src) + c);
-                const int c0 = cc2 - D::HB - dv0[0], c1 = cc2 - D::HB - dv0[1];
-                if (c0 >= 0 && c0 < D::SC) d0[c0] = v.x;
-                if (c1 >= 0 && c1 < D::SC) d1[c1] = v.y;
+        constexpr int NCP = D::SC + 1, NJ = (NCP + 31) / 32, RB = 4;
+        const int o0 = D::HB + dv0[0], o1 = D::HB + dv0[1];             // plane column = cc2 - o
+        for (int rq = warp * RB; rq < 2 * D::SR; rq += LT_WARPS * RB) {
+            float2 v[RB][NJ];
+            #pragma unroll
+            for (int i = 0; i < RB; ++i) {
+                const int r = rbase + rq + i;
+                const bool rowok = r >= 0 && r < g.H && r >= g.hr_lo && r < g.hr_hi;
+                const float2* src = reinterpret_cast<const float2*>(a.hr + (size_t)(r - g.hr_lo) * g.W) + cbase;
+                #pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    const int cc2 = lane + 32 * j, c = cbase + cc2;
+                    v[i][j] = make_float2(0.f, 0.f);
+                    if (rowok && cc2 < NCP && c >= 0 && c < g.w) v[i][j] = __ldg(src + cc2);
+                }
+            }
+            #pragma unroll
+            for (int i = 0; i < RB; ++i) {
+                const int rr2 = rq + i, pr = rr2 & 1;                   // rbase is even
+                const int rr = ((rr2 - pr) >> 1) - D::HB - du0[pr];
+                if (rr < 0 || rr >= D::SR) continue;                    // warp-uniform
+                float* d0 = sm + ((pr * 2 + 0) * D::SR + rr) * D::SP - o0;
+                float* d1 = sm + ((pr * 2 + 1) * D::SR + rr) * D::SP - o1;
+                #pragma unroll
+                for (int j = 0; j < NJ; ++j) {
+                    const int cc2 = lane + 32 * j;
+                    if (cc2 >= o0 && cc2 < D::SC + o0) d0[cc2] = v[i][j].x;
+                    if (cc2 >= o1 && cc2 < D::SC + o1) d1[cc2] = v[i][j].y;
+                }
             }
         }
     }
@@ -152,12 +204,7 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_const
         const int us = (P + D::RT - pr) & 1, vs = (Q + D::RT - pc) & 1;
         const float* base = sm + (ph * D::SR + lane) * D::SP + LT_NB * warp;
         const int ntu = NT - us;                             // the odd tap set has NT-1 rows
-        #pragma unroll 1
-        for (int tu = 0; tu < ntu; ++tu) {
-            u64 xp[(LT_NB + NT) / 2];
-            lat_load_window<NT>(base + tu * D::SP, xp);
-            lat_conv_row<NT, 0>(xp, a.tab.e[us][vs][tu], a.tab.o[us][vs][tu], acc);
-        }
+        lat_conv_phase<NT, 0>(base, D::SP, wsm[us][vs], ntu, acc);
     }
     const int ar = A0 + lane, bc = B0 + LT_NB * warp;
     if (ar < g.sa_hi && bc < g.w) {
@@ -194,6 +241,7 @@ __global__ void __launch_bounds__(256) k_lat_edge_b(const LatEdgeBArgs a) {
     const int x = wid < ntop ? wid : 0;
     const int K = 2 * a.RT + 1;
     float v = 0.f;
+    #pragma unroll 8
     for (int t = lane; t < K * K; t += 32) {
         const int u = t / K, vv = t - u * K;
         const int r = y + a.RT - u, c = x + a.RT - vv;
@@ -250,6 +298,7 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
         for (int ar = r0; ar < r1; ++ar) {
             const float* blrow = a.bl[s] + (size_t)(ar - g.sa_lo) * g.pitch;
             float* arow_out = a.A[s] + (size_t)(ar - g.sa_lo) * g.pitch;
+            #pragma unroll 4
             for (int b = tid; b < g.w; b += 256) {
                 const float bl = __ldg(blrow + b);
                 float acc = 0.f, q = 0.f;
@@ -343,22 +392,23 @@ struct alignas(16) LatBwdArgs {
     int has_row0, has_col0;
 };
 
+struct LatEdgeRefs { const float* arow; const float* acol; const float* psf; int W, y_lo, y_hi, has_row0, has_col0; };
+
 template <int NT>
-__device__ __forceinline__ float lat_edge_terms(const LatBwdArgs<NT>& a, int Y, int X) {
+__device__ __noinline__ float lat_edge_terms(LatEdgeRefs e, int Y, int X) {
     constexpr int RT = NT - 1, K = 2 * RT + 1;
-    const LatGeom& g = a.g;
     float v = 0.f;
-    if (a.has_row0 && Y <= RT) {
-        const float* pr = a.psf + (RT - Y) * K;
+    if (e.has_row0 && Y <= RT) {
+        const float* pr = e.psf + (RT - Y) * K;
         for (int t = 0; t < K; ++t) {
             const int x = X - RT + t;
-            if (x >= 0 && x < g.W) v = fmaf(__ldg(pr + t), __ldg(a.arow + x), v);
+            if (x >= 0 && x < e.W) v = fmaf(__ldg(pr + t), __ldg(e.arow + x), v);
         }
     }
-    if (a.has_col0 && X <= RT) {
+    if (e.has_col0 && X <= RT) {
         for (int t = 0; t < K; ++t) {
             const int y = Y - RT + t;
-            if (y >= 0 && y < g.H && y >= g.hr_lo && y < g.hr_hi) v = fmaf(__ldg(a.psf + t * K + (RT - X)), __ldg(a.acol + y), v);
+            if (y >= e.y_lo && y < e.y_hi) v = fmaf(__ldg(e.psf + t * K + (RT - X)), __ldg(e.acol + y), v);
         }
     }
     return v;
@@ -367,23 +417,36 @@ __device__ __forceinline__ float lat_edge_terms(const LatBwdArgs<NT>& a, int Y, 
 template <int NT>
 __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_bwd(const __grid_constant__ LatBwdArgs<NT> a) {
     typedef LatDims<NT> D;
-    extern __shared__ __align__(16) float sm[];             // [nslot][SR][SP]
+    extern __shared__ __align__(16) float sm[];             // [nslot][SR][SP] + weight table
     const LatGeom& g = a.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    u64 (*wsm)[2][NT][NT + 2] = reinterpret_cast<u64 (*)[2][NT][NT + 2]>(sm + g.nslot * D::SR * D::SP);
+    for (int i = tid; i < 4 * NT * (NT + 2); i += LT_WARPS * 32) (&wsm[0][0][0][0])[i] = (&a.tab.w[0][0][0][0])[i];
     const int M0 = a.m_lo + blockIdx.y * LT_ROWS, N0 = blockIdx.x * LT_COLS;
 
     // ---- stage the residual planes around the tile: rows [M0-HB, M0-HB+SR), cols [N0-HB, N0-HB+SC) -------
     for (int s = 0; s < g.nslot; ++s) {
         const float* src = a.A[s];
         float* dst = sm + s * D::SR * D::SP;
-        for (int rr = warp; rr < D::SR; rr += LT_WARPS) {
-            const int ar = M0 - D::HB + rr;
-            const bool rowok = ar >= g.sa_lo && ar < g.sa_hi;
-            const float* row = src + (size_t)(ar - g.sa_lo) * g.pitch;
-            for (int cc = lane; cc < D::SP; cc += 32) {
-                const int b = N0 - D::HB + cc;
-                dst[rr * D::SP + cc] = (rowok && b >= 0 && b < g.w) ? __ldg(row + b) : 0.f;
+        constexpr int NC4 = D::SP / 4, NEL = D::SR * NC4, NTH = LT_WARPS * 32, BATCH = (NEL + NTH - 1) / NTH;
+        float4 v[BATCH];
+        #pragma unroll
+        for (int k = 0; k < BATCH; ++k) {                            // all loads first (independent), then the stores
+            const int e = tid + k * NTH;
+            const int rr = e / NC4, c4 = e - rr * NC4;
+            const int ar = M0 - D::HB + rr, b = N0 - D::HB + 4 * c4;     // b is a multiple of 4, pitch too
+            v[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+            if (e < NEL && ar >= g.sa_lo && ar < g.sa_hi && b >= 0 && b < g.w) {
+                v[k] = __ldg(reinterpret_cast<const float4*>(src + (size_t)(ar - g.sa_lo) * g.pitch + b));
+                if (b + 1 >= g.w) v[k].y = 0.f;
+                if (b + 2 >= g.w) v[k].z = 0.f;
+                if (b + 3 >= g.w) v[k].w = 0.f;
             }
+        }
+        #pragma unroll
+        for (int k = 0; k < BATCH; ++k) {
+            const int e = tid + k * NTH;
+            if (e < NEL) *reinterpret_cast<float4*>(dst + 4 * e) = v[k];   // rr * SP + 4 * c4 == 4 * e
         }
     }
     __syncthreads();
@@ -405,21 +468,8 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_bwd(const __grid_const
                 const int ro = D::HB - (qy >> 1), delta = D::HB - (qx >> 1);     // 0 or 1
                 const float* base = sm + (s * D::SR + lane + ro) * D::SP + LT_NB * warp;
                 const int ntu = NT - us;
-                if (delta == 0) {
-                    #pragma unroll 1
-                    for (int tu = 0; tu < ntu; ++tu) {
-                        u64 xp[(LT_NB + NT) / 2];
-                        lat_load_window<NT>(base + tu * D::SP, xp);
-                        lat_conv_row<NT, 0>(xp, a.tab.e[us][vs][tu], a.tab.o[us][vs][tu], acc);
-                    }
-                } else {
-                    #pragma unroll 1
-                    for (int tu = 0; tu < ntu; ++tu) {
-                        u64 xp[(LT_NB + NT) / 2];
-                        lat_load_window<NT>(base + tu * D::SP, xp);
-                        lat_conv_row<NT, 1>(xp, a.tab.e[us][vs][tu], a.tab.o[us][vs][tu], acc);
-                    }
-                }
+                if (delta == 0) lat_conv_phase<NT, 0>(base, D::SP, wsm[us][vs], ntu, acc);
+                else            lat_conv_phase<NT, 1>(base, D::SP, wsm[us][vs], ntu, acc);
             }
             if (px == 0) {
                 #pragma unroll
@@ -436,8 +486,9 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_bwd(const __grid_const
                     const float4 hv = __ldg(reinterpret_cast<const float4*>(hin) + q);
                     float c0 = v0[2 * q], c1 = lat_sum2(acc[2 * q]), c2 = v0[2 * q + 1], c3 = lat_sum2(acc[2 * q + 1]);
                     if (edge) {
-                        c0 += lat_edge_terms<NT>(a, Y, X0 + 4 * q);     c1 += lat_edge_terms<NT>(a, Y, X0 + 4 * q + 1);
-                        c2 += lat_edge_terms<NT>(a, Y, X0 + 4 * q + 2); c3 += lat_edge_terms<NT>(a, Y, X0 + 4 * q + 3);
+                        const LatEdgeRefs er{a.arow, a.acol, a.psf, g.W, max(g.hr_lo, 0), min(g.hr_hi, g.H), a.has_row0, a.has_col0};
+                        c0 += lat_edge_terms<NT>(er, Y, X0 + 4 * q);     c1 += lat_edge_terms<NT>(er, Y, X0 + 4 * q + 1);
+                        c2 += lat_edge_terms<NT>(er, Y, X0 + 4 * q + 2); c3 += lat_edge_terms<NT>(er, Y, X0 + 4 * q + 3);
                     }
                     float4 r;
                     r.x = fminf(fmaxf(fmaf(a.alpha, c0, hv.x), a.lo), a.hi);
@@ -473,8 +524,9 @@ static void build_tab(const std::vector<float>& psfP, bool forward, LatTab<NT>& 
                     const int v = forward ? 2 * RT - vs - 2 * tv : 2 * tv + vs;
                     w[tv + 1] = (u >= 0 && u < K && v >= 0 && v < K) ? psfP[(size_t)u * K + v] : 0.f;
                 }
-                for (int m = 0; m < NT / 2; ++m)  t.e[us][vs][tu][m] = pack_pair(w[2 * m + 1], w[2 * m + 2]);
-                for (int m = 0; m <= NT / 2; ++m) t.o[us][vs][tu][m] = pack_pair(w[2 * m], w[2 * m + 1]);
+                for (int m = 0; m < NT / 2; ++m)  t.w[us][vs][tu][m] = pack_pair(w[2 * m + 1], w[2 * m + 2]);
+                for (int m = 0; m <= NT / 2; ++m) t.w[us][vs][tu][NT / 2 + m] = pack_pair(w[2 * m], w[2 * m + 1]);
+                t.w[us][vs][tu][NT + 1] = 0ull;
             }
 }
 
@@ -554,7 +606,7 @@ static void lat_setup(const LatPlan* L, const LatCall& c, LatSetup& S) {
     }
     S.has_row0 = 0; S.has_col0 = 0;
     for (int k = 0; k < c.n; ++k) { if (c.sy[k] == -1 && c.hr_lo == 0) S.has_row0 = 1; if (c.sx[k] == -1) S.has_col0 = 1; }
-    S.rows_per_cta = 4;
+    S.rows_per_cta = 1;
     S.nsite_cta = (g.sa_hi - g.sa_lo + S.rows_per_cta - 1) / S.rows_per_cta;
 }
 
@@ -590,10 +642,10 @@ template <int NT>
 static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const LatTab<NT>& ft, const LatTab<NT>& bt, cudaStream_t st) {
     typedef LatDims<NT> D;
     const LatGeom& g = S.g;
-    const size_t smem_f = sizeof(float) * 4 * D::SR * D::SP, smem_b = sizeof(float) * g.nslot * D::SR * D::SP;
+    const size_t smem_f = sizeof(float) * 4 * D::SR * D::SP + sizeof(LatTab<NT>), smem_b = sizeof(float) * g.nslot * D::SR * D::SP + sizeof(LatTab<NT>);
     if (!L->attr_done) {
         SR_CUDA(cudaFuncSetAttribute(k_lat_fwd<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
-        SR_CUDA(cudaFuncSetAttribute(k_lat_bwd<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * kMaxSlots * D::SR * D::SP)));
+        SR_CUDA(cudaFuncSetAttribute(k_lat_bwd<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * kMaxSlots * D::SR * D::SP + sizeof(LatTab<NT>))));
         L->attr_done = true;
     }
     const int tiles_x = (g.w + LT_COLS - 1) / LT_COLS;
