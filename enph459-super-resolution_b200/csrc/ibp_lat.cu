@@ -106,19 +106,26 @@ __device__ __forceinline__ void lat_load_wo(const u64* row, u64 (&wo)[NT / 2 + 2
 // software-pipelined: next window and next weight packing are fetched under the FFMA2 of the current ones
 template <int NT, int DELTA>
 __device__ __forceinline__ void lat_conv_phase(const float* base, int pitch, const u64 (*wt)[NT + 2], int ntu, u64 (&acc)[LT_NB]) {
-    u64 x[(LT_NB + NT) / 2], xn[(LT_NB + NT) / 2], we[NT / 2], wo[NT / 2 + 2];
-    lat_load_window<NT>(base, x);
+    u64 xa[(LT_NB + NT) / 2], xb[(LT_NB + NT) / 2], we[NT / 2], wo[NT / 2 + 2];
+    lat_load_window<NT>(base, xa);
     lat_load_we<NT>(wt[0], we);
-    #pragma unroll 2
-    for (int tu = 0; tu < ntu; ++tu) {
-        const int t1 = min(tu + 1, ntu - 1);
+    #pragma unroll 1
+    for (int tu = 0; tu < ntu; tu += 2) {                    // two tap rows per trip: windows alternate xa / xb
+        const int t1 = min(tu + 1, ntu - 1), t2 = min(tu + 2, ntu - 1);
         lat_load_wo<NT>(wt[tu], wo);
-        lat_load_window<NT>(base + t1 * pitch, xn);
-        lat_conv_even<NT, DELTA>(x, we, acc);
+        lat_load_window<NT>(base + t1 * pitch, xb);
+        lat_conv_even<NT, DELTA>(xa, we, acc);
         lat_load_we<NT>(wt[t1], we);
-        lat_conv_odd<NT, DELTA>(x, wo, acc);
-        #pragma unroll
-        for (int i = 0; i < (LT_NB + NT) / 2; ++i) x[i] = xn[i];
+        lat_conv_odd<NT, DELTA>(xa, wo, acc);
+        if (tu + 1 < ntu) {                                  // warp-uniform
+            lat_load_wo<NT>(wt[t1], wo);
+            lat_load_window<NT>(base + t2 * pitch, xa);
+            lat_conv_even<NT, DELTA>(xb, we, acc);
+            lat_load_we<NT>(wt[t2], we);
+            lat_conv_odd<NT, DELTA>(xb, wo, acc);
+        } else {
+            lat_load_we<NT>(wt[t2], we);
+        }
     }
 }
 
@@ -136,7 +143,7 @@ template <int NT> struct LatDims {
 // =====================================================================================================
 template <int NT>
 struct alignas(16) LatFwdArgs {
-    LatTab<NT> tab;                     // w(tu,tv) = psf[2RT - us - 2tu][2RT - vs - 2tv]
+    const ulonglong2* tab;              // LatTab<NT>, device: w(tu,tv) = psf[2RT - us - 2tu][2RT - vs - 2tv]
     LatGeom g;
     const float* hr;                    // local buffer, row 0 = HR row hr_lo
     float* bl[kMaxSlots];
@@ -150,7 +157,7 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_const
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int s = blockIdx.z;
     u64 (*wsm)[2][NT][NT + 2] = reinterpret_cast<u64 (*)[2][NT][NT + 2]>(sm + 4 * D::SR * D::SP);
-    for (int i = tid; i < 4 * NT * (NT + 2); i += LT_WARPS * 32) (&wsm[0][0][0][0])[i] = (&a.tab.w[0][0][0][0])[i];
+    for (int i = tid; i < 2 * NT * (NT + 2); i += LT_WARPS * 32) reinterpret_cast<ulonglong2*>(wsm)[i] = __ldg(a.tab + i);
     const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
     const int A0 = g.sa_lo + blockIdx.y * LT_ROWS, B0 = blockIdx.x * LT_COLS;
     int du0[2], dv0[2];
@@ -269,6 +276,7 @@ struct LatResidArgs {
     float* arow;                        // [W] clamp duplicates on HR row 0
     float* acol;                        // [H] clamp duplicates on HR column 0 ((0,0): only frames with sy != -1)
     int rows_per_cta, nsite_cta;        // part A: CTAs per slot = ceil(rows / rows_per_cta)
+    int nrow_cta, ncol_cta;             // parts B/C: CTAs of 256 columns along row 0 / 256 rows along column 0
     double* partial;                    // one slot per CTA
 };
 
@@ -291,32 +299,46 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
         // ---- part A: regular sites ------------------------------------------------------------------
         const int s = blockIdx.x / a.nsite_cta, cb = blockIdx.x - s * a.nsite_cta;
         const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
-        int ks[kMaxFrames], oy[kMaxFrames], ox[kMaxFrames], cnt = 0;
-        for (int k = 0; k < a.n; ++k)
-            if (a.slot_of[k] == s) { ks[cnt] = k; oy[cnt] = (P + a.sy[k]) >> 1; ox[cnt] = (Q + a.sx[k]) >> 1; ++cnt; }
         const int r0 = g.sa_lo + cb * a.rows_per_cta, r1 = min(r0 + a.rows_per_cta, g.sa_hi);
         for (int ar = r0; ar < r1; ++ar) {
             const float* blrow = a.bl[s] + (size_t)(ar - g.sa_lo) * g.pitch;
             float* arow_out = a.A[s] + (size_t)(ar - g.sa_lo) * g.pitch;
-            #pragma unroll 4
+            // per-frame row pointers (null: the frame has no sample on this site row); unrolled -> registers
+            const float* rowp[kMaxFrames]; int jmax[kMaxFrames]; bool own[kMaxFrames];
+            #pragma unroll
+            for (int k = 0; k < kMaxFrames; ++k) {
+                rowp[k] = nullptr; jmax[k] = 0; own[k] = false;
+                if (k < a.n && a.slot_of[k] == s) {
+                    const int i = ar + ((P + a.sy[k]) >> 1), ox = (Q + a.sx[k]) >> 1;
+                    if (i < g.h && i >= a.lr_lo && i < a.lr_hi) {
+                        rowp[k] = a.lr[k] + (size_t)(i - a.lr_lo) * g.w + ox;
+                        jmax[k] = g.w - ox;                              // site columns b < jmax have a sample
+                        own[k] = i >= a.own_i0 && i < a.own_i1;
+                    }
+                }
+            }
+            #pragma unroll 2
             for (int b = tid; b < g.w; b += 256) {
                 const float bl = __ldg(blrow + b);
+                float v[kMaxFrames];
+                #pragma unroll
+                for (int k = 0; k < kMaxFrames; ++k) v[k] = (rowp[k] && b < jmax[k]) ? __ldg(rowp[k] + b) : bl;   // all loads first
                 float acc = 0.f, q = 0.f;
-                for (int f = 0; f < cnt; ++f) {
-                    const int i = ar + oy[f], j = b + ox[f];
-                    if (i >= g.h || j >= g.w || i < a.lr_lo || i >= a.lr_hi) continue;
-                    const float e = __ldg(a.lr[ks[f]] + (size_t)(i - a.lr_lo) * g.w + j) - bl;
+                #pragma unroll
+                for (int k = 0; k < kMaxFrames; ++k) {
+                    const float e = v[k] - bl;                           // exactly 0 where there is no sample
                     acc += e;
-                    if (i >= a.own_i0 && i < a.own_i1) q = fmaf(e, e, q);
+                    if (own[k]) q = fmaf(e, e, q);
                 }
                 arow_out[b] = acc;
                 e2 += (double)q;
             }
         }
-    } else if ((int)blockIdx.x == nA) {
+    } else if ((int)blockIdx.x < nA + a.nrow_cta) {
+        const int c0 = ((int)blockIdx.x - nA) * 256;                       // this CTA's 256 columns
         // ---- parts B/C along HR row 0 / LR row 0 (only where the local rows include them) -----------------
         if (g.hr_lo == 0) {
-            for (int x = tid; x < g.W; x += 256) {
+            for (int x = c0 + tid; x < min(g.W, c0 + 256); x += 256) {
                 float acc = 0.f;
                 for (int k = 0; k < a.n; ++k) {
                     if (a.sy[k] != -1) continue;
@@ -329,7 +351,7 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
                 a.arow[x] = acc;
             }
             if (a.own_i0 == 0) {
-                for (int j = tid; j < g.w; j += 256)
+                for (int j = c0 + tid; j < min(g.w, c0 + 256); j += 256)
                     for (int k = 0; k < a.n; ++k) {
                         if (a.sy[k] != +1) continue;                          // i = 0 samples the clamped row 0
                         const int bx = min(max(2 * j - a.sx[k], 0), g.W - 1);
@@ -340,7 +362,8 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
         }
     } else {
         // ---- parts B/C along HR column 0 / LR column 0 ----------------------------------------------------------
-        for (int y = g.hr_lo + tid; y < g.hr_hi; y += 256) {
+        const int r0 = ((int)blockIdx.x - nA - a.nrow_cta) * 256;           // this CTA's 256 rows
+        for (int y = g.hr_lo + r0 + tid; y < min(g.hr_hi, g.hr_lo + r0 + 256); y += 256) {
             float acc = 0.f;
             for (int k = 0; k < a.n; ++k) {
                 if (a.sx[k] != -1) continue;
@@ -354,7 +377,8 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
             }
             a.acol[y] = acc;
         }
-        for (int i = max(a.own_i0, a.lr_lo) + tid; i < min(a.own_i1, a.lr_hi); i += 256)
+        for (int i = a.lr_lo + r0 + tid; i < min(a.lr_hi, a.lr_lo + r0 + 256); i += 256) {
+            if (i < a.own_i0 || i >= a.own_i1) continue;
             for (int k = 0; k < a.n; ++k) {
                 if (a.sx[k] != +1) continue;                                  // j = 0 samples the clamped column 0
                 if (i == 0 && a.sy[k] == +1) continue;                        // counted with row 0 above
@@ -362,6 +386,7 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
                 const float e = __ldg(a.lr[k] + (size_t)(i - a.lr_lo) * g.w) - lat_bval(a, k, by, 0);
                 e2 += (double)(e * e);
             }
+        }
     }
     __shared__ double red[8];
     #pragma unroll
@@ -382,7 +407,7 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
 // =====================================================================================================
 template <int NT>
 struct alignas(16) LatBwdArgs {
-    LatTab<NT> tab;                     // w(tu,tv) = psf[2tu + us][2tv + vs]
+    const ulonglong2* tab;              // LatTab<NT>, device: w(tu,tv) = psf[2tu + us][2tv + vs]
     LatGeom g;
     const float* A[kMaxSlots];
     const float* hr_in; float* hr_out;  // local buffers, row 0 = HR row hr_lo
@@ -415,13 +440,13 @@ __device__ __noinline__ float lat_edge_terms(LatEdgeRefs e, int Y, int X) {
 }
 
 template <int NT>
-__global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_bwd(const __grid_constant__ LatBwdArgs<NT> a) {
+__global__ void __launch_bounds__(LT_WARPS * 32, 4) k_lat_bwd(const __grid_constant__ LatBwdArgs<NT> a) {
     typedef LatDims<NT> D;
     extern __shared__ __align__(16) float sm[];             // [nslot][SR][SP] + weight table
     const LatGeom& g = a.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     u64 (*wsm)[2][NT][NT + 2] = reinterpret_cast<u64 (*)[2][NT][NT + 2]>(sm + g.nslot * D::SR * D::SP);
-    for (int i = tid; i < 4 * NT * (NT + 2); i += LT_WARPS * 32) (&wsm[0][0][0][0])[i] = (&a.tab.w[0][0][0][0])[i];
+    for (int i = tid; i < 2 * NT * (NT + 2); i += LT_WARPS * 32) reinterpret_cast<ulonglong2*>(wsm)[i] = __ldg(a.tab + i);
     const int M0 = a.m_lo + blockIdx.y * LT_ROWS, N0 = blockIdx.x * LT_COLS;
 
     // ---- stage the residual planes around the tile: rows [M0-HB, M0-HB+SR), cols [N0-HB, N0-HB+SC) -------
@@ -536,6 +561,7 @@ struct LatPlan {
     LatTab<16> f16, b16;
     LatTab<8>  f8, b8;
     float* d_psf = nullptr;
+    void *d_tabf = nullptr, *d_tabb = nullptr;   // device copies of the forward / backward tables
     // planes (allocated for one geometry)
     int rows = 0, pitch = 0, nslot = 0, H = 0, W = 0;
     float* d_bl[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
@@ -548,6 +574,8 @@ struct LatPlan {
 bool lat_supported(int kh, int kw, int smax, int W) {
     return (kh & 1) && (kw & 1) && kh / 2 <= 15 && kw / 2 <= 15 && smax <= 1 && (W % 4) == 0;
 }
+
+void lat_destroy(LatPlan* L);
 
 int lat_create(LatPlan** out, const double* psf, int kh, int kw) {
     LatPlan* L = new (std::nothrow) LatPlan();
@@ -565,6 +593,15 @@ int lat_create(LatPlan** out, const double* psf, int kh, int kw) {
         set_error("lat_create: device allocation failed"); delete L; return SR459_ECUDA;
     }
     L->bytes += (int64_t)sizeof(float) * K * K;
+    const void* hf = L->NT == 16 ? (const void*)&L->f16 : (const void*)&L->f8;
+    const void* hb = L->NT == 16 ? (const void*)&L->b16 : (const void*)&L->b8;
+    const size_t tb = L->NT == 16 ? sizeof(LatTab<16>) : sizeof(LatTab<8>);
+    if (cudaMalloc(&L->d_tabf, tb) != cudaSuccess || cudaMalloc(&L->d_tabb, tb) != cudaSuccess ||
+        cudaMemcpy(L->d_tabf, hf, tb, cudaMemcpyHostToDevice) != cudaSuccess ||
+        cudaMemcpy(L->d_tabb, hb, tb, cudaMemcpyHostToDevice) != cudaSuccess) {
+        set_error("lat_create: device allocation failed"); lat_destroy(L); return SR459_ECUDA;
+    }
+    L->bytes += 2 * (int64_t)tb;
     *out = L;
     return SR459_OK;
 }
@@ -583,12 +620,14 @@ void lat_destroy(LatPlan* L) {
     if (!L) return;
     lat_free_planes(L);
     if (L->d_psf) cudaFree(L->d_psf);
+    if (L->d_tabf) cudaFree(L->d_tabf);
+    if (L->d_tabb) cudaFree(L->d_tabb);
     delete L;
 }
 
 int64_t lat_scratch_bytes(const LatPlan* L) { return L ? L->bytes : 0; }
 
-struct LatSetup { LatGeom g; int slot_of[kMaxFrames]; int has_row0, has_col0; int nsite_cta, rows_per_cta; };
+struct LatSetup { LatGeom g; int slot_of[kMaxFrames]; int has_row0, has_col0; int nsite_cta, rows_per_cta, nrow_cta, ncol_cta; };
 
 static void lat_setup(const LatPlan* L, const LatCall& c, LatSetup& S) {
     LatGeom& g = S.g;
@@ -608,11 +647,13 @@ static void lat_setup(const LatPlan* L, const LatCall& c, LatSetup& S) {
     for (int k = 0; k < c.n; ++k) { if (c.sy[k] == -1 && c.hr_lo == 0) S.has_row0 = 1; if (c.sx[k] == -1) S.has_col0 = 1; }
     S.rows_per_cta = 1;
     S.nsite_cta = (g.sa_hi - g.sa_lo + S.rows_per_cta - 1) / S.rows_per_cta;
+    S.nrow_cta = (g.W + 255) / 256;
+    S.ncol_cta = (g.hr_hi - g.hr_lo + 255) / 256;
 }
 
 int lat_per_iter(const LatPlan* L, const LatCall& c) {
     LatSetup S; lat_setup(L, c, S);
-    return S.nsite_cta * S.g.nslot + 2;
+    return S.nsite_cta * S.g.nslot + S.nrow_cta + S.ncol_cta;
 }
 
 static int lat_ensure_planes(LatPlan* L, const LatGeom& g) {
@@ -651,7 +692,7 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
     const int tiles_x = (g.w + LT_COLS - 1) / LT_COLS;
     {   // forward
         LatFwdArgs<NT> a;
-        a.tab = ft; a.g = g; a.hr = c.hr_in;
+        a.tab = reinterpret_cast<const ulonglong2*>(L->d_tabf); a.g = g; a.hr = c.hr_in;
         for (int s = 0; s < kMaxSlots; ++s) a.bl[s] = L->d_bl[s];
         dim3 grid(tiles_x, (g.sa_hi - g.sa_lo + LT_ROWS - 1) / LT_ROWS, g.nslot);
         k_lat_fwd<NT><<<grid, LT_WARPS * 32, smem_f, st>>>(a);
@@ -670,14 +711,14 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
         a.lr_lo = c.lr_lo; a.lr_hi = c.lr_hi; a.own_i0 = c.own_i0; a.own_i1 = c.own_i1;
         for (int s = 0; s < kMaxSlots; ++s) { a.bl[s] = L->d_bl[s]; a.A[s] = L->d_A[s]; }
         a.btop = L->d_btop; a.bleft = L->d_bleft; a.arow = L->d_arow; a.acol = L->d_acol;
-        a.rows_per_cta = S.rows_per_cta; a.nsite_cta = S.nsite_cta;
+        a.rows_per_cta = S.rows_per_cta; a.nsite_cta = S.nsite_cta; a.nrow_cta = S.nrow_cta; a.ncol_cta = S.ncol_cta;
         a.partial = c.partial;
-        k_lat_resid<<<S.nsite_cta * g.nslot + 2, 256, 0, st>>>(a);
+        k_lat_resid<<<S.nsite_cta * g.nslot + S.nrow_cta + S.ncol_cta, 256, 0, st>>>(a);
         SR_LAUNCH_CHECK("k_lat_resid");
     }
     {   // backward + update
         LatBwdArgs<NT> a;
-        a.tab = bt; a.g = g;
+        a.tab = reinterpret_cast<const ulonglong2*>(L->d_tabb); a.g = g;
         for (int s = 0; s < kMaxSlots; ++s) a.A[s] = L->d_A[s];
         a.hr_in = c.hr_in; a.hr_out = c.hr_out;
         a.m_lo = c.upd_y0 / 2; a.m_hi = c.upd_y1 / 2;
