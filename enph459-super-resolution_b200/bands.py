@@ -136,9 +136,15 @@ class BandPlan:
         _lib.check(self._lib.sr459_plan_set_path(self._h, int(path)))
         return self
 
-    def run(self, lr_local: Sequence, hr_local, n_iter: int, group=None, exchange: Optional[Callable] = exchange_halos):
+    def run(self, lr_local: Sequence, hr_local, n_iter: int, group=None, exchange: Optional[Callable] = exchange_halos,
+            graph: bool = False):
         """IBP on this rank's band.  lr_local: the n frames' rows [lr_lo, lr_hi); hr_local: float32 CUDA
-        tensor with HR rows [hr_lo, hr_hi) (halos filled).  Returns (hr_local_result, errors)."""
+        tensor with HR rows [hr_lo, hr_hi) (halos filled).  Returns (hr_local_result, errors).
+
+        graph=True captures the whole K-iteration loop -- kernels AND the NCCL send/recv of every
+        iteration -- into one CUDA graph and replays it: the loop is launch-bound otherwise (one
+        ctypes call + one batched P2P group per iteration is ~60 us of host time against 20-200 us of
+        kernels).  Every rank must pass the same flag."""
         from . import ops
         torch = ops._torch()
         lay = self.layout
@@ -155,12 +161,40 @@ class BandPlan:
         def iterate(cur, nxt, it):
             _lib.check(self._lib.sr459_band_iterate(self._h, arr, ops._ptr(cur), ops._ptr(nxt), int(it), ops._stream_ptr()))
 
-        res = band_loop(lay, hr_local, scratch, int(n_iter), iterate, exchange or (lambda *a: None), group)
+        exch = exchange or (lambda *a: None)
+        if graph and n_iter > 0:
+            hr0 = hr_local.clone()
+            # un-captured warm-up: lazy plan scratch gets allocated, NCCL P2P channels get connected.
+            # It only writes `scratch` (rewritten by iteration 0) and partial-sum slot 0 (ditto).
+            iterate(hr_local, scratch, 0)
+            exch(scratch, lay, group)
+            torch.cuda.synchronize()
+            side = torch.cuda.Stream()
+            side.wait_stream(torch.cuda.current_stream())
+            g = torch.cuda.CUDAGraph()
+            with torch.cuda.graph(g, stream=side, capture_error_mode="thread_local"):
+                res = band_loop(lay, hr_local, scratch, int(n_iter), iterate, exch, group)
+            hr_local.copy_(hr0)                              # the warm-up left hr_local untouched, the capture too
+            if lay.world > 1:
+                import torch.distributed as dist
+                dist.barrier(group)                          # replays start together (capture time differs per rank)
+                torch.cuda.synchronize()
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            g.replay()
+            e1.record()
+            self._graph = g                                  # keeps the captured launches alive until the next run
+        else:
+            e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            e0.record()
+            res = band_loop(lay, hr_local, scratch, int(n_iter), iterate, exch, group)
+            e1.record()
         sums = np.zeros(max(int(n_iter), 0), dtype=np.float64)
         if n_iter > 0:
             _lib.check(self._lib.sr459_band_errors(self._h, int(n_iter), sums.ctypes.data_as(C.POINTER(C.c_double)),
                                                    ops._stream_ptr()))
         errors = reduce_errors(sums, self.n, lay, group, device=hr_local.device)
+        self.last_loop_ms = e0.elapsed_time(e1) if n_iter > 0 else 0.0      # device time of the K-iteration loop
         return res, errors
 
 

@@ -134,3 +134,136 @@ class FrameSetPipeline:
 def shard_indices(n_items: int, rank: int, world: int) -> List[int]:
     """Item i goes to rank i mod world (batch mode)."""
     return list(range(rank, n_items, world))
+
+
+class BurstStream:
+    """Continuous frame sets at camera rate (BASELINE config 5): one HR image per n-frame XPR cycle.
+
+    The reference acquires one frame per mirror corner (settle, trigger, capture --
+    data_collection/collect_hw_triggered.py:183-188) or streams bursts through a frame callback
+    that copies every frame into a list (api/allied_vision_camera.py:90-115) and only then runs
+    run_sr.py offline.  Here the callback side is `frame_buffer()` / `commit_frame()` (or
+    `push_frame()`): every uint8 frame goes into a pinned ring slot and its H2D copy is enqueued
+    at once, so when the LAST frame of a set arrives only that frame's copy (3 MB) is still
+    ahead of the kernels.  The job (u8 -> f32, SAA, K IBP iterations, clip + truncation to u8)
+    runs on its own stream -- optionally as one captured CUDA graph launch -- and the uint8 HR
+    image is copied back to pinned host memory.  `wait_result()` returns it with the latency
+    from the last frame's commit to the result being on the host.
+    """
+
+    def __init__(self, n_frames, h, w, shifts_yx, kernel, n_iter, factor=2, step=ops.IBP_STEP_SIZE,
+                 depth=3, use_graph=False, device=None):
+        torch = ops._torch()
+        self.torch = torch
+        if device is not None:
+            torch.cuda.set_device(device)
+        self.dev = torch.device("cuda", torch.cuda.current_device())
+        self.n, self.h, self.w, self.n_iter = int(n_frames), int(h), int(w), int(n_iter)
+        self.depth = int(depth)
+        self.use_graph = bool(use_graph)
+        self.s_h2d, self.s_cmp, self.s_d2h = (torch.cuda.Stream() for _ in range(3))
+        self.slots = []
+        for _ in range(self.depth):
+            plan = ops.Plan(n_frames, h, w, shifts_yx, kernel, factor, step)     # one plan per slot: graphs bake pointers
+            H, W = plan.H, plan.W
+            self.slots.append(dict(
+                plan=plan,
+                host_in=torch.empty((self.n, self.h, self.w), dtype=torch.uint8).pin_memory(),
+                raw=torch.empty((self.n, self.h, self.w), dtype=torch.uint8, device=self.dev),
+                lr=torch.empty((self.n, self.h, self.w), dtype=torch.float32, device=self.dev),
+                hr=torch.empty((H, W), dtype=torch.float32, device=self.dev),
+                out=torch.empty((H, W), dtype=torch.uint8, device=self.dev),
+                host_out=torch.empty((H, W), dtype=torch.uint8).pin_memory(),
+                ev_in=torch.cuda.Event(), ev_cmp=torch.cuda.Event(), ev_out=torch.cuda.Event(),
+                graph=None, set_index=-1, t_commit=0.0,
+            ))
+        self.H, self.W = self.slots[0]["plan"].H, self.slots[0]["plan"].W
+        self.frames_in = 0                       # frames committed so far
+        self.sets_out = 0                        # results handed out so far
+        self.h2d_bytes = self.n * self.h * self.w
+        self.d2h_bytes = self.H * self.W
+        for slot in self.slots:                  # warm-up: lazy plan scratch is allocated outside any capture
+            self._job(slot)
+        torch.cuda.synchronize()
+        if self.use_graph:
+            for slot in self.slots:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.s_cmp):
+                    self._job(slot)
+                slot["graph"] = g
+
+    def close(self):
+        self.torch.cuda.synchronize()
+        for slot in self.slots:
+            slot["graph"] = None
+            slot["plan"].close()
+
+    def _job(self, slot):
+        """u8 -> f32, SAA + IBP, clip + truncation, on the current stream (run_sr.py:73-75, :181-209, :303)."""
+        import ctypes as C
+        lib = ops._lib.load()
+        st = C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+        ops._lib.check(lib.sr459_u8_to_f32(ops._ptr(slot["raw"]), slot["raw"].numel(), ops._ptr(slot["lr"]), st))
+        slot["plan"].saa_ibp([slot["lr"][k] for k in range(self.n)], self.n_iter, out=slot["hr"], want_errors=False)
+        ops._lib.check(lib.sr459_f32_to_u8(ops._ptr(slot["hr"]), slot["hr"].numel(), ops._ptr(slot["out"]), st))
+
+    # -- producer side (camera callback) -------------------------------------------------------------
+    def frame_buffer(self):
+        """Pinned uint8 view (h, w) the next frame should be written into (zero-copy hand-over)."""
+        set_idx, k = divmod(self.frames_in, self.n)
+        slot = self.slots[set_idx % self.depth]
+        if k == 0 and slot["set_index"] >= 0 and slot["set_index"] >= self.sets_out:
+            raise RuntimeError("BurstStream ring is full: wait_result() must drain older sets first")
+        return slot["host_in"][k]
+
+    def commit_frame(self):
+        """The frame written into frame_buffer() is complete: enqueue its H2D copy; launch the job on the last one."""
+        torch = self.torch
+        set_idx, k = divmod(self.frames_in, self.n)
+        slot = self.slots[set_idx % self.depth]
+        with torch.cuda.stream(self.s_h2d):
+            if k == 0:
+                self.s_h2d.wait_event(slot["ev_cmp"])        # the slot's previous job has consumed raw
+            slot["raw"][k].copy_(slot["host_in"][k], non_blocking=True)
+            if k == self.n - 1:
+                slot["ev_in"].record(self.s_h2d)
+        self.frames_in += 1
+        if k != self.n - 1:
+            return None
+        slot["t_commit"] = time.perf_counter()
+        slot["set_index"] = set_idx
+        with torch.cuda.stream(self.s_cmp):
+            self.s_cmp.wait_event(slot["ev_in"])
+            self.s_cmp.wait_event(slot["ev_out"])            # previous read-back of this slot's out buffer
+            if slot["graph"] is not None:
+                slot["graph"].replay()
+            else:
+                self._job(slot)
+            slot["ev_cmp"].record(self.s_cmp)
+        with torch.cuda.stream(self.s_d2h):
+            self.s_d2h.wait_event(slot["ev_cmp"])
+            slot["host_out"].copy_(slot["out"], non_blocking=True)
+            slot["ev_out"].record(self.s_d2h)
+        return set_idx
+
+    def push_frame(self, frame):
+        """Copy a uint8 frame (numpy or torch, h x w) into the ring and commit it."""
+        buf = self.frame_buffer()
+        if isinstance(frame, np.ndarray):
+            buf.numpy()[...] = frame
+        else:
+            buf.copy_(frame)
+        return self.commit_frame()
+
+    # -- consumer side -----------------------------------------------------------------------------------
+    def wait_result(self):
+        """Block until the oldest outstanding HR image is on the host.  Returns (set_index, pinned uint8 H x W
+        tensor -- valid until `depth` further sets have been committed --, latency in seconds)."""
+        if self.sets_out * self.n + self.n > self.frames_in:
+            raise RuntimeError("no complete frame set is outstanding")
+        slot = self.slots[self.sets_out % self.depth]
+        slot["ev_out"].synchronize()
+        lat = time.perf_counter() - slot["t_commit"]
+        idx = self.sets_out
+        self.sets_out += 1
+        return idx, slot["host_out"], lat

@@ -576,6 +576,39 @@ def test_row_bands_emulated_vs_oracle(sr, world, case):
     _errs_close(errs, e_o)
 
 
+@pytest.mark.parametrize("use_graph", [False, True])
+def test_burst_stream_matches_oracle(sr, use_graph):
+    """Streaming burst mode (config 5): frames committed one by one, uint8 HR images out, ring re-use."""
+    from sr459.driver import BurstStream
+    rng = np.random.default_rng(55)
+    h, w, K = 48, 64, 5
+    psf = O.make_gaussian_psf()
+    sets = [[rng.integers(0, 256, (h, w), dtype=np.uint8) for _ in NOMINAL] for _ in range(5)]
+    bs = BurstStream(4, h, w, NOMINAL, psf, K, depth=2, use_graph=use_graph)
+    got = []
+    for i, frames in enumerate(sets):
+        for k, f in enumerate(frames):
+            r = bs.push_frame(f)
+            assert (r == i) if k == 3 else (r is None)
+        if i >= 1:                                             # keep one set in flight
+            idx, img, lat = bs.wait_result()
+            got.append((idx, img.clone().numpy())); assert lat > 0
+    idx, img, lat = bs.wait_result()
+    got.append((idx, img.clone().numpy()))
+    with pytest.raises(RuntimeError):
+        bs.wait_result()
+    bs.close()
+    assert [g[0] for g in got] == list(range(5))
+    for i, img in got:
+        lrs = [f.astype(np.float64) for f in sets[i]]
+        saa = O.shift_and_add_integer(lrs, NOMINAL)
+        ref, _ = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa, n_iter=K)
+        ref8 = np.clip(ref, 0, 255).astype(np.uint8)
+        # truncation makes a +-1 difference possible where the float value sits within the tolerance of an integer
+        d = np.abs(img.astype(np.int16) - ref8.astype(np.int16))
+        assert d.max() <= 1 and (d > 0).mean() < 1e-3, f"set {i}: {d.max()} / {(d > 0).mean()}"
+
+
 def test_band_plan_refuses_fractional_shifts(sr):
     from sr459.bands import BandPlan
     with pytest.raises(sr.Sr459Error) as ei:
