@@ -102,6 +102,14 @@ def main():
         line["mse_rel_vs_single_gpu"] = float(np.max(np.abs(np.array(errs) / np.array(ref_errs) - 1.0)))
     if rank == 0:
         print(json.dumps(line), flush=True)
+    if args.graph:
+        # a process group whose NCCL communicator has work captured in a CUDA graph does not tear down cleanly
+        # (destroy_process_group blocks); everything is measured and printed, so leave without the teardown
+        torch.cuda.synchronize()
+        if world > 1:
+            dist.barrier()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
     bp.close(); full_plan.close()
     if world > 1:
         dist.destroy_process_group()

@@ -1,7 +1,7 @@
 #!/usr/bin/env python3
 """Dev helper: per-stage device timings (CUDA events) of the BASELINE configs that are not the bench line.
 
-    python tools/time_configs.py [c1 c2 c2int monocal c1meas ...]
+    python tools/time_configs.py [--path=N] [c1 c2 c2int monocal c1meas c4 ...]
 """
 import os
 import sys
@@ -45,7 +45,9 @@ CONFIGS = {
 def main():
     import torch
     import sr459
-    names = sys.argv[1:] or ["c1", "c2", "c2int", "monocal", "c1meas"]
+    argv = [a for a in sys.argv[1:] if not a.startswith("--path=")]
+    force = [int(a.split("=")[1]) for a in sys.argv[1:] if a.startswith("--path=")]
+    names = argv or ["c1", "c2", "c2int", "monocal", "c1meas", "c4"]
     rng = np.random.default_rng(459)
     for name in names:
         h, w, shifts, psfname, iters = CONFIGS[name]
@@ -53,6 +55,8 @@ def main():
         n = len(shifts)
         frames = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in range(n)]
         plan = sr459.Plan(n, h, w, shifts, psf)
+        if force:
+            plan.set_path(force[0])
         hr = torch.empty((2 * h, 2 * w), dtype=torch.float32, device="cuda")
         ev = [torch.cuda.Event(enable_timing=True) for _ in range(4)]
         best = None
