@@ -180,6 +180,7 @@ class BurstStream:
         self.H, self.W = self.slots[0]["plan"].H, self.slots[0]["plan"].W
         self.frames_in = 0                       # frames committed so far
         self.sets_out = 0                        # results handed out so far
+        self.sets_committed = 0                  # sets whose job AND read-back have been enqueued (set last in commit_frame)
         self.h2d_bytes = self.n * self.h * self.w
         self.d2h_bytes = self.H * self.W
         for slot in self.slots:                  # warm-up: lazy plan scratch is allocated outside any capture
@@ -244,6 +245,7 @@ class BurstStream:
             self.s_d2h.wait_event(slot["ev_cmp"])
             slot["host_out"].copy_(slot["out"], non_blocking=True)
             slot["ev_out"].record(self.s_d2h)
+        self.sets_committed = set_idx + 1                    # only now may a consumer thread wait on ev_out
         return set_idx
 
     def push_frame(self, frame):
@@ -259,7 +261,7 @@ class BurstStream:
     def wait_result(self):
         """Block until the oldest outstanding HR image is on the host.  Returns (set_index, pinned uint8 H x W
         tensor -- valid until `depth` further sets have been committed --, latency in seconds)."""
-        if self.sets_out * self.n + self.n > self.frames_in:
+        if self.sets_out >= self.sets_committed:
             raise RuntimeError("no complete frame set is outstanding")
         slot = self.slots[self.sets_out % self.depth]
         slot["ev_out"].synchronize()

@@ -70,7 +70,7 @@ def main():
     t0 = time.perf_counter()
     th.start()
     for s in range(args.sets):
-        while bs.sets_out * n + n > bs.frames_in:         # the set has not been committed yet
+        while bs.sets_out >= bs.sets_committed:           # the set has not been committed yet
             time.sleep(0.0001)
         idx, img, l = bs.wait_result()
         lat.append(l)
