@@ -127,6 +127,32 @@ __device__ __forceinline__ float pf_fetch(const PrefilterJob& j, int Y, int X) {
     return __ldg(j.src + (size_t)i * j.sw + k);
 }
 
+// one 96-sample line at p[0], p[stride], ...: in-place symmetric exponential filter by warp scan (see k_prefilter2d)
+__device__ __forceinline__ void pf_scan_line(float* p, int stride, int lane) {
+    const float z = kPoleF, z2 = z * z, z3 = z2 * z, z6 = z3 * z3, z12 = z6 * z6;
+    float* q = p + 3 * lane * stride;
+    const float x0 = q[0], x1 = q[stride], x2 = q[2 * stride];
+    // causal: P
+    const float a0 = x0, a1 = fmaf(z, a0, x1), a2 = fmaf(z, a1, x2);
+    float C = a2, t;
+    t = __shfl_up_sync(0xffffffffu, C, 1); if (lane >= 1) C = fmaf(z3, t, C);
+    t = __shfl_up_sync(0xffffffffu, C, 2); if (lane >= 2) C = fmaf(z6, t, C);
+    t = __shfl_up_sync(0xffffffffu, C, 4); if (lane >= 4) C = fmaf(z12, t, C);
+    float cin = __shfl_up_sync(0xffffffffu, C, 1); if (lane == 0) cin = 0.0f;
+    const float P0 = fmaf(z, cin, a0), P1 = fmaf(z2, cin, a1), P2 = fmaf(z3, cin, a2);
+    // anticausal: Q
+    const float b2 = x2, b1 = fmaf(z, b2, x1), b0 = fmaf(z, b1, x0);
+    float Dn = b0;
+    t = __shfl_down_sync(0xffffffffu, Dn, 1); if (lane < 31) Dn = fmaf(z3, t, Dn);
+    t = __shfl_down_sync(0xffffffffu, Dn, 2); if (lane < 30) Dn = fmaf(z6, t, Dn);
+    t = __shfl_down_sync(0xffffffffu, Dn, 4); if (lane < 28) Dn = fmaf(z12, t, Dn);
+    float din = __shfl_down_sync(0xffffffffu, Dn, 1); if (lane == 31) din = 0.0f;
+    const float Q2 = fmaf(z, din, b2), Q1 = fmaf(z2, din, b1), Q0 = fmaf(z3, din, b0);
+    q[0]          = kSqrt3F * (P0 + Q0 - x0);
+    q[stride]     = kSqrt3F * (P1 + Q1 - x1);
+    q[2 * stride] = kSqrt3F * (P2 + Q2 - x2);
+}
+
 struct PrefilterJobs { PrefilterJob job[8]; };
 
 // 256 threads = 8 warps.  Load / store: warp w takes tile rows w, w+8, ..., lanes run along x (coalesced).
@@ -161,44 +187,15 @@ __global__ void __launch_bounds__(256) k_prefilter2d(const __grid_constant__ Pre
         }
     }
     __syncthreads();
-    // axis 0 (down the columns), all 96 columns
-    if (tid < PF_S) {
-        float p = 0.0f;
-        #pragma unroll 8
-        for (int r = 0; r < PF_S; ++r) {
-            p = fmaf(z, p, s[r * PF_P + tid]);
-            s[r * PF_P + tid] = p;
-        }
-        float q = 0.0f;
-        #pragma unroll 8
-        for (int r = PF_S - 1; r >= 0; --r) {
-            float S  = s[r * PF_P + tid];
-            float Sm = r > 0 ? s[(r - 1) * PF_P + tid] : 0.0f;
-            float x  = fmaf(-z, Sm, S);
-            q = fmaf(z, q, x);
-            s[r * PF_P + tid] = kSqrt3F * (S + q - x);
-        }
-    }
+    // Both passes as warp scans: a line of 96 samples = 3 consecutive samples per lane.  The symmetric filter
+    // c = sqrt(3) * (P + Q - x) with P[i] = sum_k z^k x[i-k], Q[i] = sum_k z^k x[i+k]; inside a lane the sums are
+    // serial, across lanes three shuffle steps (carry factors z^3, z^6, z^12) cover 24 samples, i.e. the same
+    // z^16-or-better truncation as the 16-sample warm-up halo.  No serial recursion over the line, no idle threads.
+    // axis 0 (down the columns), all 96 columns: warp w takes columns w, w+8, ...; lane l holds rows 3l..3l+2
+    for (int c = warp; c < PF_S; c += 8) pf_scan_line(s + c, PF_P, lane);
     __syncthreads();
     // axis 1 (along the rows), the 64 interior rows
-    if (tid < PF_T) {
-        float* row = s + (PF_WARM + tid) * PF_P;
-        float p = 0.0f;
-        #pragma unroll 8
-        for (int c = 0; c < PF_S; ++c) {
-            p = fmaf(z, p, row[c]);
-            row[c] = p;
-        }
-        float q = 0.0f;
-        #pragma unroll 8
-        for (int c = PF_S - 1; c >= 0; --c) {
-            float S  = row[c];
-            float Sm = c > 0 ? row[c - 1] : 0.0f;
-            float x  = fmaf(-z, Sm, S);
-            q = fmaf(z, q, x);
-            row[c] = kSqrt3F * (S + q - x);
-        }
-    }
+    for (int r = warp; r < PF_T; r += 8) pf_scan_line(s + (PF_WARM + r) * PF_P, 1, lane);
     __syncthreads();
     const int X0 = tx0 + lane, X1 = tx0 + lane + 32;
     #pragma unroll 4
@@ -334,11 +331,19 @@ __global__ void __launch_bounds__(256) k_resample_tile(const __grid_constant__ R
         const int rmin = bnd[0], cmin = bnd[2];
         const int nr = min(bnd[1] - rmin + 1, ZR_R), nc = min(bnd[3] - cmin + 1, ZR_C);
         // ---- stage ----------------------------------------------------------------------------------------
-        {
+        {   // all of a thread's loads are issued before the first store (the region is at most 38 x 70)
             const float* src = a.coef[k] + (size_t)rmin * a.cpitch[k] + cmin;
-            for (int rr = warp; rr < nr; rr += 8) {
-                const float* row = src + (size_t)rr * a.cpitch[k];
-                for (int cc = lane; cc < nc; cc += 32) R[rr * ZR_P + cc] = __ldg(row + cc);
+            constexpr int NST = (ZR_R * ZR_C + 255) / 256;
+            float v[NST];
+            #pragma unroll
+            for (int q = 0; q < NST; ++q) {
+                const int e = tid + 256 * q, rr = e / ZR_C, cc = e - rr * ZR_C;
+                v[q] = (rr < nr && cc < nc) ? __ldg(src + (size_t)rr * a.cpitch[k] + cc) : 0.0f;
+            }
+            #pragma unroll
+            for (int q = 0; q < NST; ++q) {
+                const int e = tid + 256 * q, rr = e / ZR_C, cc = e - rr * ZR_C;
+                if (rr < ZR_R) R[rr * ZR_P + cc] = v[q];
             }
         }
         __syncthreads();
