@@ -244,7 +244,7 @@ def run_b200_arm(args):
     errs = plan.errors(iters)
 
     # ---- e2e through the host API ------------------------------------------------------------
-    pipe = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="f32", out_dtype="f32")
+    pipe = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="f32", out_dtype="f32", use_graph=True)
     sets = [host_sets[i % ring] for i in range(args.steps)]
     pipe.run([host_sets[i % ring] for i in range(max(args.warmup, 3))])
     barrier()
@@ -256,7 +256,7 @@ def run_b200_arm(args):
     barrier()
     # the same jobs in the reference's file formats: uint8 frames in (load_gray, run_sr.py:73-75), uint8 HR image
     # out (clip + truncation, run_sr.py:303) -- 4x fewer PCIe bytes; reported beside the float32 e2e, not instead of it
-    pipe8 = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="u8", out_dtype="u8")
+    pipe8 = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="u8", out_dtype="u8", use_graph=True)
     sets8 = [torch.from_numpy(rng.integers(0, 256, (n, h, w), dtype=np.uint8)).pin_memory() for _ in range(ring)]
     pipe8.run([sets8[i % ring] for i in range(max(args.warmup, 3))])
     barrier()
@@ -305,7 +305,7 @@ def run_b200_arm(args):
                      "algorithmic_bytes_per_launch": alg_iter, "peak_source": peak_src, "launch_ms": k_ms},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
                 "ms_per_step": e2e_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat),
-                "api": "sr459.driver.FrameSetPipeline.run (pinned f32 frames in, f32 HR image out, 3 jobs in flight)"},
+                "api": "sr459.driver.FrameSetPipeline.run (pinned f32 frames in, f32 HR image out, 3 jobs in flight, one CUDA-graph replay per job)"},
         "e2e_u8": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
                    "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps,
                    "api": "FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): the reference's PNG-side formats, converted on the device"},

@@ -29,9 +29,10 @@ class FrameSetPipeline:
     """
 
     def __init__(self, n_frames, h, w, shifts_yx, kernel, n_iter, factor=2, step=ops.IBP_STEP_SIZE,
-                 depth=3, in_dtype="f32", out_dtype="f32", device=None):
+                 depth=3, in_dtype="f32", out_dtype="f32", device=None, use_graph=False):
         torch = ops._torch()
         self.torch = torch
+        self.use_graph = bool(use_graph)
         if device is not None:
             torch.cuda.set_device(device)
         self.dev = torch.device("cuda", torch.cuda.current_device())
@@ -52,14 +53,42 @@ class FrameSetPipeline:
                 out=torch.empty((self.H, self.W), dtype=torch.uint8, device=self.dev) if out_dtype == "u8" else None,
                 host_out=torch.empty((self.H, self.W), dtype=tout).pin_memory(),
                 ev_in=torch.cuda.Event(), ev_cmp=torch.cuda.Event(), ev_out=torch.cuda.Event(),
-                busy=False, errors=None,
+                busy=False, errors=None, graph=None,
             ))
         self.h2d_bytes = self.n * self.h * self.w * (1 if in_dtype == "u8" else 4)
         self.d2h_bytes = self.H * self.W * (1 if out_dtype == "u8" else 4)
         self._next = 0
+        if self.use_graph:
+            # one captured launch sequence per slot (slot buffers and the plan's scratch are baked in); the
+            # un-captured warm-up run allocates the plan's lazy scratch first
+            with torch.cuda.stream(self.s_cmp):
+                self._compute(self.slots[0])
+            torch.cuda.synchronize()
+            for slot in self.slots:
+                g = torch.cuda.CUDAGraph()
+                with torch.cuda.graph(g, stream=self.s_cmp):
+                    self._compute(slot)
+                slot["graph"] = g
 
     def close(self):
+        self.torch.cuda.synchronize()
+        for slot in self.slots:
+            slot["graph"] = None
         self.plan.close()
+
+    def _compute(self, slot):
+        """(u8 -> f32,) SAA + IBP (, clip + truncation to u8) of one slot on the current stream."""
+        import ctypes as C
+        lib = ops._lib.load()
+        st = C.c_void_p(self.torch.cuda.current_stream().cuda_stream)
+        if self.in_dtype == "u8":
+            ops._lib.check(lib.sr459_u8_to_f32(ops._ptr(slot["raw"]), slot["raw"].numel(), ops._ptr(slot["lr"]), st))
+            frames = slot["lr"]
+        else:
+            frames = slot["raw"]
+        self.plan.saa_ibp([frames[k] for k in range(self.n)], self.n_iter, out=slot["hr"], want_errors=False)
+        if self.out_dtype == "u8":
+            ops._lib.check(lib.sr459_f32_to_u8(ops._ptr(slot["hr"]), slot["hr"].numel(), ops._ptr(slot["out"]), st))
 
     # -- one job ------------------------------------------------------------------------
     def _submit(self, slot, host_frames):
@@ -75,16 +104,10 @@ class FrameSetPipeline:
         with torch.cuda.stream(self.s_cmp):
             self.s_cmp.wait_event(slot["ev_in"])
             self.s_cmp.wait_event(slot["ev_out"])   # previous D2H of this slot finished reading hr/out
-            if self.in_dtype == "u8":
-                ops._lib.check(lib.sr459_u8_to_f32(ops._ptr(slot["raw"]), slot["raw"].numel(), ops._ptr(slot["lr"]),
-                                                   C.c_void_p(self.s_cmp.cuda_stream)))
-                frames = slot["lr"]
+            if slot["graph"] is not None:
+                slot["graph"].replay()
             else:
-                frames = slot["raw"]
-            self.plan.saa_ibp([frames[k] for k in range(self.n)], self.n_iter, out=slot["hr"], want_errors=False)
-            if self.out_dtype == "u8":
-                ops._lib.check(lib.sr459_f32_to_u8(ops._ptr(slot["hr"]), slot["hr"].numel(), ops._ptr(slot["out"]),
-                                                   C.c_void_p(self.s_cmp.cuda_stream)))
+                self._compute(slot)
             slot["ev_cmp"].record(self.s_cmp)
         with torch.cuda.stream(self.s_d2h):
             self.s_d2h.wait_event(slot["ev_cmp"])

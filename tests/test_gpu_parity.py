@@ -609,6 +609,37 @@ def test_burst_stream_matches_oracle(sr, use_graph):
         assert d.max() <= 1 and (d > 0).mean() < 1e-3, f"set {i}: {d.max()} / {(d > 0).mean()}"
 
 
+@pytest.mark.parametrize("use_graph", [False, True])
+@pytest.mark.parametrize("dt", ["f32", "u8"])
+def test_frame_set_pipeline_matches_oracle(sr, dt, use_graph):
+    """Batched driver (config 3): pinned host sets in, results out, slots re-used, optional CUDA-graph replay."""
+    import torch
+    from sr459.driver import FrameSetPipeline, shard_indices
+    rng = np.random.default_rng(56)
+    h, w, K = 40, 64, 4
+    psf = O.make_gaussian_psf()
+    if dt == "u8":
+        sets = [torch.from_numpy(rng.integers(0, 256, (4, h, w), dtype=np.uint8)).pin_memory() for _ in range(5)]
+    else:
+        sets = [torch.from_numpy(rng.uniform(0, 255, (4, h, w)).astype(np.float32)).pin_memory() for _ in range(5)]
+    pipe = FrameSetPipeline(4, h, w, NOMINAL, psf, K, depth=2, in_dtype=dt, out_dtype=dt, use_graph=use_graph)
+    res = pipe.run(sets, keep_results=True)
+    again = pipe.run(sets[:2], keep_results=True)              # the ring is re-usable
+    pipe.close()
+    assert len(res) == 5 and len(again) == 2
+    for i, r in enumerate(res):
+        lrs = [sets[i][k].numpy().astype(np.float64) for k in range(4)]
+        saa = O.shift_and_add_integer(lrs, NOMINAL)
+        ref, _ = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa, n_iter=K)
+        if dt == "u8":
+            d = np.abs(r.numpy().astype(np.int16) - np.clip(ref, 0, 255).astype(np.uint8).astype(np.int16))
+            assert d.max() <= 1 and (d > 0).mean() < 1e-3
+        else:
+            _close(r.numpy(), ref, what=f"pipeline set {i}")
+    assert torch.equal(again[0], res[0]) and torch.equal(again[1], res[1])
+    assert shard_indices(10, 1, 4) == [1, 5, 9]
+
+
 def test_band_plan_refuses_fractional_shifts(sr):
     from sr459.bands import BandPlan
     with pytest.raises(sr.Sr459Error) as ei:
