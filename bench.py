@@ -52,6 +52,27 @@ def log(*a):
     print(*a, file=sys.stderr, flush=True)
 
 
+_REAL_STDOUT = None
+
+
+def guard_stdout():
+    """stdout carries exactly ONE JSON line: anything libraries print there (NCCL's version banner comes from C)
+    is sent to stderr; emit() writes the line to the real stdout."""
+    global _REAL_STDOUT
+    if _REAL_STDOUT is None:
+        sys.stdout.flush()
+        _REAL_STDOUT = os.dup(1)
+        os.dup2(2, 1)
+
+
+def emit(line):
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode()); sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def measured_peak():
     p = os.path.join(ROOT, "MEASURED_PEAKS.json")
     try:
@@ -173,7 +194,7 @@ def run_reference_arm(args):
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     return 0
 
 
@@ -328,7 +349,7 @@ def run_b200_arm(args):
                        "float64 scipy calls identical to the reference's; per-iteration cost extrapolated to the 50-iteration job"),
         }
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     pipe.close()
     pipe8.close()
     plan.close()
@@ -346,6 +367,7 @@ def main():
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c1")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     args = ap.parse_args()
+    guard_stdout()
     if args.impl == "reference":
         return run_reference_arm(args)
     return run_b200_arm(args)
