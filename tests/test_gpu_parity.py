@@ -640,6 +640,27 @@ def test_frame_set_pipeline_matches_oracle(sr, dt, use_graph):
     assert shard_indices(10, 1, 4) == [1, 5, 9]
 
 
+def test_mtf50_of_cuda_output_equals_mtf50_of_reference_output(sr):
+    """Row f3: the slanted-edge MTF50 / MTF10 (analysis.ipynb cells 7-10) of the CUDA SAA+IBP image and of the
+    float64 oracle image agree far inside the measurement's own resolution."""
+    from sr459 import analysis as A
+    rng = np.random.default_rng(77)
+    n = 200
+    yy, xx = np.mgrid[:n, :n].astype(np.float64)
+    d = (xx - n / 2) * np.cos(0.25) + (yy - n / 2) * np.sin(0.25)
+    truth = np.where(np.abs(d) < 9, 35.0, 215.0)
+    psf = O.make_gaussian_psf()
+    lrs = [np.clip(O.forward_model(truth, psf, s, 2) + rng.normal(0, 1, (n // 2, n // 2)), 0, 255) for s in NOMINAL]
+    saa_o = O.shift_and_add(lrs, NOMINAL)
+    hr_o, _ = O.ibp(lrs, NOMINAL, psf, saa_o, n_iter=10)
+    hr, _ = sr.ibp(lrs, NOMINAL, psf, sr.shift_and_add(lrs, NOMINAL), n_iter=10)
+    roi = (slice(20, 180), slice(20, 180))
+    for img_a, img_b in ((hr, hr_o), (sr.shift_and_add(lrs, NOMINAL), saa_o)):
+        a50, a10 = A.mtf50_mtf10(img_a, roi)
+        b50, b10 = A.mtf50_mtf10(img_b, roi)
+        assert abs(a50 - b50) <= 1e-3 * b50 and abs(a10 - b10) <= 1e-3 * b10, (a50, b50, a10, b10)
+
+
 def test_band_plan_refuses_fractional_shifts(sr):
     from sr459.bands import BandPlan
     with pytest.raises(sr.Sr459Error) as ei:
