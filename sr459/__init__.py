@@ -9,7 +9,7 @@ if _root not in _sys.path:
     _sys.path.insert(0, _root)
 _real = "enph459-super-resolution_b200"
 _pkg = _importlib.import_module(_real)
-for _sub in ("_lib", "ops", "build", "driver", "bands", "run_sr", "ingest", "analysis"):
+for _sub in ("_lib", "ops", "build", "driver", "bands", "run_sr", "ingest", "analysis", "calibration"):
     try:
         _m = _importlib.import_module(f"{_real}.{_sub}")
     except ModuleNotFoundError:
