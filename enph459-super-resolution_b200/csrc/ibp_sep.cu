@@ -107,40 +107,48 @@ int sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pi
 }
 
 // ---- lattice sums (once per ibp() call) ----------------------------------------------------------------
+constexpr int LS_ROWS = 8;                             // plane rows per CTA: 8 x n independent loads per thread, one atomic per CTA
 __global__ void __launch_bounds__(256) k_lattice_sums(const __grid_constant__ LatticeArgs a) {
     const int slot = blockIdx.z;
     const int b = blockIdx.x * 256 + threadIdx.x;
-    const int ar = blockIdx.y;                         // plane row; site row index a = a.row0 + ar
-    const int ag = a.row0 + ar;
-    float v = 0.0f;
+    double vd = 0.0;
     if (b < a.w) {
-        float x[kMaxFrames];
-        int m = 0;
-        float s = 0.0f;
-        #pragma unroll
-        for (int f = 0; f < kMaxFrames; ++f) {
-            x[f] = 0.0f;
-            if (f < a.slot_n[slot]) {
-                const int k = a.slot_k[slot][f];
-                const int i = ag + a.slot_oy[slot][f], j = b + a.slot_ox[slot][f];
-                if (i >= a.lr_lo && i < a.lr_hi && i < a.h && j < a.w) {
-                    x[f] = __ldg(a.lr[k] + (size_t)(i - a.lr_lo) * a.w + j);
-                    s += x[f];
-                    m |= 1 << f;
+        #pragma unroll 2
+        for (int rr = 0; rr < LS_ROWS; ++rr) {
+            const int ar = blockIdx.y * LS_ROWS + rr;      // plane row; site row index a = a.row0 + ar
+            if (ar >= a.rows) break;
+            const int ag = a.row0 + ar;
+            float x[kMaxFrames];
+            int m = 0;
+            float s = 0.0f;
+            #pragma unroll
+            for (int f = 0; f < kMaxFrames; ++f) {
+                x[f] = 0.0f;
+                if (f < a.slot_n[slot]) {
+                    const int k = a.slot_k[slot][f];
+                    const int i = ag + a.slot_oy[slot][f], j = b + a.slot_ox[slot][f];
+                    if (i >= a.lr_lo && i < a.lr_hi && i < a.h && j < a.w) {
+                        x[f] = __ldg(a.lr[k] + (size_t)(i - a.lr_lo) * a.w + j);
+                        m |= 1 << f;
+                    }
                 }
             }
-        }
-        a.s1[slot][(size_t)ar * a.pitch + b] = s;
-        const int cnt = __popc(m);
-        if (cnt > 0 && ag >= a.own_a0 && ag < a.own_a1) {
-            const float mu = s / (float)cnt;
             #pragma unroll
-            for (int f = 0; f < kMaxFrames; ++f)
-                if (m & (1 << f)) { const float d = x[f] - mu; v = fmaf(d, d, v); }
+            for (int f = 0; f < kMaxFrames; ++f) s += x[f];      // frame order, as before (absent frames add 0)
+            a.s1[slot][(size_t)ar * a.pitch + b] = s;
+            const int cnt = __popc(m);
+            if (cnt > 0 && ag >= a.own_a0 && ag < a.own_a1) {
+                const float mu = s / (float)cnt;
+                float v = 0.0f;
+                #pragma unroll
+                for (int f = 0; f < kMaxFrames; ++f)
+                    if (m & (1 << f)) { const float d = x[f] - mu; v = fmaf(d, d, v); }
+                vd += (double)v;                               // per-site f32, across sites f64 (as before)
+            }
         }
     }
     __shared__ double red[8];
-    double d = (double)v;
+    double d = vd;
     #pragma unroll
     for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = d;
@@ -156,7 +164,7 @@ __global__ void __launch_bounds__(256) k_lattice_sums(const __grid_constant__ La
 int launch_lattice_sums(const LatticeArgs& a, cudaStream_t st) {
     if (a.nslot <= 0 || a.rows <= 0) return SR459_OK;
     SR_CUDA(cudaMemsetAsync(a.vsum, 0, sizeof(double), st));
-    dim3 grid((a.w + 255) / 256, a.rows, a.nslot);
+    dim3 grid((a.w + 255) / 256, (a.rows + LS_ROWS - 1) / LS_ROWS, a.nslot);
     k_lattice_sums<<<grid, 256, 0, st>>>(a);
     SR_LAUNCH_CHECK("k_lattice_sums");
     return SR459_OK;
