@@ -43,6 +43,7 @@ _SIGNATURES = {
     "sr459_last_error": (C.c_char_p, []),
     "sr459_launch_count": (C.c_uint64, []),
     "sr459_psf_gaussian": (_I, [_I, _D, _PD]),
+    "sr459_fir_bp_axis": (_I, [_I, _I, _D, _PI, C.POINTER(C.c_float)]),
     "sr459_psf_measured": (_I, [_P, _I, _I, _I, _I, _I, _PD, _PI, _PI, _P]),
     "sr459_u8_to_f32": (_I, [_P, _L, _P, _P]),
     "sr459_extract_red": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),

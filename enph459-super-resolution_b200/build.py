@@ -15,7 +15,7 @@ import sys
 HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 LIB = os.path.join(HERE, "libsr459.so")
-SOURCES = ["api.cu", "spline.cu", "conv.cu", "ibp_dense.cu", "ibp_fast.cu", "ibp_sep.cu", "ibp_ws.cu", "ibp_stream.cu", "ibp_lat.cu", "misc.cu"]
+SOURCES = ["api.cu", "spline.cu", "conv.cu", "ibp_dense.cu", "ibp_fast.cu", "ibp_sep.cu", "ibp_ws.cu", "ibp_stream.cu", "ibp_lat.cu", "fir.cu", "misc.cu"]
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",
     "-O3", "-std=c++17", "-lineinfo",

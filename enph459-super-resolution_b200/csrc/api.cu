@@ -90,6 +90,7 @@ struct sr459_plan {
     AxisTap *d_zoom_y = nullptr, *d_zoom_x = nullptr;
     AxisTap *d_saa_ty = nullptr, *d_saa_tx = nullptr;
     AxisTap *d_fwd_ty = nullptr, *d_fwd_tx = nullptr, *d_bwd_ty = nullptr, *d_bwd_tx = nullptr;
+    int *d_fir_iy0 = nullptr, *d_fir_ix0 = nullptr; float *d_fir_wy = nullptr, *d_fir_wx = nullptr; bool fir_ok = false;   // fir.cu
     TapList taps_f, taps_b;
     float psf7[49] = {0};
     bool  separable = false;          // psf7[u][v] == acol[u] * brow[v]
@@ -227,7 +228,7 @@ static void plan_free(sr459_plan* p) {
     cudaSetDevice(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
-                    p->d_partial, p->d_errors, p->d_edge, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
+                    p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
     for (void* q : ptrs) if (q) cudaFree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
@@ -286,6 +287,27 @@ static int plan_generic_tables(sr459_plan* p) {
     SR_TRY(upload_taps_tbl(fx, &p->d_fwd_tx));
     SR_TRY(upload_taps_tbl(by, &p->d_bwd_ty));
     SR_TRY(upload_taps_tbl(bx, &p->d_bwd_tx));
+    // FIR tables of the back-projection (fir.cu): every frame, both axes; refused -> the spline stages stay in use
+    if (f >= 2 && p->H == p->h * f && p->W == p->w * f) {
+        std::vector<int> iy((size_t)p->n * p->H), ix((size_t)p->n * p->W), i1;
+        std::vector<float> wy((size_t)p->n * p->H * kFirTaps), wx((size_t)p->n * p->W * kFirTaps), w1;
+        bool ok = true;
+        for (int k = 0; k < p->n && ok; ++k) {
+            ok = build_fir_bp_axis(p->h, f, -p->shifts[2 * k] * f, i1, w1);
+            if (ok) { std::copy(i1.begin(), i1.end(), iy.begin() + (size_t)k * p->H); std::copy(w1.begin(), w1.end(), wy.begin() + (size_t)k * p->H * kFirTaps); }
+            ok = ok && build_fir_bp_axis(p->w, f, -p->shifts[2 * k + 1] * f, i1, w1);
+            if (ok) { std::copy(i1.begin(), i1.end(), ix.begin() + (size_t)k * p->W); std::copy(w1.begin(), w1.end(), wx.begin() + (size_t)k * p->W * kFirTaps); }
+        }
+        if (ok) {
+            SR_TRY(dev_alloc(&p->d_fir_iy0, iy.size())); SR_TRY(dev_alloc(&p->d_fir_ix0, ix.size()));
+            SR_TRY(dev_alloc(&p->d_fir_wy, wy.size()));  SR_TRY(dev_alloc(&p->d_fir_wx, wx.size()));
+            SR_CUDA(cudaMemcpy(p->d_fir_iy0, iy.data(), iy.size() * sizeof(int), cudaMemcpyHostToDevice));
+            SR_CUDA(cudaMemcpy(p->d_fir_ix0, ix.data(), ix.size() * sizeof(int), cudaMemcpyHostToDevice));
+            SR_CUDA(cudaMemcpy(p->d_fir_wy, wy.data(), wy.size() * sizeof(float), cudaMemcpyHostToDevice));
+            SR_CUDA(cudaMemcpy(p->d_fir_wx, wx.data(), wx.size() * sizeof(float), cudaMemcpyHostToDevice));
+            p->fir_ok = true;
+        }
+    }
     return SR459_OK;
 }
 
@@ -354,6 +376,15 @@ static int iterate_generic(sr459_plan* p, const float* const* lr, const float* c
     e.partial = p->d_partial + (size_t)it * p->per_iter;
     SR_TRY(launch_resample_err(e, st, nullptr));
     // backward: zero-insert + pad + prefilter per frame, evaluate at -s, sum, transposed blur + update
+    if (p->fir_ok && p->path == 0) {                        // the same linear map as ONE table-driven FIR kernel (fir.cu)
+        FirBpArgs fb{};
+        for (int k = 0; k < p->n; ++k) fb.err[k] = p->d_err + k * lpx;
+        fb.n = p->n; fb.h = p->h; fb.w = p->w; fb.H = p->H; fb.W = p->W;
+        fb.iy0 = p->d_fir_iy0; fb.ix0 = p->d_fir_ix0; fb.wy = p->d_fir_wy; fb.wx = p->d_fir_wx; fb.out = p->d_acc;
+        SR_TRY(launch_fir_bp(fb, st));
+        CorrArgs u2{p->d_acc, p->H, p->W, &p->taps_b, nxt, 1, cur, (float)(p->step / p->n), (float)p->lo, (float)p->hi};
+        return launch_corr2d(u2, st);
+    }
     PrefilterJob jobs[kMaxFrames];
     for (int k = 0; k < p->n; ++k)
         jobs[k] = PrefilterJob{p->d_err + k * lpx, p->d_coef_pad + (size_t)k * PH * PW, p->h, p->w, p->H, p->W, PH, PW, SRC_ZI_EDGEPAD, p->factor};
@@ -887,6 +918,15 @@ int sr459_plan_set_path(sr459_plan* plan, int path) {
     if ((path == 2 || path == 3) && !fused_supported(plan)) { set_error("fused integer path not available for this plan"); return SR459_EUNSUPPORTED; }
     if (path == 3 && !(ibp_fast_supported(plan->kh, plan->kw, plan->smax) && plan->W % 4 == 0)) { set_error("fast interior kernel not available for this plan"); return SR459_EUNSUPPORTED; }
     plan->path = path;
+    return SR459_OK;
+}
+
+int sr459_fir_bp_axis(int n_lr, int factor, double shift, int* h_i0, float* h_w) {
+    if (n_lr < 1 || factor < 1 || !h_i0 || !h_w) { set_error("fir_bp_axis: bad arguments"); return SR459_EINVAL; }
+    std::vector<int> i0; std::vector<float> w;
+    if (!build_fir_bp_axis(n_lr, factor, shift, i0, w)) { set_error("fir_bp_axis: axis of %d samples is shorter than %d taps (or the shift is too large)", n_lr, kFirTaps); return SR459_EUNSUPPORTED; }
+    std::copy(i0.begin(), i0.end(), h_i0);
+    std::copy(w.begin(), w.end(), h_w);
     return SR459_OK;
 }
 

@@ -1,0 +1,183 @@
+// fir.cu -- back-projection with FRACTIONAL shifts as one table-driven FIR kernel.
+//
+// The reference's back_project (mono_cal_target/run_sr.py:168-178) zero-inserts the LR residual onto the HR grid and
+// calls scipy.ndimage.shift(up, (-2dy, -2dx), order=3, mode='nearest'): edge-pad by 12, cubic-B-spline prefilter
+// (an all-pole IIR filter), 4-tap spline evaluation at o + s + 12.  Every step is linear and, per axis, the chain
+// is  out[o] = sum_j w_j(o) * sum_d h[d] * up[clamp(p_j(o) - d - 12)]  with h[d] = sqrt(3) z^|d| (the prefilter's impulse
+// response, z = sqrt(3) - 2; |d| <= 16 keeps everything above 7e-10) and up[Y] = err[Y/f] on multiples of the factor f,
+// zero elsewhere.  Folding the zero pattern, the clamps of the edge padding and the spline weights together gives,
+// for every HR output index o, at most 20 taps on consecutive LR samples:  out[o] = sum_a M[o][a] * err[i0[o] + a].
+// The tables M (float, built in double on the host) carry ALL boundary rules; the kernel is a plain separable
+// 20 x 20-tap gather per frame, accumulated over the frames -- no full-resolution prefilter (4 frames x 2 passes over
+// (H+24) x (W+24)) and no 64-tap coefficient gather (k_prefilter2d + k_resample_sum of the generic path).
+#include "internal.h"
+#include <math.h>
+#include <algorithm>
+
+namespace sr459 {
+
+static inline void fir_cubic_w(double t, double w[4]) {     // scipy's cubic B-spline weights at fraction t
+    const double u = 1.0 - t;
+    w[0] = u * u * u / 6.0;
+    w[1] = (t * t * (t - 2.0) * 3.0 + 4.0) / 6.0;
+    w[2] = (u * u * (u - 2.0) * 3.0 + 4.0) / 6.0;
+    w[3] = 1.0 - w[0] - w[1] - w[2];
+}
+
+// One axis: HR length N = f * n_lr, shift s (HR pixels, the argument scipy.ndimage.shift receives).
+// i0[o] (first LR tap) and w[o * kFirTaps + a].  Returns false if the axis is too short for the fixed tap count.
+bool build_fir_bp_axis(int n_lr, int f, double s, std::vector<int>& i0, std::vector<float>& w) {
+    const int N = n_lr * f, NP = N + 2 * kPad, R = 16;
+    if (n_lr < kFirTaps) return false;
+    const double z = sqrt(3.0) - 2.0;
+    double h[2 * 16 + 1];
+    for (int d = -R; d <= R; ++d) h[d + R] = sqrt(3.0) * pow(z, abs(d));
+    i0.assign(N, 0);
+    w.assign((size_t)N * kFirTaps, 0.0f);
+    std::vector<double> acc(kFirTaps);
+    for (int o = 0; o < N; ++o) {
+        double x = (double)o - s + (double)kPad;
+        x = std::min(std::max(x, 0.0), (double)(NP - 1));           // mode='nearest' coordinate clip
+        const double fl = floor(x);
+        double cw[4];
+        fir_cubic_w(x - fl, cw);
+        const long long base = (long long)fl - 1;
+        // first LR sample any tap can touch (before clamping), then clamp the window into the array
+        long long ylo = base - R - kPad;
+        long long first = ylo <= 0 ? 0 : (ylo + f - 1) / f;
+        first = std::min<long long>(std::max<long long>(first, 0), n_lr - kFirTaps);
+        std::fill(acc.begin(), acc.end(), 0.0);
+        for (int j = 0; j < 4; ++j) {
+            const long long p = std::min<long long>(std::max<long long>(base + j, 0), NP - 1);   // tap index clamp
+            for (int d = -R; d <= R; ++d) {
+                long long Y = p - d - kPad;                           // index into the unpadded HR array
+                Y = std::min<long long>(std::max<long long>(Y, 0), N - 1);     // edge padding + 'nearest' extension
+                if (Y % f) continue;                                  // zero-inserted sample
+                const long long i = Y / f;
+                const long long a = i - first;
+                if (a < 0 || a >= kFirTaps) return false;             // cannot happen for |s| << 12; refuse rather than drop
+                acc[(size_t)a] += cw[j] * h[d + R];
+            }
+        }
+        i0[o] = (int)first;
+        for (int a = 0; a < kFirTaps; ++a) w[(size_t)o * kFirTaps + a] = (float)acc[(size_t)a];
+    }
+    return true;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// kernel: out[Y][X] = sum_k sum_a My_k[Y][a] * sum_b Mx_k[X][b] * err_k[iy0_k[Y] + a][ix0_k[X] + b]
+// One CTA (256 threads) owns a 32 x 128 output tile; per frame: stage the LR region, x pass into T, y pass into
+// 4 x 4 register accumulators per thread.
+// ---------------------------------------------------------------------------------------------------------------
+constexpr int FB_TH = 32, FB_TW = 128;
+constexpr int FB_RR = FB_TH / 2 + kFirTaps + 2;     // 38 staged LR rows   (factor >= 2)
+constexpr int FB_RC = FB_TW / 2 + kFirTaps + 4;     // 88 staged LR columns
+constexpr int FB_RP = FB_RC + 1;
+
+__global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBpArgs a) {
+    __shared__ float R[FB_RR * FB_RP];
+    __shared__ __align__(16) float T[FB_RR * FB_TW];
+    __shared__ float wy[FB_TH * kFirTaps];
+    __shared__ int iy[FB_TH];
+    __shared__ int bnd[4];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y0 = blockIdx.y * FB_TH, x0 = blockIdx.x * FB_TW;
+    const int th = min(FB_TH, a.H - y0), tw = min(FB_TW, a.W - x0);
+    float acc[4][4];
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; }
+
+    for (int k = 0; k < a.n; ++k) {
+        const int* iy0 = a.iy0 + (size_t)k * a.H + y0;
+        const int* ix0 = a.ix0 + (size_t)k * a.W + x0;
+        const float* wyk = a.wy + ((size_t)k * a.H + y0) * kFirTaps;
+        const float* wxk = a.wx + ((size_t)k * a.W + x0) * kFirTaps;
+        __syncthreads();                                   // previous frame's passes are done with R / T / wy
+        if (tid < 64) {                                    // bounds of the LR region (i0 is monotone, but stay general)
+            const int* src = tid < 32 ? iy0 : ix0;
+            const int cnt = tid < 32 ? th : tw;
+            int lo = 0x7fffffff, hi = -1;
+            for (int q = lane; q < cnt; q += 32) { const int v = __ldg(src + q); lo = min(lo, v); hi = max(hi, v); }
+            #pragma unroll
+            for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+            if (lane == 0) { bnd[(tid >> 5) * 2] = lo; bnd[(tid >> 5) * 2 + 1] = hi; }
+        }
+        for (int q = tid; q < th * kFirTaps; q += 256) wy[q] = __ldg(wyk + q);
+        if (tid < th) iy[tid] = __ldg(iy0 + tid);
+        __syncthreads();
+        const int rmin = bnd[0], cmin = bnd[2];
+        const int nr = min(bnd[1] - rmin + kFirTaps, FB_RR), nc = min(bnd[3] - cmin + kFirTaps, FB_RC);
+        {   // stage: all loads of a thread first
+            constexpr int NST = (FB_RR * FB_RC + 255) / 256;
+            float v[NST];
+            const float* src = a.err[k] + (size_t)rmin * a.w + cmin;
+            #pragma unroll
+            for (int q = 0; q < NST; ++q) {
+                const int e = tid + 256 * q, rr = e / FB_RC, cc = e - rr * FB_RC;
+                v[q] = (rr < nr && cc < nc && rmin + rr < a.h && cmin + cc < a.w) ? __ldg(src + (size_t)rr * a.w + cc) : 0.f;
+            }
+            #pragma unroll
+            for (int q = 0; q < NST; ++q) {
+                const int e = tid + 256 * q, rr = e / FB_RC, cc = e - rr * FB_RC;
+                if (rr < FB_RR) R[rr * FB_RP + cc] = v[q];
+            }
+        }
+        __syncthreads();
+        {   // x pass: T[rr][x], one column per thread, two row phases
+            const int x = tid & (FB_TW - 1), half = tid >> 7;
+            if (x < tw) {
+                float wreg[kFirTaps];
+                #pragma unroll
+                for (int b = 0; b < kFirTaps; ++b) wreg[b] = __ldg(wxk + (size_t)x * kFirTaps + b);
+                const int off = __ldg(ix0 + x) - cmin;
+                for (int rr = half; rr < nr; rr += 2) {
+                    const float* r = R + rr * FB_RP + off;
+                    float s = 0.f;
+                    #pragma unroll
+                    for (int b = 0; b < kFirTaps; ++b) s = fmaf(wreg[b], r[b], s);
+                    T[rr * FB_TW + x] = s;
+                }
+            } else {
+                for (int rr = half; rr < nr; rr += 2) T[rr * FB_TW + x] = 0.f;
+            }
+        }
+        __syncthreads();
+        {   // y pass: rows warp, warp+8, warp+16, warp+24; columns 4*lane .. 4*lane+3
+            const float4* tp = reinterpret_cast<const float4*>(T) + lane;
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                const int y = warp + 8 * i;
+                if (y < th) {
+                    const float* wrow = wy + y * kFirTaps;
+                    const float4* t0 = tp + (iy[y] - rmin) * (FB_TW / 4);
+                    #pragma unroll
+                    for (int q = 0; q < kFirTaps; ++q) {
+                        const float4 v = t0[q * (FB_TW / 4)];
+                        const float wq = wrow[q];
+                        acc[i][0] = fmaf(wq, v.x, acc[i][0]); acc[i][1] = fmaf(wq, v.y, acc[i][1]);
+                        acc[i][2] = fmaf(wq, v.z, acc[i][2]); acc[i][3] = fmaf(wq, v.w, acc[i][3]);
+                    }
+                }
+            }
+        }
+    }
+    const int gx = x0 + 4 * lane;
+    #pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const int gy = y0 + warp + 8 * i;
+        if (gy >= a.H || gx >= a.W) continue;
+        float* d = a.out + (size_t)gy * a.W + gx;
+        if (gx + 3 < a.W && (a.W & 3) == 0) *reinterpret_cast<float4*>(d) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
+        else for (int q = 0; q < 4 && gx + q < a.W; ++q) d[q] = acc[i][q];
+    }
+}
+
+int launch_fir_bp(const FirBpArgs& a, cudaStream_t st) {
+    dim3 grid((a.W + FB_TW - 1) / FB_TW, (a.H + FB_TH - 1) / FB_TH);
+    k_fir_bp<<<grid, 256, 0, st>>>(a);
+    SR_LAUNCH_CHECK("k_fir_bp");
+    return SR459_OK;
+}
+
+}  // namespace sr459

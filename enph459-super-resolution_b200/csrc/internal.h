@@ -104,6 +104,19 @@ struct ResampleErrArgs {
 };
 int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_out);
 
+// ---- FIR form of the fractional-shift back-projection (fir.cu) ---------------------
+constexpr int kFirTaps = 20;            // LR taps per axis: (2*16 + 4) HR samples / factor 2, rounded up
+// one axis of  shift(zero_insert(err, f), s, order=3, mode='nearest'): out[o] = sum_a w[o][a] * err[i0[o] + a]
+bool build_fir_bp_axis(int n_lr, int f, double s, std::vector<int>& i0, std::vector<float>& w);
+struct FirBpArgs {
+    const float* err[8];                // LR residuals, h x w, pitch w
+    int n, h, w, H, W;
+    const int* iy0; const int* ix0;     // [k * H + Y], [k * W + X]
+    const float* wy; const float* wx;   // [(k * H + Y) * kFirTaps + a], [(k * W + X) * kFirTaps + b]
+    float* out;                         // sum over frames, H x W
+};
+int launch_fir_bp(const FirBpArgs& a, cudaStream_t st);
+
 // ---- correlation / convolution ------------------------------------------------
 // out[y,x] = sum_t w[t] * in0[y+dy[t], x+dx[t]]   (zero outside), taps with w==0 dropped
 struct TapList {

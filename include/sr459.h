@@ -99,6 +99,11 @@ int sr459_blur(const float* d_img, int H, int W, const double* h_psf, int kh, in
 /* scipy.ndimage.zoom(a, factor, order=3), defaults      call sites run_sr.py:185, :279.
  * out is round(h*factor) x round(w*factor).                                   */
 int sr459_zoom(const float* d_in, int h, int w, int factor, float* d_out, void* stream);
+/* One axis of back_project's  shift(zero_insert(err, factor), s, order=3, mode='nearest')  (run_sr.py:170-176) as a
+ * banded matrix: out[o] = sum_{a<20} h_w[o*20 + a] * err[h_i0[o] + a], o = 0 .. factor*n_lr-1; `shift` is the HR
+ * shift scipy receives (-factor*d).  Host only (no device work): the tables the FIR back-projection kernel uses.
+ * Returns SR459_EUNSUPPORTED when n_lr < 20.                                                                  */
+int sr459_fir_bp_axis(int n_lr, int factor, double shift, int* h_i0, float* h_w);
 /* scipy.ndimage.shift(a, (sy,sx), order=3, mode='nearest')  call sites :163,:176,:186 */
 int sr459_shift(const float* d_in, int H, int W, double sy, double sx, float* d_out, void* stream);
 /* forward_model(hr, kernel, shift_yx, factor)           run_sr.py:161-165.

@@ -143,3 +143,25 @@ def test_run_sr_cli_session_discovery(tmp_path):
     with pytest.raises(FileNotFoundError):
         run_sr.find_sessions("rgb_barcodes", str(tmp_path / "empty"))
     assert run_sr.EXPERIMENTS["rgb_cal_target"][0] == 50 and run_sr.EXPERIMENTS["mono_barcodes"][0] == 80
+
+
+def test_fir_back_projection_tables_match_scipy_shift_of_zero_inserted_data(lib):
+    """sr459_fir_bp_axis (host only): the banded matrix of one axis of back_project's
+    shift(zero_insert(err), s, order=3, mode='nearest') -- run_sr.py:170-176 -- against the oracle's restatement of
+    scipy.ndimage.shift.  float32 tables: 1e-5 on +-100 data."""
+    rng = np.random.default_rng(1)
+    for n_lr, s in [(40, 0.9445), (40, -0.8677), (33, 0.37), (64, -1.0), (25, 1.9), (48, 0.0), (30, -2.6), (20, 0.5)]:
+        N = 2 * n_lr
+        i0 = np.zeros(N, dtype=np.int32)
+        w = np.zeros(N * 20, dtype=np.float32)
+        rc = lib.sr459_fir_bp_axis(n_lr, 2, float(s), i0.ctypes.data_as(C.POINTER(C.c_int)), w.ctypes.data_as(C.POINTER(C.c_float)))
+        assert rc == 0
+        assert i0.min() >= 0 and i0.max() + 20 <= n_lr and np.all(np.diff(i0) >= 0)
+        w = w.reshape(N, 20).astype(np.float64)
+        err = rng.uniform(-100, 100, (n_lr, 5))
+        up = np.zeros((N, 10)); up[::2, ::2] = err
+        ref = O.ndi_shift_cubic_nearest(up, (s, 0.0))[:, ::2]
+        got = np.stack([(w[o][:, None] * err[i0[o]:i0[o] + 20]).sum(axis=0) for o in range(N)])
+        assert np.abs(got - ref).max() < 1e-4, (n_lr, s, np.abs(got - ref).max())
+    small = np.zeros(20, dtype=np.int32)
+    assert lib.sr459_fir_bp_axis(10, 2, 0.5, small.ctypes.data_as(C.POINTER(C.c_int)), w.ctypes.data_as(C.POINTER(C.c_float))) == -4
