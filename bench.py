@@ -228,12 +228,21 @@ def run_b200_arm(args):
     plan = sr459.Plan(n, h, w, NOMINAL, psf)
     hr = torch.empty((H, W), dtype=torch.float32, device="cuda")
 
-    def job(i, ev=None):
+    def job_eager(i):
         frames = [dev_sets[i % ring][k] for k in range(n)]
-        if ev: ev[0].record()
         plan.saa(frames, out=hr)
-        if ev: ev[1].record()
         plan.ibp_(frames, hr, iters, want_errors=False)
+
+    # One captured launch sequence per stage and ring slot (CUDA graphs: the 55 launches of a job replay without
+    # host launch gaps); the stage events are recorded between the replays, on the same stream.
+    graphs = []
+
+    def job(i, ev=None):
+        g_saa, g_ibp = graphs[i % ring]
+        if ev: ev[0].record()
+        g_saa.replay()
+        if ev: ev[1].record()
+        g_ibp.replay()
         if ev: ev[2].record()
 
     def barrier():
@@ -241,6 +250,20 @@ def run_b200_arm(args):
             dist.barrier()
         torch.cuda.synchronize()
 
+    job_eager(0)                                     # lazy plan scratch is allocated outside any capture
+    torch.cuda.synchronize()
+    cap = torch.cuda.Stream()
+    launches_per_job = 0
+    for i in range(ring):
+        frames = [dev_sets[i][k] for k in range(n)]
+        c0 = lib.sr459_launch_count()
+        g_saa, g_ibp = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g_saa, stream=cap):
+            plan.saa(frames, out=hr)
+        with torch.cuda.graph(g_ibp, stream=cap):
+            plan.ibp_(frames, hr, iters, want_errors=False)
+        graphs.append((g_saa, g_ibp))
+        launches_per_job = lib.sr459_launch_count() - c0      # kernels captured = kernels every replay launches
     for i in range(args.warmup):
         job(i)
     barrier()
@@ -252,13 +275,12 @@ def run_b200_arm(args):
     evs = [[torch.cuda.Event(enable_timing=True) for _ in range(3)] for _ in range(args.steps)]
     start, end = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
-    launches0 = lib.sr459_launch_count()
     start.record()
     for i in range(args.steps):
         job(args.warmup + i, evs[i])
     end.record()
     barrier()
-    launches = lib.sr459_launch_count() - launches0
+    launches = launches_per_job * args.steps
     total_ms = start.elapsed_time(end)
     saa_ms = sum(e[0].elapsed_time(e[1]) for e in evs) / args.steps
     ibp_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
@@ -314,7 +336,7 @@ def run_b200_arm(args):
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": {"workload": f"config1: {n}x{h}x{w} mono frames -> {H}x{W}, Gaussian 7x7 PSF, nominal +-0.5 px shifts, "
-                               f"SAA + {iters} IBP iterations per step; one independent frame set per step per GPU",
+                               f"SAA + {iters} IBP iterations per step; one independent frame set per step per GPU; each stage replayed as a CUDA graph",
                    "n_frames": n, "lr_shape": [h, w], "hr_shape": [H, W], "ibp_iterations": iters, "psf": "gaussian7",
                    "cache": f"ring of {ring} distinct frame sets ({ring * n * h * w * 4 >> 20} MiB LR) + {3 * H * W * 4 >> 20} MiB HR "
                             "working set per job, larger than the 126 MB L2; no explicit flush",
@@ -323,7 +345,11 @@ def run_b200_arm(args):
         "job_hbm_frac": alg_job / (total_ms / args.steps * 1e-3) / 1e9 / peak,
         "roofline": {"bound": "hbm", "kernel": "k_ibp_stream (fused IBP iteration: register-streaming warps, TMA row ring; rank-1 PSF, integer HR shifts)",
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                     "algorithmic_bytes_per_launch": alg_iter, "peak_source": peak_src, "launch_ms": k_ms},
+                     "algorithmic_bytes_per_launch": alg_iter, "peak_source": peak_src, "launch_ms": k_ms,
+                     "dram_achieved": (traffic / (k_ms * 1e-3) / 1e9) if traffic else None,
+                     "note": "frac is algorithmic bytes over the measured DRAM copy peak; it can exceed 1 because the hr ping-pong "
+                             "pair (96 MiB) largely stays in the 126 MB L2: ncu counts `traffic` DRAM bytes per launch (cold L2), "
+                             "dram_achieved = traffic / launch time"},
         "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
                 "ms_per_step": e2e_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat),
                 "api": "sr459.driver.FrameSetPipeline.run (pinned f32 frames in, f32 HR image out, 3 jobs in flight, one CUDA-graph replay per job)"},
