@@ -10,8 +10,11 @@ iterations, on synthetic S1-noise frames (np.random.default_rng(459), SURVEY.md 
   value    whole-job throughput with the LR frames already resident in HBM, CUDA-event timed,
            max over ranks; a ring of 4 distinct frame sets (200 MB of LR data + 150 MB of HR
            working set per job > the 126 MB L2) is cycled so no step finds its inputs cached.
-  e2e      the same jobs through the public host API (FrameSetPipeline): pinned host float32
-           frames -> H2D -> SAA+IBP -> D2H of the float32 HR image, copies inside the timed region.
+  e2e      the same jobs through the public host API (FrameSetPipeline) in the formats run_sr.py moves: pinned host
+           uint8 frames (what load_gray reads, run_sr.py:73-75) -> H2D -> u8->f32, SAA+IBP, clip + truncation ->
+           D2H of the uint8 HR image (what run_sr.py:303 writes), copies inside the timed region.
+  e2e_f32  the same with float32 frames in and the float32 HR image out (4x the PCIe bytes: 100 MB per job, which
+           saturates the host side beyond 2 GPUs; reported beside e2e, not instead of it).
   roofline the fused IBP-iteration kernel: algorithmic bytes (8+n)*H*W per launch divided by its
            mean duration, measured live with CUDA events around the IBP loop of every timed step.
   cpu_baseline  the reference's CPU path (oracle/scipy_port.py: the same scipy calls the reference
@@ -297,8 +300,7 @@ def run_b200_arm(args):
     e2e_s = time.perf_counter() - t0
     lat = pipe.run_latency(sets[: min(5, len(sets))])
     barrier()
-    # the same jobs in the reference's file formats: uint8 frames in (load_gray, run_sr.py:73-75), uint8 HR image
-    # out (clip + truncation, run_sr.py:303) -- 4x fewer PCIe bytes; reported beside the float32 e2e, not instead of it
+    # the headline e2e: the same jobs in run_sr.py's file formats, uint8 frames in (load_gray, :73-75), uint8 HR image out (:303)
     pipe8 = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="u8", out_dtype="u8", use_graph=True)
     sets8 = [torch.from_numpy(rng.integers(0, 256, (n, h, w), dtype=np.uint8)).pin_memory() for _ in range(ring)]
     pipe8.run([sets8[i % ring] for i in range(max(args.warmup, 3))])
@@ -307,6 +309,7 @@ def run_b200_arm(args):
     pipe8.run([sets8[i % ring] for i in range(args.steps)])
     torch.cuda.synchronize()
     e2e8_s = time.perf_counter() - t0
+    lat8 = pipe8.run_latency([sets8[i % ring] for i in range(min(5, args.steps))])
     barrier()
     clocks = sampler.stop() if rank == 0 else None
 
@@ -350,12 +353,14 @@ def run_b200_arm(args):
                      "note": "frac is algorithmic bytes over the measured DRAM copy peak; it can exceed 1 because the hr ping-pong "
                              "pair (96 MiB) largely stays in the 126 MB L2: ncu counts `traffic` DRAM bytes per launch (cold L2), "
                              "dram_achieved = traffic / launch time"},
-        "e2e": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-                "ms_per_step": e2e_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat),
-                "api": "sr459.driver.FrameSetPipeline.run (pinned f32 frames in, f32 HR image out, 3 jobs in flight, one CUDA-graph replay per job)"},
-        "e2e_u8": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
-                   "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps,
-                   "api": "FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): the reference's PNG-side formats, converted on the device"},
+        "e2e": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
+                "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat8),
+                "api": "sr459.driver.FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): run_sr.py's own I/O formats -- pinned uint8 frames in "
+                       "(load_gray, :73-75), uint8 HR image out (clip + truncation, :303), conversions on the device; 3 jobs in flight, "
+                       "one CUDA-graph replay per job"},
+        "e2e_f32": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
+                    "ms_per_step": e2e_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat),
+                    "api": "the same pipeline with pinned float32 frames in and the float32 HR image out (100 MB of PCIe traffic per job)"},
         "gpu_launches": int(launches),
         "final_mse": errs[-1],
         "clocks": clocks,

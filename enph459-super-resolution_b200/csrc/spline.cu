@@ -288,11 +288,69 @@ constexpr int ZT_H = 64, ZT_W = 128;
 constexpr int ZR_R = ZT_H / 2 + 6, ZR_C = ZT_W / 2 + 6;     // staged coefficient region (rows x cols)
 constexpr int ZR_P = ZR_C + 1;
 
-__global__ void __launch_bounds__(256) k_resample_tile(const __grid_constant__ ResampleSumArgs a) {
+// Per-frame table bounds of the tile: warp 0 the rows (also copies the row taps to shared memory), warp 1 the columns.
+__device__ __forceinline__ void zt_bounds(const AxisTap* ty, const AxisTap* tx, int th, int tw, AxisTap* sty, int* bnd,
+                                          int warp, int lane) {
+    if (warp == 0) {
+        int lo = 0x7fffffff, hi = -1;
+        for (int y = lane; y < th; y += 32) {
+            const AxisTap t = load_tap(ty + y);
+            sty[y] = t;
+            lo = min(lo, min(min(t.idx[0], t.idx[1]), min(t.idx[2], t.idx[3])));
+            hi = max(hi, max(max(t.idx[0], t.idx[1]), max(t.idx[2], t.idx[3])));
+        }
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+        if (lane == 0) { bnd[0] = lo; bnd[1] = hi; }
+    } else if (warp == 1) {
+        int lo = 0x7fffffff, hi = -1;
+        for (int x = lane; x < tw; x += 32) {
+            const int4 i4 = __ldg(reinterpret_cast<const int4*>(tx + x));
+            lo = min(lo, min(min(i4.x, i4.y), min(i4.z, i4.w)));
+            hi = max(hi, max(max(i4.x, i4.y), max(i4.z, i4.w)));
+        }
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
+        if (lane == 0) { bnd[2] = lo; bnd[3] = hi; }
+    }
+}
+
+constexpr int ZT_NSR = (ZR_R + 7) / 8;          // staged rows per warp (warp w: rows w, w+8, ...)
+constexpr int ZT_NSC = (ZR_C + 31) / 32;        // column chunks per lane (lane, lane+32, ...)
+
+// all of a thread's loads of one frame's coefficient region (at most 38 x 70), issued back to back into registers
+__device__ __forceinline__ void zt_fetch(float (&v)[ZT_NSR][ZT_NSC], const float* coef, int pitch, int rmin, int cmin, int nr, int nc,
+                                         int warp, int lane) {
+    const float* src = coef + (size_t)(rmin + warp) * pitch + cmin + lane;
+    #pragma unroll
+    for (int i = 0; i < ZT_NSR; ++i) {
+        const bool rok = warp + 8 * i < nr;
+        #pragma unroll
+        for (int c = 0; c < ZT_NSC; ++c)
+            v[i][c] = (rok && lane + 32 * c < nc) ? __ldg(src + 32 * c) : 0.0f;
+        src += (size_t)8 * pitch;
+    }
+}
+__device__ __forceinline__ void zt_stage(float* R, const float (&v)[ZT_NSR][ZT_NSC], int warp, int lane) {
+    float* d = R + warp * ZR_P + lane;
+    #pragma unroll
+    for (int i = 0; i < ZT_NSR; ++i) {
+        if (warp + 8 * i < ZR_R) {
+            #pragma unroll
+            for (int c = 0; c < ZT_NSC; ++c)
+                if (lane + 32 * c < ZR_C) d[32 * c] = v[i][c];
+        }
+        d += 8 * ZR_P;
+    }
+}
+
+// Software pipeline over the frames: while frame k runs its x and y passes out of shared memory, the table bounds of
+// frame k+1 are reduced (warps 0/1, double-buffered) and its coefficient region is already in flight into registers.
+__global__ void __launch_bounds__(256, 3) k_resample_tile(const __grid_constant__ ResampleSumArgs a) {
     __shared__ float R[ZR_R * ZR_P];            // staged coefficients
     __shared__ __align__(16) float T[ZR_R * ZT_W];   // x-passed rows
-    __shared__ __align__(16) AxisTap sty[ZT_H];
-    __shared__ int bnd[4];                      // rmin, rmax, cmin, cmax
+    __shared__ __align__(16) AxisTap sty[2][ZT_H];
+    __shared__ int bnd[2][4];                   // rmin, rmax, cmin, cmax
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y0 = blockIdx.y * ZT_H, x0 = blockIdx.x * ZT_W;
     const int th = min(ZT_H, a.Hout - y0), tw = min(ZT_W, a.Wout - x0);
@@ -301,80 +359,58 @@ __global__ void __launch_bounds__(256) k_resample_tile(const __grid_constant__ R
     #pragma unroll
     for (int i = 0; i < 8; ++i) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.0f; }
 
+    float v[ZT_NSR][ZT_NSC];
+    zt_bounds(a.ty + y0, a.tx + x0, th, tw, sty[0], bnd[0], warp, lane);
+    __syncthreads();
+    int rmin = bnd[0][0], cmin = bnd[0][2];
+    int nr = min(bnd[0][1] - rmin + 1, ZR_R), nc = min(bnd[0][3] - cmin + 1, ZR_C);
+    zt_fetch(v, a.coef[0], a.cpitch[0], rmin, cmin, nr, nc, warp, lane);
+
     for (int k = 0; k < a.n; ++k) {
-        const AxisTap* ty = a.ty + (size_t)k * a.Hout + y0;
+        const int cur = k & 1, nxt = cur ^ 1;
         const AxisTap* tx = a.tx + (size_t)k * a.Wout + x0;
-        // ---- bounds of the coefficient region, table rows of the tile -> shared memory -------------------
-        if (warp == 0) {
-            int lo = 0x7fffffff, hi = -1;
-            for (int y = lane; y < th; y += 32) {
-                const AxisTap t = load_tap(ty + y);
-                sty[y] = t;
-                lo = min(lo, min(min(t.idx[0], t.idx[1]), min(t.idx[2], t.idx[3])));
-                hi = max(hi, max(max(t.idx[0], t.idx[1]), max(t.idx[2], t.idx[3])));
-            }
-            #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
-            if (lane == 0) { bnd[0] = lo; bnd[1] = hi; }
-        } else if (warp == 1) {
-            int lo = 0x7fffffff, hi = -1;
-            for (int x = lane; x < tw; x += 32) {
-                const int4 i4 = __ldg(reinterpret_cast<const int4*>(tx + x));
-                lo = min(lo, min(min(i4.x, i4.y), min(i4.z, i4.w)));
-                hi = max(hi, max(max(i4.x, i4.y), max(i4.z, i4.w)));
-            }
-            #pragma unroll
-            for (int o = 16; o > 0; o >>= 1) { lo = min(lo, __shfl_xor_sync(0xffffffffu, lo, o)); hi = max(hi, __shfl_xor_sync(0xffffffffu, hi, o)); }
-            if (lane == 0) { bnd[2] = lo; bnd[3] = hi; }
-        }
-        __syncthreads();                          // also: the previous frame's y pass is done with T
-        const int rmin = bnd[0], cmin = bnd[2];
-        const int nr = min(bnd[1] - rmin + 1, ZR_R), nc = min(bnd[3] - cmin + 1, ZR_C);
-        // ---- stage ----------------------------------------------------------------------------------------
-        {   // all of a thread's loads are issued before the first store (the region is at most 38 x 70)
-            const float* src = a.coef[k] + (size_t)rmin * a.cpitch[k] + cmin;
-            constexpr int NST = (ZR_R * ZR_C + 255) / 256;
-            float v[NST];
-            #pragma unroll
-            for (int q = 0; q < NST; ++q) {
-                const int e = tid + 256 * q, rr = e / ZR_C, cc = e - rr * ZR_C;
-                v[q] = (rr < nr && cc < nc) ? __ldg(src + (size_t)rr * a.cpitch[k] + cc) : 0.0f;
-            }
-            #pragma unroll
-            for (int q = 0; q < NST; ++q) {
-                const int e = tid + 256 * q, rr = e / ZR_C, cc = e - rr * ZR_C;
-                if (rr < ZR_R) R[rr * ZR_P + cc] = v[q];
-            }
-        }
-        __syncthreads();
+        // ---- stage (the x pass of frame k-1 finished before its second barrier) ----------------------------
+        zt_stage(R, v, warp, lane);
+        __syncthreads();                          // also: frame k-1's y pass is done with T, sty[nxt] and bnd[nxt]
+        if (k + 1 < a.n)      // tables of the next frame; read after the next barrier
+            zt_bounds(a.ty + (size_t)(k + 1) * a.Hout + y0, a.tx + (size_t)(k + 1) * a.Wout + x0, th, tw, sty[nxt], bnd[nxt], warp, lane);
         // ---- x pass: T[rr][x] -----------------------------------------------------------------------------
         {
             const int x = tid & (ZT_W - 1), half = tid >> 7;
             if (x < tw) {
                 const AxisTap t = load_tap(tx + x);
-                const int o0 = t.idx[0] - cmin, o1 = t.idx[1] - cmin, o2 = t.idx[2] - cmin, o3 = t.idx[3] - cmin;
-                #pragma unroll 2
-                for (int rr = half; rr < nr; rr += 2) {
-                    const float* r = R + rr * ZR_P;
-                    T[rr * ZT_W + x] = fmaf(t.w[3], r[o3], fmaf(t.w[2], r[o2], fmaf(t.w[1], r[o1], t.w[0] * r[o0])));
+                // fully unrolled over the (at most 19) rows of this half: every address is a register plus an immediate
+                const float* r0 = R + half * ZR_P + (t.idx[0] - cmin), * r1 = R + half * ZR_P + (t.idx[1] - cmin);
+                const float* r2 = R + half * ZR_P + (t.idx[2] - cmin), * r3 = R + half * ZR_P + (t.idx[3] - cmin);
+                float* tp = T + half * ZT_W + x;
+                #pragma unroll
+                for (int i = 0; i < ZR_R / 2; ++i) {
+                    // rows >= nr of R hold staged zeros and the matching rows of T are never read: no guard
+                    tp[2 * i * ZT_W] = fmaf(t.w[3], r3[2 * i * ZR_P], fmaf(t.w[2], r2[2 * i * ZR_P], fmaf(t.w[1], r1[2 * i * ZR_P], t.w[0] * r0[2 * i * ZR_P])));
                 }
             } else {
-                for (int rr = half; rr < nr; rr += 2) T[rr * ZT_W + x] = 0.0f;
+                for (int rr = half; rr < ZR_R; rr += 2) T[rr * ZT_W + x] = 0.0f;
             }
         }
         __syncthreads();
-        // ---- y pass ---------------------------------------------------------------------------------------
+        // ---- next frame's coefficients into flight, then the y pass of this one ---------------------------
+        const int rmin_cur = rmin;
+        if (k + 1 < a.n) {
+            rmin = bnd[nxt][0]; cmin = bnd[nxt][2];
+            nr = min(bnd[nxt][1] - rmin + 1, ZR_R); nc = min(bnd[nxt][3] - cmin + 1, ZR_C);
+            zt_fetch(v, a.coef[k + 1], a.cpitch[k + 1], rmin, cmin, nr, nc, warp, lane);
+        }
         #pragma unroll
         for (int i = 0; i < 8; ++i) {
             const int y = 8 * yq + i;
             if (y < th) {
-                const AxisTap t = sty[y];
+                const AxisTap t = sty[cur][y];
                 const float4* tp = reinterpret_cast<const float4*>(T) + xq;
                 #pragma unroll
                 for (int q = 0; q < 4; ++q) {
-                    const float4 v = tp[(t.idx[q] - rmin) * (ZT_W / 4)];
-                    acc[i][0] = fmaf(t.w[q], v.x, acc[i][0]); acc[i][1] = fmaf(t.w[q], v.y, acc[i][1]);
-                    acc[i][2] = fmaf(t.w[q], v.z, acc[i][2]); acc[i][3] = fmaf(t.w[q], v.w, acc[i][3]);
+                    const float4 vv = tp[(t.idx[q] - rmin_cur) * (ZT_W / 4)];
+                    acc[i][0] = fmaf(t.w[q], vv.x, acc[i][0]); acc[i][1] = fmaf(t.w[q], vv.y, acc[i][1]);
+                    acc[i][2] = fmaf(t.w[q], vv.z, acc[i][2]); acc[i][3] = fmaf(t.w[q], vv.w, acc[i][3]);
                 }
             }
         }
