@@ -127,30 +127,55 @@ __device__ __forceinline__ float pf_fetch(const PrefilterJob& j, int Y, int X) {
     return __ldg(j.src + (size_t)i * j.sw + k);
 }
 
-// one 96-sample line at p[0], p[stride], ...: in-place symmetric exponential filter by warp scan (see k_prefilter2d)
-__device__ __forceinline__ void pf_scan_line(float* p, int stride, int lane) {
-    const float z = kPoleF, z2 = z * z, z3 = z2 * z, z6 = z3 * z3, z12 = z6 * z6;
-    float* q = p + 3 * lane * stride;
-    const float x0 = q[0], x1 = q[stride], x2 = q[2 * stride];
-    // causal: P
-    const float a0 = x0, a1 = fmaf(z, a0, x1), a2 = fmaf(z, a1, x2);
-    float C = a2, t;
-    t = __shfl_up_sync(0xffffffffu, C, 1); if (lane >= 1) C = fmaf(z3, t, C);
-    t = __shfl_up_sync(0xffffffffu, C, 2); if (lane >= 2) C = fmaf(z6, t, C);
-    t = __shfl_up_sync(0xffffffffu, C, 4); if (lane >= 4) C = fmaf(z12, t, C);
-    float cin = __shfl_up_sync(0xffffffffu, C, 1); if (lane == 0) cin = 0.0f;
-    const float P0 = fmaf(z, cin, a0), P1 = fmaf(z2, cin, a1), P2 = fmaf(z3, cin, a2);
-    // anticausal: Q
-    const float b2 = x2, b1 = fmaf(z, b2, x1), b0 = fmaf(z, b1, x0);
-    float Dn = b0;
-    t = __shfl_down_sync(0xffffffffu, Dn, 1); if (lane < 31) Dn = fmaf(z3, t, Dn);
-    t = __shfl_down_sync(0xffffffffu, Dn, 2); if (lane < 30) Dn = fmaf(z6, t, Dn);
-    t = __shfl_down_sync(0xffffffffu, Dn, 4); if (lane < 28) Dn = fmaf(z12, t, Dn);
-    float din = __shfl_down_sync(0xffffffffu, Dn, 1); if (lane == 31) din = 0.0f;
-    const float Q2 = fmaf(z, din, b2), Q1 = fmaf(z2, din, b1), Q0 = fmaf(z3, din, b0);
-    q[0]          = kSqrt3F * (P0 + Q0 - x0);
-    q[stride]     = kSqrt3F * (P1 + Q1 - x1);
-    q[2 * stride] = kSqrt3F * (P2 + Q2 - x2);
+// Lane-dependent carry factors of the scans (16 lanes per line, 6 samples per lane): z^6, z^12 where the neighbour
+// 1 / 2 lanes away exists on that side of the line, 0 otherwise (a multiply by zero instead of a select per step),
+// and the 0/1 gates of the carry-in.
+struct PfLane { float u1, u2, ug, d1, d2, dg; };
+__device__ __forceinline__ PfLane pf_lane(int lane) {
+    const float z = kPoleF, z3 = z * z * z, z6 = z3 * z3, z12 = z6 * z6;
+    const int l = lane & 15;
+    PfLane f;
+    f.u1 = l >= 1 ? z6 : 0.f;   f.u2 = l >= 2 ? z12 : 0.f;   f.ug = l >= 1 ? 1.f : 0.f;
+    f.d1 = l <= 14 ? z6 : 0.f;  f.d2 = l <= 13 ? z12 : 0.f;  f.dg = l <= 14 ? 1.f : 0.f;
+    // a shuffle from the own lane: opaque to ptxas, which otherwise re-materialises the compare + select pairs for
+    // every line instead of keeping the values in registers
+    f.u1 = __shfl_sync(0xffffffffu, f.u1, lane); f.u2 = __shfl_sync(0xffffffffu, f.u2, lane); f.ug = __shfl_sync(0xffffffffu, f.ug, lane);
+    f.d1 = __shfl_sync(0xffffffffu, f.d1, lane); f.d2 = __shfl_sync(0xffffffffu, f.d2, lane); f.dg = __shfl_sync(0xffffffffu, f.dg, lane);
+    return f;
+}
+
+// Two 96-sample lines per warp (one per half warp), in place: q points at this lane's 6 consecutive samples
+// q[0], q[stride], ...  Symmetric exponential filter c = P + Q - x with P[i] = sum_k z^k x[i-k], Q[i] = sum_k z^k x[i+k]:
+// serial inside the lane, two shuffle steps (carry factors z^6, z^12) across the 16 lanes of the line, i.e. 24 samples
+// of carry -- the same z^16-or-better truncation as the 16-sample warm-up halo.  The result is multiplied by `gain`
+// (1 after the first axis, 3 = sqrt(3)^2 after the second).
+__device__ __forceinline__ void pf_scan_line6(float* q, int stride, const PfLane& f, float gain) {
+    const float z = kPoleF, z2 = z * z, z3 = z2 * z, z4 = z2 * z2, z5 = z4 * z, z6 = z3 * z3;
+    const float zp[7] = {1.f, z, z2, z3, z4, z5, z6};
+    float x[6], a[6], b[6];
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) x[i] = q[i * stride];
+    a[0] = x[0];
+    #pragma unroll
+    for (int i = 1; i < 6; ++i) a[i] = fmaf(z, a[i - 1], x[i]);
+    b[5] = x[5];
+    #pragma unroll
+    for (int i = 4; i >= 0; --i) b[i] = fmaf(z, b[i + 1], x[i]);
+    float C = a[5], D = b[0];
+    C = fmaf(f.u1, __shfl_up_sync(0xffffffffu, C, 1, 16), C);
+    D = fmaf(f.d1, __shfl_down_sync(0xffffffffu, D, 1, 16), D);
+    C = fmaf(f.u2, __shfl_up_sync(0xffffffffu, C, 2, 16), C);
+    D = fmaf(f.d2, __shfl_down_sync(0xffffffffu, D, 2, 16), D);
+    const float cin = f.ug * __shfl_up_sync(0xffffffffu, C, 1, 16);
+    const float din = f.dg * __shfl_down_sync(0xffffffffu, D, 1, 16);
+    // P[i] + Q[i] - x[i] = a[i] + z b[i+1] + z^(i+1) cin + z^(6-i) din      (b[6] = 0)
+    #pragma unroll
+    for (int i = 0; i < 6; ++i) {
+        float v = fmaf(zp[i + 1], cin, a[i]);
+        v = fmaf(zp[6 - i], din, v);
+        if (i < 5) v = fmaf(z, b[i + 1], v);
+        q[i * stride] = gain * v;
+    }
 }
 
 struct PrefilterJobs { PrefilterJob job[8]; };
@@ -164,7 +189,8 @@ __global__ void __launch_bounds__(256) k_prefilter2d(const __grid_constant__ Pre
     const int ty0 = blockIdx.y * PF_T, tx0 = blockIdx.x * PF_T;
     if (ty0 >= j.ny || tx0 >= j.nx) return;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const float z = kPoleF;
+    const PfLane pl = pf_lane(lane);
+    const int half = lane >> 4, l16 = lane & 15;
 
     // region [ty0-16, ty0+80) x [tx0-16, tx0+80) of the (virtual) coefficient array
     const int off = (j.mode == SRC_PLAIN) ? 0 : kPad;
@@ -187,15 +213,14 @@ __global__ void __launch_bounds__(256) k_prefilter2d(const __grid_constant__ Pre
         }
     }
     __syncthreads();
-    // Both passes as warp scans: a line of 96 samples = 3 consecutive samples per lane.  The symmetric filter
-    // c = sqrt(3) * (P + Q - x) with P[i] = sum_k z^k x[i-k], Q[i] = sum_k z^k x[i+k]; inside a lane the sums are
-    // serial, across lanes three shuffle steps (carry factors z^3, z^6, z^12) cover 24 samples, i.e. the same
-    // z^16-or-better truncation as the 16-sample warm-up halo.  No serial recursion over the line, no idle threads.
-    // axis 0 (down the columns), all 96 columns: warp w takes columns w, w+8, ...; lane l holds rows 3l..3l+2
-    for (int c = warp; c < PF_S; c += 8) pf_scan_line(s + c, PF_P, lane);
+    // Both passes as half-warp scans (pf_scan_line6): a line of 96 samples = 6 consecutive samples per lane, two lines per
+    // warp.  No serial recursion over the line, no idle threads, 3 shuffles per direction for two lines.
+    // axis 0 (down the columns), all 96 columns: warp w takes the column pairs w, w+8, ...; lane l holds rows 6l..6l+5
+    // (pitch 97: the 16 lanes of a column hit 16 distinct even banks, the neighbouring column the odd ones)
+    for (int cp = warp; cp < PF_S / 2; cp += 8) pf_scan_line6(s + 2 * cp + half + 6 * l16 * PF_P, PF_P, pl, 1.0f);
     __syncthreads();
     // axis 1 (along the rows), the 64 interior rows
-    for (int r = warp; r < PF_T; r += 8) pf_scan_line(s + (PF_WARM + r) * PF_P, 1, lane);
+    for (int rp = warp; rp < PF_T / 2; rp += 8) pf_scan_line6(s + (PF_WARM + 2 * rp + half) * PF_P + 6 * l16, 1, pl, 3.0f);
     __syncthreads();
     const int X0 = tx0 + lane, X1 = tx0 + lane + 32;
     #pragma unroll 4
