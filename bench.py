@@ -350,9 +350,11 @@ def run_b200_arm(args):
                      "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                      "algorithmic_bytes_per_launch": alg_iter, "peak_source": peak_src, "launch_ms": k_ms,
                      "dram_achieved": (traffic / (k_ms * 1e-3) / 1e9) if traffic else None,
-                     "note": "frac is algorithmic bytes over the measured DRAM copy peak; it can exceed 1 because the hr ping-pong "
-                             "pair (96 MiB) largely stays in the 126 MB L2: ncu counts `traffic` DRAM bytes per launch (cold L2), "
-                             "dram_achieved = traffic / launch time"},
+                     "kernel_bytes_per_launch": 9 * H * W,
+                     "note": "frac is SURVEY 8(d)'s algorithmic bytes, (8 + n) per HR pixel, over the measured DRAM copy peak; it can exceed 1 "
+                             "because the kernel reads ONE pre-summed LR plane instead of the n frames (kernel_bytes_per_launch = 9 per HR "
+                             "pixel) and part of the hr ping-pong pair (96 MiB) stays in the 126 MB L2: ncu counts `traffic` DRAM bytes per "
+                             "launch (cold L2), dram_achieved = traffic / launch time"},
         "e2e": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
                 "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat8),
                 "api": "sr459.driver.FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): run_sr.py's own I/O formats -- pinned uint8 frames in "
