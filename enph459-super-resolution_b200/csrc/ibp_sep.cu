@@ -108,21 +108,24 @@ int sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pi
 
 // ---- lattice sums (once per ibp() call) ----------------------------------------------------------------
 constexpr int LS_ROWS = 8;                             // plane rows per CTA: 8 x n independent loads per thread, one atomic per CTA
+// NF = compile-time bound on the frames of a lattice (>= every slot_n): the per-frame code is fully unrolled and predicated,
+// so a 4-frame set must not pay for kMaxFrames slots
+template <int NF>
 __global__ void __launch_bounds__(256) k_lattice_sums(const __grid_constant__ LatticeArgs a) {
     const int slot = blockIdx.z;
     const int b = blockIdx.x * 256 + threadIdx.x;
     double vd = 0.0;
     if (b < a.w) {
-        #pragma unroll 2
+        #pragma unroll (NF <= 4 ? 4 : 2)
         for (int rr = 0; rr < LS_ROWS; ++rr) {
             const int ar = blockIdx.y * LS_ROWS + rr;      // plane row; site row index a = a.row0 + ar
             if (ar >= a.rows) break;
             const int ag = a.row0 + ar;
-            float x[kMaxFrames];
+            float x[NF];
             int m = 0;
             float s = 0.0f;
             #pragma unroll
-            for (int f = 0; f < kMaxFrames; ++f) {
+            for (int f = 0; f < NF; ++f) {
                 x[f] = 0.0f;
                 if (f < a.slot_n[slot]) {
                     const int k = a.slot_k[slot][f];
@@ -134,14 +137,14 @@ __global__ void __launch_bounds__(256) k_lattice_sums(const __grid_constant__ La
                 }
             }
             #pragma unroll
-            for (int f = 0; f < kMaxFrames; ++f) s += x[f];      // frame order, as before (absent frames add 0)
+            for (int f = 0; f < NF; ++f) s += x[f];      // frame order, as before (absent frames add 0)
             a.s1[slot][(size_t)ar * a.pitch + b] = s;
             const int cnt = __popc(m);
             if (cnt > 0 && ag >= a.own_a0 && ag < a.own_a1) {
                 const float mu = s / (float)cnt;
                 float v = 0.0f;
                 #pragma unroll
-                for (int f = 0; f < kMaxFrames; ++f)
+                for (int f = 0; f < NF; ++f)
                     if (m & (1 << f)) { const float d = x[f] - mu; v = fmaf(d, d, v); }
                 vd += (double)v;                               // per-site f32, across sites f64 (as before)
             }
@@ -165,7 +168,12 @@ int launch_lattice_sums(const LatticeArgs& a, cudaStream_t st) {
     if (a.nslot <= 0 || a.rows <= 0) return SR459_OK;
     SR_CUDA(cudaMemsetAsync(a.vsum, 0, sizeof(double), st));
     dim3 grid((a.w + 255) / 256, (a.rows + LS_ROWS - 1) / LS_ROWS, a.nslot);
-    k_lattice_sums<<<grid, 256, 0, st>>>(a);
+    int nmax = 1;
+    for (int sl = 0; sl < a.nslot; ++sl) nmax = std::max(nmax, a.slot_n[sl]);
+    if (nmax <= 1)      k_lattice_sums<1><<<grid, 256, 0, st>>>(a);
+    else if (nmax <= 2) k_lattice_sums<2><<<grid, 256, 0, st>>>(a);
+    else if (nmax <= 4) k_lattice_sums<4><<<grid, 256, 0, st>>>(a);
+    else                k_lattice_sums<kMaxFrames><<<grid, 256, 0, st>>>(a);
     SR_LAUNCH_CHECK("k_lattice_sums");
     return SR459_OK;
 }
