@@ -91,6 +91,8 @@ struct sr459_plan {
     AxisTap *d_saa_ty = nullptr, *d_saa_tx = nullptr;
     AxisTap *d_fwd_ty = nullptr, *d_fwd_tx = nullptr, *d_bwd_ty = nullptr, *d_bwd_tx = nullptr;
     int *d_fir_iy0 = nullptr, *d_fir_ix0 = nullptr; float *d_fir_wy = nullptr, *d_fir_wx = nullptr; bool fir_ok = false;   // fir.cu
+    FirPolyArgs fir_poly{}; bool fir_poly_ok = false;                      // interior polyphase form of the same tables
+    cudaStream_t side = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // k_fir_poly runs beside k_fir_bp's border tiles
     TapList taps_f, taps_b;
     float psf7[49] = {0};
     bool  separable = false;          // psf7[u][v] == acol[u] * brow[v]
@@ -233,6 +235,9 @@ static void plan_free(sr459_plan* p) {
     free_taps(p->taps_f);
     free_taps(p->taps_b);
     lat_destroy(p->lat);
+    if (p->ev_fork) cudaEventDestroy(p->ev_fork);
+    if (p->ev_join) cudaEventDestroy(p->ev_join);
+    if (p->side) cudaStreamDestroy(p->side);
     delete p;
 }
 
@@ -306,6 +311,12 @@ static int plan_generic_tables(sr459_plan* p) {
             SR_CUDA(cudaMemcpy(p->d_fir_wy, wy.data(), wy.size() * sizeof(float), cudaMemcpyHostToDevice));
             SR_CUDA(cudaMemcpy(p->d_fir_wx, wx.data(), wx.size() * sizeof(float), cudaMemcpyHostToDevice));
             p->fir_ok = true;
+            p->fir_poly_ok = (f == 2) && fir_poly_analyse(p->n, p->H, p->W, iy, ix, wy, wx, p->fir_poly);
+            if (p->fir_poly_ok) {
+                SR_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+                SR_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+                SR_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+            }
         }
     }
     return SR459_OK;
@@ -381,7 +392,22 @@ static int iterate_generic(sr459_plan* p, const float* const* lr, const float* c
         for (int k = 0; k < p->n; ++k) fb.err[k] = p->d_err + k * lpx;
         fb.n = p->n; fb.h = p->h; fb.w = p->w; fb.H = p->H; fb.W = p->W;
         fb.iy0 = p->d_fir_iy0; fb.ix0 = p->d_fir_ix0; fb.wy = p->d_fir_wy; fb.wx = p->d_fir_wx; fb.out = p->d_acc;
-        SR_TRY(launch_fir_bp(fb, st));
+        if (p->fir_poly_ok && !getenv("SR459_NO_FIR_POLY")) {   // interior tiles: polyphase register-window kernel (env: debug switch)
+            FirPolyArgs fp = p->fir_poly;
+            for (int k = 0; k < p->n; ++k) fp.err[k] = fb.err[k];
+            fp.h = p->h; fp.w = p->w; fp.out = p->d_acc;
+            fb.skip_y0 = fp.y0; fb.skip_y1 = fp.y1; fb.skip_x0 = fp.x0; fb.skip_x1 = fp.x1;
+            // fork / join on the plan's side stream (capturable): the ~150 border CTAs of k_fir_bp are one latency-bound
+            // wave on their own, the interior kernel runs beside them
+            SR_CUDA(cudaEventRecord(p->ev_fork, st));
+            SR_CUDA(cudaStreamWaitEvent(p->side, p->ev_fork, 0));
+            SR_TRY(launch_fir_bp(fb, p->side));
+            SR_CUDA(cudaEventRecord(p->ev_join, p->side));
+            SR_TRY(launch_fir_poly(fp, st));
+            SR_CUDA(cudaStreamWaitEvent(st, p->ev_join, 0));
+        } else {
+            SR_TRY(launch_fir_bp(fb, st));
+        }
         CorrArgs u2{p->d_acc, p->H, p->W, &p->taps_b, nxt, 1, cur, (float)(p->step / p->n), (float)p->lo, (float)p->hi};
         return launch_corr2d(u2, st);
     }

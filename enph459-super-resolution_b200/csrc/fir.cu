@@ -83,6 +83,7 @@ __global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBp
     __shared__ int bnd[4];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y0 = blockIdx.y * FB_TH, x0 = blockIdx.x * FB_TW;
+    if (y0 >= a.skip_y0 && y0 < a.skip_y1 && x0 >= a.skip_x0 && x0 < a.skip_x1) return;    // k_fir_poly's tiles
     const int th = min(FB_TH, a.H - y0), tw = min(FB_TW, a.W - x0);
     float acc[4][4];
     #pragma unroll
@@ -177,6 +178,205 @@ int launch_fir_bp(const FirBpArgs& a, cudaStream_t st) {
     dim3 grid((a.W + FB_TW - 1) / FB_TW, (a.H + FB_TH - 1) / FB_TH);
     k_fir_bp<<<grid, 256, 0, st>>>(a);
     SR_LAUNCH_CHECK("k_fir_bp");
+    return SR459_OK;
+}
+
+
+// ---------------------------------------------------------------------------------------------------------------
+// polyphase interior kernel
+// ---------------------------------------------------------------------------------------------------------------
+// One CTA (256 threads) owns an 80 x 128 output tile.  Per frame: stage 64 x 88 LR samples; x pass: lane <-> staged row
+// (odd pitches: conflict-free), one task = 16 consecutive outputs of a row from a 28-sample register window, the 20
+// weights of the parity in registers (FMA : LDS = 11 : 1 instead of 1 : 1 in k_fir_bp); y pass: thread <-> column,
+// 40 output rows per thread in two chunks, a 30-sample register window down the column.
+constexpr int FP_TH = 80, FP_TW = 128;
+constexpr int FP_RR = 64, FP_RC = 88, FP_RP = 89;      // staged rows (FP_TH/2 + 21 = 61 used), columns (64 + 21 = 85 used), pitch
+constexpr int FP_TP = 129;                             // pitch of the x-passed rows
+
+template <int D0, int D1>
+__device__ __forceinline__ void fp_xpass(const float* __restrict__ r, float* __restrict__ t, const float* w0, const float* w1) {
+    float v[28], wr[kFirTaps];
+    #pragma unroll
+    for (int j = 0; j < 28; ++j) v[j] = r[j];
+    #pragma unroll
+    for (int b = 0; b < kFirTaps; ++b) wr[b] = w0[b];
+    #pragma unroll
+    for (int m = 0; m < 8; ++m) {
+        float s = 0.f;
+        #pragma unroll
+        for (int b = 0; b < kFirTaps; ++b) s = fmaf(wr[b], v[m + D0 + b], s);
+        t[2 * m] = s;
+    }
+    #pragma unroll
+    for (int b = 0; b < kFirTaps; ++b) wr[b] = w1[b];
+    #pragma unroll
+    for (int m = 0; m < 8; ++m) {
+        float s = 0.f;
+        #pragma unroll
+        for (int b = 0; b < kFirTaps; ++b) s = fmaf(wr[b], v[m + D1 + b], s);
+        t[2 * m + 1] = s;
+    }
+}
+
+template <int D0, int D1>
+__device__ __forceinline__ void fp_ypass(const float* __restrict__ tc, float (&acc)[2][2][10], const float* w0, const float* w1) {
+    #pragma unroll
+    for (int c = 0; c < 2; ++c) {
+        float v[30], wr[kFirTaps];
+        #pragma unroll
+        for (int j = 0; j < 30; ++j) v[j] = tc[(10 * c + j) * FP_TP];
+        #pragma unroll
+        for (int b = 0; b < kFirTaps; ++b) wr[b] = w0[b];
+        #pragma unroll
+        for (int m = 0; m < 10; ++m) {
+            float s = acc[c][0][m];
+            #pragma unroll
+            for (int b = 0; b < kFirTaps; ++b) s = fmaf(wr[b], v[m + D0 + b], s);
+            acc[c][0][m] = s;
+        }
+        #pragma unroll
+        for (int b = 0; b < kFirTaps; ++b) wr[b] = w1[b];
+        #pragma unroll
+        for (int m = 0; m < 10; ++m) {
+            float s = acc[c][1][m];
+            #pragma unroll
+            for (int b = 0; b < kFirTaps; ++b) s = fmaf(wr[b], v[m + D1 + b], s);
+            acc[c][1][m] = s;
+        }
+    }
+}
+
+__global__ void __launch_bounds__(256, 2) k_fir_poly(const __grid_constant__ FirPolyArgs a) {
+    extern __shared__ float fp_smem[];
+    float* R = fp_smem;                      // FP_RR x FP_RP
+    float* T = fp_smem + FP_RR * FP_RP;      // FP_RR x FP_TP
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int ty0 = a.y0 + blockIdx.y * FP_TH, tx0 = a.x0 + blockIdx.x * FP_TW;
+    const int th = min(FP_TH, a.y1 - ty0);
+    const int x = tid & (FP_TW - 1), hh = tid >> 7;
+    float acc[2][2][10];
+    #pragma unroll
+    for (int c = 0; c < 2; ++c)
+        #pragma unroll
+        for (int m = 0; m < 10; ++m) acc[c][0][m] = acc[c][1][m] = 0.f;
+
+    for (int k = 0; k < a.n; ++k) {
+        const FirPolyFrame fr = a.fr[k];
+        const int rbase = (ty0 >> 1) + fr.cy, cbase = (tx0 >> 1) + fr.cx;
+        __syncthreads();                                 // the previous frame's passes are done with R and T
+        {   // stage: warp w takes rows w, w+8, ...; two batches of 4 rows x 3 column chunks, loads first
+            const float* src = a.err[k];
+            #pragma unroll
+            for (int half = 0; half < 2; ++half) {
+                float v[4][3];
+                #pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int rr = warp + 8 * (4 * half + i), gr = rbase + rr;
+                    #pragma unroll
+                    for (int c = 0; c < 3; ++c) {
+                        const int cc = lane + 32 * c, gc = cbase + cc;
+                        v[i][c] = (cc < FP_RC && gr >= 0 && gr < a.h && gc >= 0 && gc < a.w) ? __ldg(src + (size_t)gr * a.w + gc) : 0.f;
+                    }
+                }
+                #pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const int rr = warp + 8 * (4 * half + i);
+                    #pragma unroll
+                    for (int c = 0; c < 3; ++c)
+                        if (lane + 32 * c < FP_RC) R[rr * FP_RP + lane + 32 * c] = v[i][c];
+                }
+            }
+        }
+        __syncthreads();
+        {   // x pass: lane <-> staged row, warp <-> 16-output segment, two row halves
+            const float* w0 = a.wx[k][0]; const float* w1 = a.wx[k][1];
+            const int dsel = fr.dx[0] * 2 + fr.dx[1];
+            #pragma unroll 1
+            for (int half = 0; half < 2; ++half) {
+                const int rr = lane + 32 * half;
+                const float* r = R + rr * FP_RP + 8 * warp;
+                float* t = T + rr * FP_TP + 16 * warp;
+                if (dsel == 0)      fp_xpass<0, 0>(r, t, w0, w1);
+                else if (dsel == 1) fp_xpass<0, 1>(r, t, w0, w1);
+                else if (dsel == 2) fp_xpass<1, 0>(r, t, w0, w1);
+                else                fp_xpass<1, 1>(r, t, w0, w1);
+            }
+        }
+        __syncthreads();
+        {   // y pass: output rows 40 hh + 2m + p read x-passed rows 20 hh + m + d[p] + tap
+            const float* w0 = a.wy[k][0]; const float* w1 = a.wy[k][1];
+            const float* tc = T + (20 * hh) * FP_TP + x;
+            const int dsel = fr.dy[0] * 2 + fr.dy[1];
+            if (dsel == 0)      fp_ypass<0, 0>(tc, acc, w0, w1);
+            else if (dsel == 1) fp_ypass<0, 1>(tc, acc, w0, w1);
+            else if (dsel == 2) fp_ypass<1, 0>(tc, acc, w0, w1);
+            else                fp_ypass<1, 1>(tc, acc, w0, w1);
+        }
+    }
+    float* o = a.out + (size_t)ty0 * a.W + tx0 + x;
+    #pragma unroll
+    for (int c = 0; c < 2; ++c)
+        #pragma unroll
+        for (int m = 0; m < 10; ++m) {
+            const int yy = 40 * hh + 20 * c + 2 * m;
+            if (yy < th)     o[(size_t)yy * a.W]       = acc[c][0][m];
+            if (yy + 1 < th) o[(size_t)(yy + 1) * a.W] = acc[c][1][m];
+        }
+}
+
+// Interior (2-periodic) range of one axis table: pattern taken at the centre, extended outwards while it holds.
+static bool fp_axis_range(int N, const int* i0, const float* w, int c[2], float W[2][kFirTaps], int* lo, int* hi) {
+    const int oc = (N / 2) & ~1;
+    if (oc + 1 >= N) return false;
+    for (int p = 0; p < 2; ++p) {
+        c[p] = i0[oc + p] - oc / 2;
+        for (int a = 0; a < kFirTaps; ++a) W[p][a] = w[(size_t)(oc + p) * kFirTaps + a];
+    }
+    auto ok = [&](int o) {
+        const int p = o & 1;
+        if (i0[o] != (o - p) / 2 + c[p]) return false;
+        for (int a = 0; a < kFirTaps; ++a)
+            if (fabsf(w[(size_t)o * kFirTaps + a] - W[p][a]) > 1e-7f) return false;
+        return true;
+    };
+    int l = oc, h = oc;
+    while (l > 0 && ok(l - 1)) --l;
+    while (h < N && ok(h)) ++h;
+    *lo = l; *hi = h;
+    return h > l;
+}
+
+bool fir_poly_analyse(int n, int H, int W, const std::vector<int>& iy0, const std::vector<int>& ix0,
+                      const std::vector<float>& wy, const std::vector<float>& wx, FirPolyArgs& out) {
+    if (n < 1 || n > 8) return false;
+    int ylo = 0, yhi = H, xlo = 0, xhi = W;
+    for (int k = 0; k < n; ++k) {
+        int c[2], lo, hi;
+        if (!fp_axis_range(H, iy0.data() + (size_t)k * H, wy.data() + (size_t)k * H * kFirTaps, c, out.wy[k], &lo, &hi)) return false;
+        out.fr[k].cy = std::min(c[0], c[1]); out.fr[k].dy[0] = c[0] - out.fr[k].cy; out.fr[k].dy[1] = c[1] - out.fr[k].cy;
+        ylo = std::max(ylo, lo); yhi = std::min(yhi, hi);
+        if (!fp_axis_range(W, ix0.data() + (size_t)k * W, wx.data() + (size_t)k * W * kFirTaps, c, out.wx[k], &lo, &hi)) return false;
+        out.fr[k].cx = std::min(c[0], c[1]); out.fr[k].dx[0] = c[0] - out.fr[k].cx; out.fr[k].dx[1] = c[1] - out.fr[k].cx;
+        xlo = std::max(xlo, lo); xhi = std::min(xhi, hi);
+        if (out.fr[k].dy[0] > 1 || out.fr[k].dy[1] > 1 || out.fr[k].dx[0] > 1 || out.fr[k].dx[1] > 1) return false;
+    }
+    // the region is cut to k_fir_bp's tile grid (32 x 128): that kernel skips exactly these tiles
+    out.y0 = (ylo + FB_TH - 1) / FB_TH * FB_TH; out.y1 = yhi / FB_TH * FB_TH;
+    out.x0 = (xlo + FB_TW - 1) / FB_TW * FB_TW; out.x1 = xhi / FB_TW * FB_TW;
+    out.n = n; out.H = H; out.W = W;
+    return out.y1 > out.y0 && out.x1 > out.x0;
+}
+
+int launch_fir_poly(const FirPolyArgs& a, cudaStream_t st) {
+    static bool configured = false;
+    const size_t smem = sizeof(float) * (size_t)FP_RR * (FP_RP + FP_TP);
+    if (!configured) {
+        SR_CUDA(cudaFuncSetAttribute(k_fir_poly, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        configured = true;
+    }
+    dim3 grid((a.x1 - a.x0 + FP_TW - 1) / FP_TW, (a.y1 - a.y0 + FP_TH - 1) / FP_TH);
+    k_fir_poly<<<grid, 256, smem, st>>>(a);
+    SR_LAUNCH_CHECK("k_fir_poly");
     return SR459_OK;
 }
 

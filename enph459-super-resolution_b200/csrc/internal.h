@@ -114,8 +114,25 @@ struct FirBpArgs {
     const int* iy0; const int* ix0;     // [k * H + Y], [k * W + X]
     const float* wy; const float* wx;   // [(k * H + Y) * kFirTaps + a], [(k * W + X) * kFirTaps + b]
     float* out;                         // sum over frames, H x W
+    int skip_y0, skip_y1, skip_x0, skip_x1;   // HR-pixel rectangle (tile aligned) left to launch_fir_poly; empty if y1 <= y0
 };
 int launch_fir_bp(const FirBpArgs& a, cudaStream_t st);
+// Polyphase fast path of the same map (factor 2): away from the borders the tables are 2-periodic -- output o of parity
+// p reads LR samples (o - p) / 2 + c + d[p] + tap with ONE weight set per parity -- so interior tiles run a register-
+// window FIR with the weights in registers; launch_fir_bp then skips the tiles of the region [y0, y1) x [x0, x1).
+struct FirPolyFrame { int cy, cx, dy[2], dx[2]; };
+struct FirPolyArgs {
+    const float* err[8];
+    int n, h, w, H, W;
+    float* out;
+    int y0, y1, x0, x1;                 // region in HR pixels: rows a multiple of 32, columns a multiple of 128
+    FirPolyFrame fr[8];
+    float wy[8][2][kFirTaps], wx[8][2][kFirTaps];
+};
+// host analysis of the per-frame tables (layout of FirBpArgs); false if no interior region exists
+bool fir_poly_analyse(int n, int H, int W, const std::vector<int>& iy0, const std::vector<int>& ix0,
+                      const std::vector<float>& wy, const std::vector<float>& wx, FirPolyArgs& out);
+int launch_fir_poly(const FirPolyArgs& a, cudaStream_t st);
 
 // ---- correlation / convolution ------------------------------------------------
 // out[y,x] = sum_t w[t] * in0[y+dy[t], x+dx[t]]   (zero outside), taps with w==0 dropped

@@ -771,3 +771,26 @@ def test_run_sr_cli_errors(sr, tmp_path):
         run_sr.main(["--experiment", "mono_cal_target", "--data-dir", str(tmp_path / "data"), "--output-dir", str(tmp_path / "o")])
     with pytest.raises(FileNotFoundError):
         run_sr.main(["--experiment", "mono_barcodes", "--data-dir", str(tmp_path / "data"), "--output-dir", str(tmp_path / "o")])
+
+
+def test_fractional_shift_interior_polyphase_kernel_vs_oracle_and_spline_path(sr):
+    """Fractional shifts at a size whose back-projection has interior tiles (k_fir_poly, fir.cu) as well as border
+    tiles (k_fir_bp): both against the float64 oracle and against the stage-by-stage spline path (path 1)."""
+    import torch
+    rng = np.random.default_rng(4592)
+    h, w = 176, 336
+    lrs64 = [rng.uniform(0, 255, (h, w)) for _ in range(4)]
+    psf = O.make_gaussian_psf()
+    lrs = [torch.from_numpy(l.astype(np.float32)).cuda() for l in lrs64]
+    plan = sr.Plan(4, h, w, CALIBRATED, psf)
+    saa = plan.saa(lrs)
+    a = saa.clone(); ea = plan.set_path(0).ibp_(lrs, a, 4)
+    b = saa.clone(); eb = plan.set_path(1).ibp_(lrs, b, 4)
+    plan.close()
+    _close(a.cpu().numpy(), b.cpu().numpy(), what="polyphase + table FIR vs spline stages")
+    np.testing.assert_allclose(ea, eb, rtol=1e-5)
+    saa_o = O.shift_and_add([l.astype(np.float32).astype(np.float64) for l in lrs64], CALIBRATED)
+    hr_o, errs_o = O.ibp([l.astype(np.float32).astype(np.float64) for l in lrs64], CALIBRATED, psf, saa_o, n_iter=4)
+    _close(saa.cpu().numpy(), saa_o, what="saa")
+    _close(a.cpu().numpy(), hr_o, what="ibp (polyphase interior) vs oracle")
+    _errs_close(ea, errs_o)
