@@ -67,12 +67,15 @@ bool build_fir_bp_axis(int n_lr, int f, double s, std::vector<int>& i0, std::vec
 
 // ---------------------------------------------------------------------------------------------------------------
 // kernel: out[Y][X] = sum_k sum_a My_k[Y][a] * sum_b Mx_k[X][b] * err_k[iy0_k[Y] + a][ix0_k[X] + b]
-// One CTA (256 threads) owns a 32 x 128 output tile; per frame: stage the LR region, x pass into T, y pass into
-// 4 x 4 register accumulators per thread.
+// One CTA (256 threads) owns a 32 x 64 output tile (narrow: with k_fir_poly taking the interior these are the image
+// borders, one latency-bound wave); per frame: stage the LR region, x pass into T, y pass into register accumulators.
 // ---------------------------------------------------------------------------------------------------------------
-constexpr int FB_TH = 32, FB_TW = 128;
+constexpr int FB_TH = 32, FB_TW = 64;
+constexpr int FB_LPR = FB_TW / 4;                  // y pass: lanes per output row (4 columns per lane)
+constexpr int FB_RPI = 8 * (32 / FB_LPR);           // y pass: output rows per CTA iteration
+constexpr int FB_NI  = FB_TH / FB_RPI;
 constexpr int FB_RR = FB_TH / 2 + kFirTaps + 2;     // 38 staged LR rows   (factor >= 2)
-constexpr int FB_RC = FB_TW / 2 + kFirTaps + 4;     // 88 staged LR columns
+constexpr int FB_RC = FB_TW / 2 + kFirTaps + 4;     // 56 staged LR columns
 constexpr int FB_RP = FB_RC + 1;
 
 __global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBpArgs a) {
@@ -81,13 +84,14 @@ __global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBp
     __shared__ float wy[FB_TH * kFirTaps];
     __shared__ int iy[FB_TH];
     __shared__ int bnd[4];
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int tid = threadIdx.x, lane = tid & 31;
     const int y0 = blockIdx.y * FB_TH, x0 = blockIdx.x * FB_TW;
     if (y0 >= a.skip_y0 && y0 < a.skip_y1 && x0 >= a.skip_x0 && x0 < a.skip_x1) return;    // k_fir_poly's tiles
     const int th = min(FB_TH, a.H - y0), tw = min(FB_TW, a.W - x0);
-    float acc[4][4];
+    float acc[FB_NI][4];
     #pragma unroll
-    for (int i = 0; i < 4; ++i) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; }
+    for (int i = 0; i < FB_NI; ++i) { acc[i][0] = acc[i][1] = acc[i][2] = acc[i][3] = 0.f; }
+    const int yrow = (tid / FB_LPR), ycol = tid % FB_LPR;      // y pass: row within an iteration, 4-column group
 
     for (int k = 0; k < a.n; ++k) {
         const int* iy0 = a.iy0 + (size_t)k * a.H + y0;
@@ -126,13 +130,14 @@ __global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBp
         }
         __syncthreads();
         {   // x pass: T[rr][x], one column per thread, two row phases
-            const int x = tid & (FB_TW - 1), half = tid >> 7;
+            constexpr int NPH = 256 / FB_TW;
+            const int x = tid & (FB_TW - 1), half = tid / FB_TW;
             if (x < tw) {
                 float wreg[kFirTaps];
                 #pragma unroll
                 for (int b = 0; b < kFirTaps; ++b) wreg[b] = __ldg(wxk + (size_t)x * kFirTaps + b);
                 const int off = __ldg(ix0 + x) - cmin;
-                for (int rr = half; rr < nr; rr += 2) {
+                for (int rr = half; rr < nr; rr += NPH) {
                     const float* r = R + rr * FB_RP + off;
                     float s = 0.f;
                     #pragma unroll
@@ -140,15 +145,15 @@ __global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBp
                     T[rr * FB_TW + x] = s;
                 }
             } else {
-                for (int rr = half; rr < nr; rr += 2) T[rr * FB_TW + x] = 0.f;
+                for (int rr = half; rr < nr; rr += NPH) T[rr * FB_TW + x] = 0.f;
             }
         }
         __syncthreads();
-        {   // y pass: rows warp, warp+8, warp+16, warp+24; columns 4*lane .. 4*lane+3
-            const float4* tp = reinterpret_cast<const float4*>(T) + lane;
+        {   // y pass: rows yrow, yrow + FB_RPI, ...; columns 4*ycol .. 4*ycol+3
+            const float4* tp = reinterpret_cast<const float4*>(T) + ycol;
             #pragma unroll
-            for (int i = 0; i < 4; ++i) {
-                const int y = warp + 8 * i;
+            for (int i = 0; i < FB_NI; ++i) {
+                const int y = yrow + FB_RPI * i;
                 if (y < th) {
                     const float* wrow = wy + y * kFirTaps;
                     const float4* t0 = tp + (iy[y] - rmin) * (FB_TW / 4);
@@ -163,10 +168,10 @@ __global__ void __launch_bounds__(256, 3) k_fir_bp(const __grid_constant__ FirBp
             }
         }
     }
-    const int gx = x0 + 4 * lane;
+    const int gx = x0 + 4 * ycol;
     #pragma unroll
-    for (int i = 0; i < 4; ++i) {
-        const int gy = y0 + warp + 8 * i;
+    for (int i = 0; i < FB_NI; ++i) {
+        const int gy = y0 + yrow + FB_RPI * i;
         if (gy >= a.H || gx >= a.W) continue;
         float* d = a.out + (size_t)gy * a.W + gx;
         if (gx + 3 < a.W && (a.W & 3) == 0) *reinterpret_cast<float4*>(d) = make_float4(acc[i][0], acc[i][1], acc[i][2], acc[i][3]);
@@ -252,7 +257,7 @@ __global__ void __launch_bounds__(256, 2) k_fir_poly(const __grid_constant__ Fir
     float* T = fp_smem + FP_RR * FP_RP;      // FP_RR x FP_TP
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int ty0 = a.y0 + blockIdx.y * FP_TH, tx0 = a.x0 + blockIdx.x * FP_TW;
-    const int th = min(FP_TH, a.y1 - ty0);
+    const int th = min(FP_TH, a.y1 - ty0), tw = min(FP_TW, a.x1 - tx0);
     const int x = tid & (FP_TW - 1), hh = tid >> 7;
     float acc[2][2][10];
     #pragma unroll
@@ -313,6 +318,7 @@ __global__ void __launch_bounds__(256, 2) k_fir_poly(const __grid_constant__ Fir
             else                fp_ypass<1, 1>(tc, acc, w0, w1);
         }
     }
+    if (x >= tw) return;                                // ragged last tile column of the region
     float* o = a.out + (size_t)ty0 * a.W + tx0 + x;
     #pragma unroll
     for (int c = 0; c < 2; ++c)
