@@ -374,11 +374,10 @@ bool fir_poly_analyse(int n, int H, int W, const std::vector<int>& iy0, const st
 }
 
 int launch_fir_poly(const FirPolyArgs& a, cudaStream_t st) {
-    static bool configured = false;
+    static PerDeviceOnce configured;
     const size_t smem = sizeof(float) * (size_t)FP_RR * (FP_RP + FP_TP);
-    if (!configured) {
+    if (configured.need()) {
         SR_CUDA(cudaFuncSetAttribute(k_fir_poly, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
     }
     dim3 grid((a.x1 - a.x0 + FP_TW - 1) / FP_TW, (a.y1 - a.y0 + FP_TH - 1) / FP_TH);
     k_fir_poly<<<grid, 256, smem, st>>>(a);

@@ -176,10 +176,9 @@ int launch_ibp_dense(const DenseArgs& a, cudaStream_t st) {
     if (ntiles <= 0) return SR459_OK;
     size_t smem = ibp_dense_smem(a.R, a.g.smax, a.tile_h, a.tile_w, a.nf, a.nb);
     if (smem > 220 * 1024) { set_error("dense IBP tile needs %zu B of shared memory", smem); return SR459_EUNSUPPORTED; }
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
+    static PerDeviceMax configured;
+    if (smem > 48 * 1024 && configured.raise(smem)) {
         SR_CUDA(cudaFuncSetAttribute(k_ibp_dense, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
     }
     k_ibp_dense<<<ntiles, 256, smem, st>>>(a);
     SR_LAUNCH_CHECK("k_ibp_dense");

@@ -442,10 +442,9 @@ int launch_ibp_fast(const FastArgs& a, cudaStream_t st) {
     int nph = 0;
     for (int p = 0; p < 4; ++p) nph += a.ph_n[p] > 0;
     size_t smem = sizeof(float) * (FH_ROWS * FH_COLS + (size_t)nph * FA_R * FA_C);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static PerDeviceMax configured;
+    if (configured.raise(smem)) {
         SR_CUDA(cudaFuncSetAttribute(k_ibp_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
     }
     dim3 grid(a.tiles_x, a.tiles_y);
     k_ibp_fast<0><<<grid, F_THREADS, smem, st>>>(a);

@@ -675,10 +675,9 @@ int launch_ibp_sep(const SepArgs& a, cudaStream_t st) {
     if (a.tiles_x <= 0 || a.tiles_y <= 0) return SR459_OK;
     if (a.nph == 1 && a.tile_counter && a.n_sm > 0) {
         const size_t smem = ibp_sep_pipe_smem();
-        static bool configured = false;
-        if (!configured) {
+        static PerDeviceOnce configured;
+        if (configured.need()) {
             SR_CUDA(cudaFuncSetAttribute(k_ibp_sep_pipe, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-            configured = true;
         }
         const int ntiles = a.tiles_x * a.tiles_y;
         const int grid = std::min(a.n_sm, (ntiles + PG_N - 1) / PG_N);
@@ -689,10 +688,9 @@ int launch_ibp_sep(const SepArgs& a, cudaStream_t st) {
     int rowpar = 0;
     for (int s = 0; s < a.nph; ++s) rowpar |= 1 << (a.ph_pq[s] >> 1);
     const size_t smem = ibp_sep_smem(a.nph, rowpar == 3 ? 2 : 1);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static PerDeviceMax configured;
+    if (configured.raise(smem)) {
         SR_CUDA(cudaFuncSetAttribute(k_ibp_sep, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
     }
     dim3 grid(a.tiles_x, a.tiles_y);
     k_ibp_sep<<<grid, S_THREADS, smem, st>>>(a);

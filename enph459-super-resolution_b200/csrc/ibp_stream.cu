@@ -556,13 +556,12 @@ int launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st) {
     const int warps = a.nseg * a.nstrip;
     if (warps <= 0) return SR459_OK;
     const size_t smem = sizeof(float) * (size_t)SS_WARPS * SS_STAGES * SS_STAGE_FLOATS;
-    static bool configured = false;
-    if (!configured) {
+    static PerDeviceOnce configured;
+    if (configured.need()) {
         SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
     }
     const int grid = (warps + SS_WARPS - 1) / SS_WARPS;
     cudaLaunchConfig_t cfg{};

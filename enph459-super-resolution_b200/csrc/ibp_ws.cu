@@ -406,10 +406,9 @@ int launch_ibp_ws(const SepArgs& a, cudaStream_t st) {
     int rowpar = 0;
     for (int s = 0; s < a.nph; ++s) rowpar |= 1 << (a.ph_pq[s] >> 1);
     const size_t smem = sizeof(float) * ((size_t)WSM_HS + (size_t)a.nph * WSM_ACC + (size_t)(rowpar == 3 ? 2 : 1) * WSM_WD);
-    static size_t configured = 0;
-    if (smem > configured) {
+    static PerDeviceMax configured;
+    if (configured.raise(smem)) {
         SR_CUDA(cudaFuncSetAttribute(k_ibp_ws, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
     }
     dim3 grid(a.tiles_x, a.tiles_y);
     k_ibp_ws<<<grid, W_THREADS, smem, st>>>(a);

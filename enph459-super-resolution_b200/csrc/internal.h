@@ -106,6 +106,30 @@ int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_
 
 // ---- FIR form of the fractional-shift back-projection (fir.cu) ---------------------
 constexpr int kFirTaps = 20;            // LR taps per axis: (2*16 + 4) HR samples / factor 2, rounded up
+// cudaFuncSetAttribute is per DEVICE: a plan may live on any device of the process (sr459_plan_create's `device`), so
+// the "already configured" memo of a launch function is kept per device.
+struct PerDeviceOnce {
+    bool done[64] = {};
+    bool need() {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return true;
+        if (done[d]) return false;
+        done[d] = true;
+        return true;
+    }
+};
+
+struct PerDeviceMax {                  // same, for launchers whose dynamic shared-memory size varies: true if `s` exceeds the device's memo
+    size_t v[64] = {};
+    bool raise(size_t s) {
+        int d = 0;
+        if (cudaGetDevice(&d) != cudaSuccess || d < 0 || d >= 64) return true;
+        if (s <= v[d]) return false;
+        v[d] = s;
+        return true;
+    }
+};
+
 // one axis of  shift(zero_insert(err, f), s, order=3, mode='nearest'): out[o] = sum_a w[o][a] * err[i0[o] + a]
 bool build_fir_bp_axis(int n_lr, int f, double s, std::vector<int>& i0, std::vector<float>& w);
 struct FirBpArgs {

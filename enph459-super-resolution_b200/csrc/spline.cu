@@ -235,11 +235,10 @@ __global__ void __launch_bounds__(256) k_prefilter2d(const __grid_constant__ Pre
 }
 
 int launch_prefilter2d(const PrefilterJob* h_jobs, int njobs, cudaStream_t st) {
-    static bool configured = false;
+    static PerDeviceOnce configured;
     size_t smem = sizeof(float) * PF_S * PF_P;
-    if (!configured) {
+    if (configured.need()) {
         SR_CUDA(cudaFuncSetAttribute(k_prefilter2d, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
     }
     for (int first = 0; first < njobs; first += 8) {
         const int cnt = std::min(8, njobs - first);

@@ -794,3 +794,27 @@ def test_fractional_shift_interior_polyphase_kernel_vs_oracle_and_spline_path(sr
     _close(saa.cpu().numpy(), saa_o, what="saa")
     _close(a.cpu().numpy(), hr_o, what="ibp (polyphase interior) vs oracle")
     _errs_close(ea, errs_o)
+
+
+def test_plans_on_two_devices_of_one_process(sr):
+    """sr459_plan_create takes a device: kernel attributes (opt-in shared memory) are per device, so a second device
+    in the same process must configure them again.  Integer and fractional paths, bit-identical to device 0."""
+    import torch
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
+    rng = np.random.default_rng(11)
+    h, w = 176, 336
+    lrs64 = [rng.uniform(0, 255, (h, w)).astype(np.float32) for _ in range(4)]
+    out = {}
+    for dev in (0, 1):
+        with torch.cuda.device(dev):
+            for tag, shifts in (("int", NOMINAL), ("frac", CALIBRATED)):
+                lrs = [torch.from_numpy(l).cuda() for l in lrs64]
+                plan = sr.Plan(4, h, w, shifts, O.make_gaussian_psf())
+                hr = plan.saa(lrs)
+                errs = plan.ibp_(lrs, hr, 3)
+                out[(dev, tag)] = (hr.cpu().numpy(), errs)
+                plan.close()
+    for tag in ("int", "frac"):
+        assert np.array_equal(out[(0, tag)][0], out[(1, tag)][0]), tag
+        np.testing.assert_allclose(out[(0, tag)][1], out[(1, tag)][1], rtol=1e-12)
