@@ -311,7 +311,8 @@ static int plan_generic_tables(sr459_plan* p) {
             SR_CUDA(cudaMemcpy(p->d_fir_wy, wy.data(), wy.size() * sizeof(float), cudaMemcpyHostToDevice));
             SR_CUDA(cudaMemcpy(p->d_fir_wx, wx.data(), wx.size() * sizeof(float), cudaMemcpyHostToDevice));
             p->fir_ok = true;
-            p->fir_poly_ok = (f == 2) && fir_poly_analyse(p->n, p->H, p->W, iy, ix, wy, wx, p->fir_poly);
+            // SR459_NO_FIR_POLY=1 (read when the plan is built) keeps every tile on k_fir_bp: a debugging switch
+            p->fir_poly_ok = (f == 2) && !getenv("SR459_NO_FIR_POLY") && fir_poly_analyse(p->n, p->H, p->W, iy, ix, wy, wx, p->fir_poly);
             if (p->fir_poly_ok) {
                 SR_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
                 SR_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
@@ -392,7 +393,7 @@ static int iterate_generic(sr459_plan* p, const float* const* lr, const float* c
         for (int k = 0; k < p->n; ++k) fb.err[k] = p->d_err + k * lpx;
         fb.n = p->n; fb.h = p->h; fb.w = p->w; fb.H = p->H; fb.W = p->W;
         fb.iy0 = p->d_fir_iy0; fb.ix0 = p->d_fir_ix0; fb.wy = p->d_fir_wy; fb.wx = p->d_fir_wx; fb.out = p->d_acc;
-        if (p->fir_poly_ok && !getenv("SR459_NO_FIR_POLY")) {   // interior tiles: polyphase register-window kernel (env: debug switch)
+        if (p->fir_poly_ok) {                               // interior tiles: polyphase register-window kernel
             FirPolyArgs fp = p->fir_poly;
             for (int k = 0; k < p->n; ++k) fp.err[k] = fb.err[k];
             fp.h = p->h; fp.w = p->w; fp.out = p->d_acc;
