@@ -10,34 +10,57 @@
 
 namespace sr459 {
 
-__global__ void k_u8_to_f32(const uint8_t* __restrict__ in, int64_t n, float* __restrict__ out) {
-    int64_t i4 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 4;
-    if (i4 + 3 < n && ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0) {
-        uchar4 v = *reinterpret_cast<const uchar4*>(in + i4);
-        *reinterpret_cast<float4*>(out + i4) = make_float4((float)v.x, (float)v.y, (float)v.z, (float)v.w);
+// 16 elements per thread: one 16-byte load -> four float4 stores (and the reverse); the ragged / unaligned tail is scalar
+__global__ void __launch_bounds__(256) k_u8_to_f32(const uint8_t* __restrict__ in, int64_t n, float* __restrict__ out, int aligned) {
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    if (i0 >= n) return;
+    if (aligned && i0 + 15 < n) {
+        const uint4 v = __ldg(reinterpret_cast<const uint4*>(in + i0));
+        const unsigned w[4] = {v.x, v.y, v.z, v.w};
+        float4* o = reinterpret_cast<float4*>(out + i0);
+        #pragma unroll
+        for (int q = 0; q < 4; ++q)
+            o[q] = make_float4((float)(w[q] & 0xffu), (float)((w[q] >> 8) & 0xffu), (float)((w[q] >> 16) & 0xffu), (float)(w[q] >> 24));
     } else {
-        for (int64_t i = i4; i < n && i < i4 + 4; ++i) out[i] = (float)in[i];
+        for (int64_t i = i0; i < n && i < i0 + 16; ++i) out[i] = (float)in[i];
     }
 }
 
 int launch_u8_to_f32(const uint8_t* in, int64_t n, float* out, cudaStream_t st) {
     if (n <= 0) return SR459_OK;
-    int64_t nt = (n + 3) / 4;
-    k_u8_to_f32<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(in, n, out);
+    const int aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    const int64_t nt = (n + 15) / 16;
+    k_u8_to_f32<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(in, n, out, aligned);
     SR_LAUNCH_CHECK("k_u8_to_f32");
     return SR459_OK;
 }
 
-__global__ void k_f32_to_u8(const float* __restrict__ in, int64_t n, uint8_t* __restrict__ out) {
-    int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= n) return;
-    float v = fminf(fmaxf(in[i], 0.0f), 255.0f);
-    out[i] = (uint8_t)(int)v;          // truncation toward zero, like ndarray.astype(np.uint8)
+__device__ __forceinline__ unsigned f32_to_u8_trunc(float x) {       // clip to [0, 255], truncation toward zero
+    return (unsigned)(int)fminf(fmaxf(x, 0.0f), 255.0f);           //   like np.clip(...).astype(np.uint8) (run_sr.py:303)
+}
+
+__global__ void __launch_bounds__(256) k_f32_to_u8(const float* __restrict__ in, int64_t n, uint8_t* __restrict__ out, int aligned) {
+    const int64_t i0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) * 16;
+    if (i0 >= n) return;
+    if (aligned && i0 + 15 < n) {
+        const float4* p = reinterpret_cast<const float4*>(in + i0);
+        unsigned w[4];
+        #pragma unroll
+        for (int q = 0; q < 4; ++q) {
+            const float4 v = __ldg(p + q);
+            w[q] = f32_to_u8_trunc(v.x) | (f32_to_u8_trunc(v.y) << 8) | (f32_to_u8_trunc(v.z) << 16) | (f32_to_u8_trunc(v.w) << 24);
+        }
+        *reinterpret_cast<uint4*>(out + i0) = make_uint4(w[0], w[1], w[2], w[3]);
+    } else {
+        for (int64_t i = i0; i < n && i < i0 + 16; ++i) out[i] = (uint8_t)f32_to_u8_trunc(in[i]);
+    }
 }
 
 int launch_f32_to_u8(const float* in, int64_t n, uint8_t* out, cudaStream_t st) {
     if (n <= 0) return SR459_OK;
-    k_f32_to_u8<<<(unsigned)((n + 255) / 256), 256, 0, st>>>(in, n, out);
+    const int aligned = ((reinterpret_cast<uintptr_t>(in) | reinterpret_cast<uintptr_t>(out)) & 15) == 0;
+    const int64_t nt = (n + 15) / 16;
+    k_f32_to_u8<<<(unsigned)((nt + 255) / 256), 256, 0, st>>>(in, n, out, aligned);
     SR_LAUNCH_CHECK("k_f32_to_u8");
     return SR459_OK;
 }
