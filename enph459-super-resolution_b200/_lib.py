@@ -49,6 +49,8 @@ _SIGNATURES = {
     "sr459_extract_red": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "sr459_mean_frames": (_I, [_PP, _I, _L, _P, _P]),
     "sr459_ingest_groups": (_I, [_PP, _I, _I, _I, _I, _I, _I, _I, _PP, _P, _P, _P]),
+    "sr459_ingest_groups_v": (_I, [_PP, _I, _PI, _I, _I, _I, _I, _I, _PP, _P, _P, _P]),
+    "sr459_source_stamp": (C.c_char_p, []),
     "sr459_f32_to_u8": (_I, [_P, _L, _P, _P]),
     "sr459_blur": (_I, [_P, _I, _I, _PD, _I, _I, _P, _P]),
     "sr459_zoom": (_I, [_P, _I, _I, _I, _P, _P]),
@@ -79,13 +81,14 @@ def load(build_if_missing: bool = True):
     with _lock:
         if _lib is not None:
             return _lib
-        if build_if_missing:
-            from . import build as _build
+        from . import build as _build
+        if build_if_missing and _build.needs_build():
+            # sources differ from the binary (or there is none): a failed build is an error, never a silent fall back
+            # to whatever stale library is lying around
             try:
                 _build.build()
-            except Exception as exc:  # a prebuilt, up-to-date enough library may still be usable
-                if not os.path.exists(LIB_PATH):
-                    raise RuntimeError(f"libsr459.so is missing and could not be built: {exc}") from exc
+            except Exception as exc:
+                raise RuntimeError(f"libsr459.so is missing or older than its sources and could not be rebuilt: {exc}") from exc
         if not os.path.exists(LIB_PATH):
             raise RuntimeError(f"{LIB_PATH} not found; run enph459-super-resolution_b200/build.py")
         lib = C.CDLL(LIB_PATH)
@@ -93,6 +96,10 @@ def load(build_if_missing: bool = True):
             fn = getattr(lib, name)          # AttributeError if the .so does not export it
             if name in _SIGNATURES:
                 fn.restype, fn.argtypes = _SIGNATURES[name]
+        have, want = lib.sr459_source_stamp().decode(), _build.source_stamp()
+        if have != want:
+            raise RuntimeError(f"libsr459.so was built from other sources (stamp {have}, sources {want}); "
+                               "run enph459-super-resolution_b200/build.py")
         _lib = lib
         return lib
 

@@ -45,6 +45,24 @@ static double np_pairwise_sum(const double* a, size_t n) {
     return np_pairwise_sum(a, n2) + np_pairwise_sum(a + n2, n - n2);
 }
 
+// The caller's current device is restored when an entry point returns: a plan may live on any device of the
+// process, and plan_free is reached from Python's garbage collector at arbitrary times.
+struct DeviceGuard {
+    int prev = -1;
+    bool ok = true;
+    explicit DeviceGuard(int dev) {
+        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
+        if (prev == dev) prev = -1;                       // nothing to switch, nothing to restore
+        else ok = (cudaSetDevice(dev) == cudaSuccess);
+    }
+    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
+    DeviceGuard(const DeviceGuard&) = delete;
+    DeviceGuard& operator=(const DeviceGuard&) = delete;
+};
+#define SR_DEVICE(dev)                                                                      \
+    sr459::DeviceGuard _device_guard(dev);                                                  \
+    if (!_device_guard.ok) { sr459::set_error("cudaSetDevice(%d) failed", (int)(dev)); return SR459_ECUDA; }
+
 template <typename T>
 static int dev_alloc(T** p, size_t count) {
     if (*p) return SR459_OK;
@@ -149,13 +167,17 @@ static int plan_ensure_errors(sr459_plan* p, int n_iter) {
 
 static bool fused_supported(const sr459_plan* p);
 
-static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int w, int factor,
-                            const double* shifts, const double* psf, int kh, int kw, double step,
-                            double lo, double hi) {
+static int plan_args_check(int n_frames, int h, int w, int factor, const double* shifts, const double* psf, int kh, int kw) {
     if (n_frames < 1 || n_frames > kMaxFrames) { set_error("n_frames must be 1..%d, got %d", kMaxFrames, n_frames); return SR459_EINVAL; }
     if (h < 1 || w < 1 || factor < 1) { set_error("bad geometry h=%d w=%d factor=%d", h, w, factor); return SR459_EINVAL; }
     if (!shifts || !psf || kh < 1 || kw < 1) { set_error("null shifts/psf or empty kernel"); return SR459_EINVAL; }
-    SR_CUDA(cudaSetDevice(device));
+    return SR459_OK;
+}
+
+static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int w, int factor,
+                            const double* shifts, const double* psf, int kh, int kw, double step,
+                            double lo, double hi) {
+    SR_TRY(plan_args_check(n_frames, h, w, factor, shifts, psf, kh, kw));
     p->device = device; p->n = n_frames; p->h = h; p->w = w; p->factor = factor;
     p->H = h * factor; p->W = w * factor;
     p->psf.assign(psf, psf + (size_t)kh * kw); p->kh = kh; p->kw = kw;
@@ -227,7 +249,7 @@ static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int 
 
 static void plan_free(sr459_plan* p) {
     if (!p) return;
-    cudaSetDevice(p->device);
+    DeviceGuard guard(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
                     p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
@@ -712,7 +734,11 @@ static int check_lr(const sr459_plan* p, const float* const* lr) {
 // =================================================================================================
 extern "C" {
 
-int sr459_version(void) { return 100; }
+#ifndef SR459_SOURCE_STAMP
+#define SR459_SOURCE_STAMP "unstamped"
+#endif
+int sr459_version(void) { return 200; }
+const char* sr459_source_stamp(void) { return SR459_SOURCE_STAMP; }
 const char* sr459_last_error(void) { return g_err; }
 uint64_t sr459_launch_count(void) { return g_launches.load(); }
 
@@ -803,12 +829,25 @@ int sr459_mean_frames(const float* const* h_d_frames, int n_frames, int64_t n_px
     return launch_mean_frames(h_d_frames, n_frames, n_px, d_out, (cudaStream_t)stream);
 }
 
+int sr459_ingest_groups_v(const uint8_t* const* h_d_imgs, int n_groups, const int* h_reps, int H, int W, int step, int row_off, int col_off,
+                          float* const* h_d_frames, float* d_mean_f32, uint8_t* d_mean_u8, void* stream) {
+    if (!h_d_imgs || !h_d_frames || !h_reps) { set_error("ingest_groups: null pointer arrays"); return SR459_EINVAL; }
+    if (n_groups < 1 || n_groups > kMaxFrames) { set_error("ingest_groups: 1..%d frames, got %d", kMaxFrames, n_groups); return SR459_EINVAL; }
+    int total = 0;
+    for (int g = 0; g < n_groups; ++g) {
+        if (h_reps[g] < 1) { set_error("ingest_groups: frame %d has %d repetitions", g, h_reps[g]); return SR459_EINVAL; }
+        if (!h_d_frames[g]) { set_error("ingest_groups: frame %d is null", g); return SR459_EINVAL; }
+        total += h_reps[g];
+    }
+    for (int k = 0; k < total; ++k) if (!h_d_imgs[k]) { set_error("ingest_groups: image %d is null", k); return SR459_EINVAL; }
+    return launch_ingest_groups(h_d_imgs, n_groups, h_reps, H, W, step, row_off, col_off, h_d_frames, d_mean_f32, d_mean_u8, (cudaStream_t)stream);
+}
+
 int sr459_ingest_groups(const uint8_t* const* h_d_imgs, int n_groups, int reps, int H, int W, int step, int row_off, int col_off,
                         float* const* h_d_frames, float* d_mean_f32, uint8_t* d_mean_u8, void* stream) {
-    if (!h_d_imgs || !h_d_frames) { set_error("ingest_groups: null pointer arrays"); return SR459_EINVAL; }
-    for (int k = 0; k < n_groups * reps && k < 32; ++k) if (!h_d_imgs[k]) { set_error("ingest_groups: image %d is null", k); return SR459_EINVAL; }
-    for (int g = 0; g < n_groups && g < 8; ++g) if (!h_d_frames[g]) { set_error("ingest_groups: frame %d is null", g); return SR459_EINVAL; }
-    return launch_ingest_groups(h_d_imgs, n_groups, reps, H, W, step, row_off, col_off, h_d_frames, d_mean_f32, d_mean_u8, (cudaStream_t)stream);
+    int r[kMaxFrames];
+    for (int g = 0; g < kMaxFrames; ++g) r[g] = reps;
+    return sr459_ingest_groups_v(h_d_imgs, n_groups, r, H, W, step, row_off, col_off, h_d_frames, d_mean_f32, d_mean_u8, stream);
 }
 
 int sr459_blur(const float* d_img, int H, int W, const double* h_psf, int kh, int kw, float* d_out, void* stream) {
@@ -919,6 +958,8 @@ int sr459_plan_create(sr459_plan** out, int device, int n_frames, int h, int w, 
                       const double* h_psf, int kh, int kw, double step, double clip_lo, double clip_hi) {
     if (!out) { set_error("plan_create: null output"); return SR459_EINVAL; }
     *out = nullptr;
+    SR_TRY(plan_args_check(n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw));
+    SR_DEVICE(device);
     sr459_plan* p = new (std::nothrow) sr459_plan();
     if (!p) { set_error("out of host memory"); return SR459_ENOMEM; }
     int rc = plan_common_init(p, device, n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw, step, clip_lo, clip_hi);
@@ -961,14 +1002,14 @@ int64_t sr459_plan_scratch_bytes(const sr459_plan* plan) { return plan ? plan->s
 
 int sr459_native2x(sr459_plan* plan, const float* d_mean_lr, float* d_hr, void* stream) {
     if (!plan || !d_mean_lr || !d_hr) { set_error("native2x: bad arguments"); return SR459_EINVAL; }
-    SR_CUDA(cudaSetDevice(plan->device));
+    SR_DEVICE(plan->device);
     return run_zoom(plan, d_mean_lr, d_hr, (cudaStream_t)stream);
 }
 
 int sr459_saa(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, void* stream) {
     SR_TRY(check_lr(plan, h_d_lr));
     if (!d_hr) { set_error("saa: null output"); return SR459_EINVAL; }
-    SR_CUDA(cudaSetDevice(plan->device));
+    SR_DEVICE(plan->device);
     return run_saa(plan, h_d_lr, d_hr, (cudaStream_t)stream);
 }
 
@@ -985,7 +1026,7 @@ int sr459_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr_inout, i
     SR_TRY(check_lr(plan, h_d_lr));
     if (!d_hr_inout) { set_error("ibp: null hr buffer"); return SR459_EINVAL; }
     if (plan->band) { set_error("ibp: use sr459_band_iterate with a band plan"); return SR459_EINVAL; }
-    SR_CUDA(cudaSetDevice(plan->device));
+    SR_DEVICE(plan->device);
     SR_TRY(run_ibp(plan, h_d_lr, d_hr_inout, n_iter, (cudaStream_t)stream));
     if (h_errors) return sr459_ibp_errors(plan, n_iter, h_errors, stream);
     return SR459_OK;
@@ -1006,6 +1047,8 @@ int sr459_band_plan_create(sr459_plan** out, int device, int n_frames, int h, in
     *out = nullptr;
     if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("band_plan_create: bad rank %d of %d", rank, nranks); return SR459_EINVAL; }
     if (h < nranks) { set_error("band_plan_create: %d LR rows cannot be split into %d bands", h, nranks); return SR459_EINVAL; }
+    SR_TRY(plan_args_check(n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw));
+    SR_DEVICE(device);
     sr459_plan* p = new (std::nothrow) sr459_plan();
     if (!p) { set_error("out of host memory"); return SR459_ENOMEM; }
     int rc = plan_common_init(p, device, n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw, step, clip_lo, clip_hi);
@@ -1040,7 +1083,7 @@ int sr459_band_layout(const sr459_plan* plan, int* h_out8) {
 int sr459_band_begin(sr459_plan* plan, const float* const* h_d_lr_local, int n_iter, void* stream) {
     SR_TRY(check_lr(plan, h_d_lr_local));
     if (!plan->band || n_iter < 0) { set_error("band_begin: not a band plan or n_iter < 0"); return SR459_EINVAL; }
-    SR_CUDA(cudaSetDevice(plan->device));
+    SR_DEVICE(plan->device);
     cudaStream_t st = (cudaStream_t)stream;
     plan->band_recipe_valid = false;
     if (n_iter == 0) return SR459_OK;
@@ -1060,7 +1103,7 @@ int sr459_band_iterate(sr459_plan* plan, const float* const* h_d_lr_local, const
     if (!plan->band || !plan->band_recipe_valid || !d_cur || !d_nxt || it < 0 || it >= plan->band_iters) {
         set_error("band_iterate: call sr459_band_begin first; it must be in [0, n_iter)"); return SR459_EINVAL;
     }
-    SR_CUDA(cudaSetDevice(plan->device));
+    SR_DEVICE(plan->device);
     const int uy0 = 2 * plan->own_i0, uy1 = 2 * plan->own_i1;
     FusedRecipe r = fused_recipe(plan, uy0, uy1);
     return iterate_fused(plan, r, h_d_lr_local, d_cur, d_nxt, plan->d_partial + (size_t)it * r.per_iter, uy0, uy1,
@@ -1071,7 +1114,7 @@ int sr459_band_errors(sr459_plan* plan, int n_iter, double* h_sums, void* stream
     if (!plan || !plan->band || !h_sums || n_iter < 0 || n_iter > plan->errors_cap) { set_error("band_errors: bad arguments"); return SR459_EINVAL; }
     if (n_iter == 0) return SR459_OK;
     cudaStream_t st = (cudaStream_t)stream;
-    SR_CUDA(cudaSetDevice(plan->device));
+    SR_DEVICE(plan->device);
     SR_TRY(launch_reduce_partials(plan->d_partial, plan->per_iter, n_iter, 1.0, plan->band_uses_vsum ? plan->d_vsum : nullptr,
                                   plan->d_errors, st));
     SR_CUDA(cudaMemcpyAsync(h_sums, plan->d_errors, sizeof(double) * n_iter, cudaMemcpyDeviceToHost, st));

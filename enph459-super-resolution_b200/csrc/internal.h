@@ -339,7 +339,7 @@ int launch_reduce_partials(const double* partial, int per_iter, int n_iter, doub
 int launch_u8_to_f32(const uint8_t* in, int64_t n, float* out, cudaStream_t st);
 int launch_f32_to_u8(const float* in, int64_t n, uint8_t* out, cudaStream_t st);
 int launch_extract_red(const void* in, int is_f32, int H, int W, int ro, int co, float* out, cudaStream_t st);
-int launch_ingest_groups(const uint8_t* const* h_imgs, int n_groups, int reps, int H, int W, int step, int ro, int co,
+int launch_ingest_groups(const uint8_t* const* h_imgs, int n_groups, const int* h_reps, int H, int W, int step, int ro, int co,
                          float* const* h_frames, float* mean_f32, uint8_t* mean_u8, cudaStream_t st);
 int launch_mean_frames(const float* const* h_frames, int n, int64_t npx, float* out, cudaStream_t st);
 int launch_argmax(const void* imgs, int is_f32, int n_img, int64_t npx, long long* d_out /*n_img packed*/, cudaStream_t st);

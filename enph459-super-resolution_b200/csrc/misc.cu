@@ -107,9 +107,9 @@ int launch_mean_frames(const float* const* h_frames, int n, int64_t npx, float* 
 // load_gray + extract_red + the per-corner repetition mean (rgb_cal_target/run_sr.py:107-108) + np.mean over
 // the frames (run_sr.py:274) in ONE pass over the uint8 files, in float64 and in numpy's order of operations
 // (sequential sums along axis 0, one division each), so LR_mean.png truncates exactly as the reference's does.
-struct IngestPtrs { const uint8_t* img[32]; float* frame[8]; };
+struct IngestPtrs { const uint8_t* const* img; float* frame[8]; int first[9]; };   // images of frame g: img[first[g] .. first[g+1])
 
-__global__ void __launch_bounds__(256) k_ingest_groups(const __grid_constant__ IngestPtrs p, int n_groups, int reps, int W,
+__global__ void __launch_bounds__(256) k_ingest_groups(const __grid_constant__ IngestPtrs p, int n_groups, int W,
                                                        int step, int ro, int co, int oh, int ow,
                                                        float* __restrict__ mean_f32, uint8_t* __restrict__ mean_u8) {
     const int j = blockIdx.x * 32 + (threadIdx.x & 31);
@@ -118,8 +118,9 @@ __global__ void __launch_bounds__(256) k_ingest_groups(const __grid_constant__ I
     const size_t src = (size_t)(step * i + ro) * W + (size_t)(step * j + co), dst = (size_t)i * ow + j;
     double total = 0.0;
     for (int g = 0; g < n_groups; ++g) {
+        const int reps = p.first[g + 1] - p.first[g];
         double s = 0.0;
-        for (int r = 0; r < reps; ++r) s += (double)p.img[g * reps + r][src];
+        for (int r = p.first[g]; r < p.first[g + 1]; ++r) s += (double)p.img[r][src];
         const double m = (reps > 1) ? s / (double)reps : s;
         p.frame[g][dst] = (float)m;
         total += m;
@@ -129,20 +130,31 @@ __global__ void __launch_bounds__(256) k_ingest_groups(const __grid_constant__ I
     if (mean_u8) mean_u8[dst] = (uint8_t)(int)fmin(fmax(mean, 0.0), 255.0);
 }
 
-int launch_ingest_groups(const uint8_t* const* h_imgs, int n_groups, int reps, int H, int W, int step, int ro, int co,
+// h_reps[g] = repetitions of frame g (any count >= 1; the frames may differ, as np.stack(...).mean(axis=0) per corner
+// allows, rgb_cal_target/run_sr.py:107-108); the image-pointer table travels through a stream-ordered device buffer
+int launch_ingest_groups(const uint8_t* const* h_imgs, int n_groups, const int* h_reps, int H, int W, int step, int ro, int co,
                          float* const* h_frames, float* mean_f32, uint8_t* mean_u8, cudaStream_t st) {
-    if (n_groups < 1 || n_groups > 8 || reps < 1 || n_groups * reps > 32) {
-        set_error("ingest_groups: 1..8 frames of 1..%d repetitions (at most 32 images), got %d x %d", 32, n_groups, reps);
-        return SR459_EINVAL;
-    }
+    if (n_groups < 1 || n_groups > 8) { set_error("ingest_groups: 1..8 frames, got %d", n_groups); return SR459_EINVAL; }
     if (step < 1 || ro < 0 || co < 0 || ro >= H || co >= W) { set_error("ingest_groups: bad lattice"); return SR459_EINVAL; }
     const int oh = (H - ro + step - 1) / step, ow = (W - co + step - 1) / step;
     IngestPtrs p{};
-    for (int k = 0; k < n_groups * reps; ++k) p.img[k] = h_imgs[k];
-    for (int g = 0; g < n_groups; ++g) p.frame[g] = h_frames[g];
+    int total = 0;
+    for (int g = 0; g < n_groups; ++g) {
+        if (h_reps[g] < 1) { set_error("ingest_groups: frame %d has %d repetitions", g, h_reps[g]); return SR459_EINVAL; }
+        p.first[g] = total; total += h_reps[g]; p.frame[g] = h_frames[g];
+    }
+    p.first[n_groups] = total;
+    const uint8_t** d_tbl = nullptr;
+    SR_CUDA(cudaMallocAsync((void**)&d_tbl, sizeof(void*) * total, st));
+    cudaError_t e = cudaMemcpyAsync(d_tbl, h_imgs, sizeof(void*) * total, cudaMemcpyHostToDevice, st);   // pageable source: staged before return
+    if (e != cudaSuccess) { cudaFreeAsync(d_tbl, st); set_error("ingest_groups: %s", cudaGetErrorString(e)); return SR459_ECUDA; }
+    p.img = d_tbl;
     dim3 grid((ow + 31) / 32, (oh + 7) / 8);
-    k_ingest_groups<<<grid, 256, 0, st>>>(p, n_groups, reps, W, step, ro, co, oh, ow, mean_f32, mean_u8);
-    SR_LAUNCH_CHECK("k_ingest_groups");
+    k_ingest_groups<<<grid, 256, 0, st>>>(p, n_groups, W, step, ro, co, oh, ow, mean_f32, mean_u8);
+    e = cudaGetLastError();
+    cudaFreeAsync(d_tbl, st);
+    if (e != cudaSuccess) { set_error("launch of k_ingest_groups failed: %s", cudaGetErrorString(e)); return SR459_ECUDA; }
+    count_launch();
     return SR459_OK;
 }
 

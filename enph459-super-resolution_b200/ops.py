@@ -48,28 +48,33 @@ def _torch():
     return torch
 
 
-def _stream_ptr():
+def _stream_ptr(device=None):
+    """The current torch stream of `device` (default: the current device)."""
     torch = _torch()
-    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+    return C.c_void_p(torch.cuda.current_stream(device).cuda_stream)
 
 
 def _is_tensor(x) -> bool:
     return type(x).__module__.startswith("torch")
 
 
-def _dev(x, dtype=None):
-    """Contiguous float32 CUDA tensor holding x (no copy if it already is one)."""
+def _dev(x, dtype=None, device=None):
+    """Contiguous float32 CUDA tensor holding x (no copy if it already is one).  `device`: the device index the
+    buffer must live on (a plan's device); host data is uploaded there, a CUDA tensor of another device is refused."""
     torch = _torch()
     dtype = dtype or torch.float32
+    target = torch.device("cuda", torch.cuda.current_device() if device is None else int(device))
     if _is_tensor(x):
         t = x
         if not t.is_cuda:
-            t = t.cuda()
+            t = t.to(target)
+        elif device is not None and t.device != target:
+            raise ValueError(f"tensor lives on {t.device}, the plan on {target}")
         return t.to(dtype).contiguous()
     a = np.ascontiguousarray(x)
     if a.dtype == np.float64 and dtype == torch.float32:
         a = a.astype(np.float32)
-    return torch.from_numpy(a).cuda().to(dtype).contiguous()
+    return torch.from_numpy(a).to(target).to(dtype).contiguous()
 
 
 def _ret(t, like_numpy: bool):
@@ -180,16 +185,18 @@ def u8_to_f32(img):
 
 
 def ingest_groups(groups, red: bool = False):
-    """Frame-set ingest in one kernel: `groups` is a list of n frames, each a list of `reps` uint8
+    """Frame-set ingest in one kernel: `groups` is a list of n frames, each a list of uint8 repetitions (any
+    count per frame, as the reference's per-corner np.stack(...).mean(axis=0) allows)
     images (H x W, numpy or CUDA uint8 tensors).  Returns (frames, mean_lr, mean_u8): the n float32
     LR frames (Bayer-red sites if `red`, mean over the repetitions), their mean and its uint8 cast --
     load_gray / extract_red / stack.mean(axis=0) / np.mean(lr_frames, axis=0) of the reference
     (rgb_cal_target/run_sr.py:73-75, :107-108; mono_cal_target/run_sr.py:274, :308)."""
     torch = _torch()
     lib = _lib.load()
-    n, reps = len(groups), len(groups[0])
-    if any(len(g) != reps for g in groups):
-        raise ValueError("every frame needs the same number of repetitions")
+    n = len(groups)
+    reps = [len(g) for g in groups]
+    if n < 1 or n > MAX_FRAMES or min(reps) < 1:
+        raise ValueError(f"need 1..{MAX_FRAMES} frames with at least one image each")
     imgs = [_dev(i, torch.uint8) for g in groups for i in g]
     H, W = imgs[0].shape
     for t in imgs:
@@ -203,7 +210,8 @@ def ingest_groups(groups, red: bool = False):
     mean_u8 = torch.empty((oh, ow), dtype=torch.uint8, device=imgs[0].device)
     ip = (C.c_void_p * len(imgs))(*[t.data_ptr() for t in imgs])
     fp = (C.c_void_p * n)(*[frames[k].data_ptr() for k in range(n)])
-    _lib.check(lib.sr459_ingest_groups(ip, n, reps, H, W, step, 0, 0, fp, _ptr(mean), _ptr(mean_u8), _stream_ptr()))
+    rp = (C.c_int * n)(*reps)
+    _lib.check(lib.sr459_ingest_groups_v(ip, n, rp, H, W, step, 0, 0, fp, _ptr(mean), _ptr(mean_u8), _stream_ptr()))
     return [frames[k] for k in range(n)], mean, mean_u8
 
 
@@ -372,10 +380,19 @@ class Plan:
         return int(self._lib.sr459_plan_scratch_bytes(self._h))
 
     # -- helpers --
+    def _stream(self):
+        """torch's current stream ON THE PLAN'S DEVICE (which need not be the current device)."""
+        return _stream_ptr(self.device)
+
+    def _out(self, t):
+        if not (t.is_cuda and t.device.index == self.device and t.dtype == _torch().float32 and t.is_contiguous()):
+            raise ValueError(f"output buffer must be a contiguous float32 tensor on cuda:{self.device}")
+        return t
+
     def _frames(self, lr_list):
         if len(lr_list) != self.n:
             raise ValueError(f"plan was built for {self.n} frames, got {len(lr_list)}")
-        ts = [_dev(f) for f in lr_list]
+        ts = [_dev(f, device=self.device) for f in lr_list]
         for t in ts:
             if tuple(t.shape) != (self.h, self.w):
                 raise ValueError(f"frame shape {tuple(t.shape)} != plan shape {(self.h, self.w)}")
@@ -384,18 +401,18 @@ class Plan:
 
     def native_2x(self, mean_lr, out=None):
         torch = _torch()
-        t = _dev(mean_lr)
+        t = _dev(mean_lr, device=self.device)
         if tuple(t.shape) != (self.h, self.w):
             raise ValueError(f"frame shape {tuple(t.shape)} != plan shape {(self.h, self.w)}")
-        out = torch.empty((self.H, self.W), dtype=torch.float32, device=t.device) if out is None else out
-        _lib.check(self._lib.sr459_native2x(self._h, _ptr(t), _ptr(out), _stream_ptr()))
+        out = torch.empty((self.H, self.W), dtype=torch.float32, device=t.device) if out is None else self._out(out)
+        _lib.check(self._lib.sr459_native2x(self._h, _ptr(t), _ptr(out), self._stream()))
         return out
 
     def saa(self, lr_list, out=None):
         torch = _torch()
         ts, arr = self._frames(lr_list)
-        out = torch.empty((self.H, self.W), dtype=torch.float32, device=ts[0].device) if out is None else out
-        _lib.check(self._lib.sr459_saa(self._h, arr, _ptr(out), _stream_ptr()))
+        out = torch.empty((self.H, self.W), dtype=torch.float32, device=ts[0].device) if out is None else self._out(out)
+        _lib.check(self._lib.sr459_saa(self._h, arr, _ptr(out), self._stream()))
         return out
 
     def ibp_(self, lr_list, hr_inout, n_iter, want_errors=True):
@@ -403,24 +420,25 @@ class Plan:
         ts, arr = self._frames(lr_list)
         if tuple(hr_inout.shape) != (self.H, self.W) or not hr_inout.is_contiguous():
             raise ValueError(f"hr shape {tuple(hr_inout.shape)} != plan HR shape {(self.H, self.W)} (contiguous)")
+        self._out(hr_inout)
         errs = np.empty(max(int(n_iter), 0), dtype=np.float64)
         ep = errs.ctypes.data_as(C.POINTER(C.c_double)) if want_errors else None
-        _lib.check(self._lib.sr459_ibp(self._h, arr, _ptr(hr_inout), int(n_iter), ep, _stream_ptr()))
+        _lib.check(self._lib.sr459_ibp(self._h, arr, _ptr(hr_inout), int(n_iter), ep, self._stream()))
         return errs.tolist() if want_errors else None
 
     def errors(self, n_iter):
         errs = np.empty(int(n_iter), dtype=np.float64)
-        _lib.check(self._lib.sr459_ibp_errors(self._h, int(n_iter), errs.ctypes.data_as(C.POINTER(C.c_double)), _stream_ptr()))
+        _lib.check(self._lib.sr459_ibp_errors(self._h, int(n_iter), errs.ctypes.data_as(C.POINTER(C.c_double)), self._stream()))
         return errs.tolist()
 
     def saa_ibp(self, lr_list, n_iter, out=None, saa_out=None, want_errors=True):
         torch = _torch()
         ts, arr = self._frames(lr_list)
-        out = torch.empty((self.H, self.W), dtype=torch.float32, device=ts[0].device) if out is None else out
+        out = torch.empty((self.H, self.W), dtype=torch.float32, device=ts[0].device) if out is None else self._out(out)
         errs = np.empty(max(int(n_iter), 0), dtype=np.float64)
         ep = errs.ctypes.data_as(C.POINTER(C.c_double)) if want_errors else None
-        _lib.check(self._lib.sr459_saa_ibp(self._h, arr, _ptr(out), _ptr(saa_out) if saa_out is not None else None,
-                                           int(n_iter), ep, _stream_ptr()))
+        _lib.check(self._lib.sr459_saa_ibp(self._h, arr, _ptr(out), _ptr(self._out(saa_out)) if saa_out is not None else None,
+                                           int(n_iter), ep, self._stream()))
         return out, (errs.tolist() if want_errors else None)
 
 

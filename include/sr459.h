@@ -45,6 +45,9 @@ typedef struct sr459_plan sr459_plan;
 /* ---- library ---------------------------------------------------------- */
 int         sr459_version(void);                 /* 100*major + minor */
 const char* sr459_last_error(void);
+/* hash of the sources this binary was built from (build.py: source_stamp());
+ * the Python binding refuses a library whose stamp differs from the sources on disk. */
+const char* sr459_source_stamp(void);
 /* number of CUDA kernels this library has launched since load (per process);
  * bench.py reports the delta over its timed region as gpu_launches.          */
 uint64_t    sr459_launch_count(void);
@@ -88,6 +91,11 @@ int sr459_mean_frames(const float* const* h_d_frames, int n_frames, int64_t n_px
 int sr459_ingest_groups(const uint8_t* const* h_d_imgs, int n_groups, int reps, int H, int W,
                         int step, int row_off, int col_off, float* const* h_d_frames,
                         float* d_mean_f32, uint8_t* d_mean_u8, void* stream);
+/* The same with a repetition count per frame (h_reps[n_groups], any counts >= 1: the reference's
+ * np.stack(reps).mean(axis=0) per corner accepts unequal counts); images are frame-major. */
+int sr459_ingest_groups_v(const uint8_t* const* h_d_imgs, int n_groups, const int* h_reps, int H, int W,
+                          int step, int row_off, int col_off, float* const* h_d_frames,
+                          float* d_mean_f32, uint8_t* d_mean_u8, void* stream);
 /* np.clip(img,0,255).astype(np.uint8)  (truncation)    run_sr.py:303          */
 int sr459_f32_to_u8(const float* d_in, int64_t n, uint8_t* d_out, void* stream);
 
