@@ -51,6 +51,10 @@ _SIGNATURES = {
     "sr459_ingest_groups": (_I, [_PP, _I, _I, _I, _I, _I, _I, _I, _PP, _P, _P, _P]),
     "sr459_ingest_groups_v": (_I, [_PP, _I, _PI, _I, _I, _I, _I, _I, _PP, _P, _P, _P]),
     "sr459_source_stamp": (C.c_char_p, []),
+    "sr459_debug_guard_bands": (_I, [_I]),
+    "sr459_debug_check_guards": (_I, []),
+    "sr459_debug_live_allocations": (_I, []),
+    "sr459_debug_poke_guard": (_I, [_I]),
     "sr459_f32_to_u8": (_I, [_P, _L, _P, _P]),
     "sr459_blur": (_I, [_P, _I, _I, _PD, _I, _I, _P, _P]),
     "sr459_zoom": (_I, [_P, _I, _I, _I, _P, _P]),

@@ -66,7 +66,7 @@ struct DeviceGuard {
 template <typename T>
 static int dev_alloc(T** p, size_t count) {
     if (*p) return SR459_OK;
-    cudaError_t e = cudaMalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T));
+    cudaError_t e = gmalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T));
     if (e != cudaSuccess) {
         set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));
         *p = nullptr;
@@ -151,7 +151,7 @@ static int plan_alloc(sr459_plan* p, T** ptr, size_t count) {
 
 static int plan_ensure_partial(sr459_plan* p, size_t count) {
     if (count <= p->partial_cap) return SR459_OK;
-    if (p->d_partial) { cudaFree(p->d_partial); p->scratch -= (int64_t)(p->partial_cap * sizeof(double)); p->d_partial = nullptr; }
+    if (p->d_partial) { gfree(p->d_partial); p->scratch -= (int64_t)(p->partial_cap * sizeof(double)); p->d_partial = nullptr; }
     SR_TRY(plan_alloc(p, &p->d_partial, count));
     p->partial_cap = count;
     return SR459_OK;
@@ -159,7 +159,7 @@ static int plan_ensure_partial(sr459_plan* p, size_t count) {
 
 static int plan_ensure_errors(sr459_plan* p, int n_iter) {
     if (n_iter <= p->errors_cap) return SR459_OK;
-    if (p->d_errors) { cudaFree(p->d_errors); p->scratch -= (int64_t)(p->errors_cap * sizeof(double)); p->d_errors = nullptr; }
+    if (p->d_errors) { gfree(p->d_errors); p->scratch -= (int64_t)(p->errors_cap * sizeof(double)); p->d_errors = nullptr; }
     SR_TRY(plan_alloc(p, &p->d_errors, (size_t)n_iter));
     p->errors_cap = n_iter;
     return SR459_OK;
@@ -253,7 +253,7 @@ static void plan_free(sr459_plan* p) {
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
                     p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
-    for (void* q : ptrs) if (q) cudaFree(q);
+    for (void* q : ptrs) if (q) gfree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
     lat_destroy(p->lat);
@@ -558,7 +558,7 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel
     const int rows = p->lr_hi - p->lr_lo;
     const int pitch = (p->w + 3) & ~3;
     if (p->s1_rows != rows || p->s1_pitch != pitch) {
-        for (int s = 0; s < kMaxSlots; ++s) if (p->d_s1[s]) { cudaFree(p->d_s1[s]); p->d_s1[s] = nullptr; }
+        for (int s = 0; s < kMaxSlots; ++s) if (p->d_s1[s]) { gfree(p->d_s1[s]); p->d_s1[s] = nullptr; }
         p->s1_rows = rows; p->s1_pitch = pitch;
     }
     SR_TRY(plan_alloc(p, &p->d_vsum, 1));
@@ -598,7 +598,7 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel
 
 static int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
     if (n_iter > p->counters_cap) {
-        if (p->d_counters) { cudaFree(p->d_counters); p->d_counters = nullptr; p->scratch -= (int64_t)p->counters_cap * 4; }
+        if (p->d_counters) { gfree(p->d_counters); p->d_counters = nullptr; p->scratch -= (int64_t)p->counters_cap * 4; }
         SR_TRY(plan_alloc(p, &p->d_counters, (size_t)n_iter));
         p->counters_cap = n_iter;
     }
@@ -761,9 +761,9 @@ int sr459_psf_measured(const void* d_imgs, int is_f32, int n_img, int H, int W, 
     if (!d_imgs || n_img < 1 || H < 1 || W < 1 || halfwidth < 1 || !h_out) { set_error("psf_measured: bad arguments"); return SR459_EINVAL; }
     const int margin = halfwidth + 6, side = 2 * margin + 1, K = 2 * halfwidth + 1;
     long long* d_keys = nullptr; int* d_peaks = nullptr; double* d_patch = nullptr;
-    SR_CUDA(cudaMalloc((void**)&d_keys, sizeof(long long) * n_img));
-    SR_CUDA(cudaMalloc((void**)&d_peaks, sizeof(int) * 2 * n_img));
-    SR_CUDA(cudaMalloc((void**)&d_patch, sizeof(double) * side * side));
+    SR_CUDA(gmalloc((void**)&d_keys, sizeof(long long) * n_img));
+    SR_CUDA(gmalloc((void**)&d_peaks, sizeof(int) * 2 * n_img));
+    SR_CUDA(gmalloc((void**)&d_patch, sizeof(double) * side * side));
     int rc = launch_argmax(d_imgs, is_f32, n_img, (int64_t)H * W, d_keys, st);
     std::vector<unsigned long long> keys(n_img);
     std::vector<int> peaks(2 * n_img, -1);
@@ -789,7 +789,7 @@ int sr459_psf_measured(const void* d_imgs, int is_f32, int n_img, int H, int W, 
         }
         if (ce == cudaSuccess) ce = cudaStreamSynchronize(st);
     }
-    cudaFree(d_keys); cudaFree(d_peaks); cudaFree(d_patch);
+    gfree(d_keys); gfree(d_peaks); gfree(d_patch);
     if (rc != SR459_OK) return rc;
     if (ce != cudaSuccess) { set_error("psf_measured: %s", cudaGetErrorString(ce)); return SR459_ECUDA; }
     if (h_peaks) memcpy(h_peaks, peaks.data(), sizeof(int) * 2 * n_img);
@@ -885,7 +885,7 @@ int sr459_zoom(const float* d_in, int h, int w, int factor, float* d_out, void* 
         rc = launch_resample_sum(a, st);
     }
     cudaStreamSynchronize(st);
-    if (dty) cudaFree(dty); if (dtx) cudaFree(dtx); if (coef) cudaFree(coef);
+    if (dty) gfree(dty); if (dtx) gfree(dtx); if (coef) gfree(coef);
     return rc;
 }
 
@@ -910,7 +910,7 @@ static int shift_like(const float* d_src, int sh, int sw, int vh, int vw, int mo
         rc = launch_resample_sum(a, st);
     }
     cudaStreamSynchronize(st);
-    if (dty) cudaFree(dty); if (dtx) cudaFree(dtx); if (coef) cudaFree(coef);
+    if (dty) gfree(dty); if (dtx) gfree(dtx); if (coef) gfree(coef);
     return rc;
 }
 
@@ -928,7 +928,7 @@ int sr459_forward_model(const float* d_hr, int H, int W, const double* h_psf, in
     int rc = sr459_blur(d_hr, H, W, h_psf, kh, kw, B, stream);
     const int oh = (H + factor - 1) / factor, ow = (W + factor - 1) / factor;
     if (rc == SR459_OK) rc = shift_like(B, H, W, H, W, SRC_EDGEPAD, 1, dy * factor, dx * factor, oh, ow, factor, d_out_lr, st);
-    cudaFree(B);
+    gfree(B);
     return rc;
 }
 
@@ -950,7 +950,7 @@ int sr459_back_project(const float* d_err, int h, int w, const double* h_psf, in
         cudaStreamSynchronize(st);
         free_taps(t);
     }
-    cudaFree(S);
+    gfree(S);
     return rc;
 }
 

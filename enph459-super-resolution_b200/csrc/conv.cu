@@ -36,9 +36,9 @@ void build_taps_host(const double* k, int kh, int kw, bool flip, TapList& t) {
 int upload_taps(TapList& t) {
     free_taps(t);
     size_t n = std::max(1, t.ntaps);
-    SR_CUDA(cudaMalloc((void**)&t.d_w, n * sizeof(float)));
-    SR_CUDA(cudaMalloc((void**)&t.d_dy, n * sizeof(int)));
-    SR_CUDA(cudaMalloc((void**)&t.d_dx, n * sizeof(int)));
+    SR_CUDA(gmalloc((void**)&t.d_w, n * sizeof(float)));
+    SR_CUDA(gmalloc((void**)&t.d_dy, n * sizeof(int)));
+    SR_CUDA(gmalloc((void**)&t.d_dx, n * sizeof(int)));
     if (t.ntaps) {
         SR_CUDA(cudaMemcpy(t.d_w, t.w.data(), t.ntaps * sizeof(float), cudaMemcpyHostToDevice));
         SR_CUDA(cudaMemcpy(t.d_dy, t.dy.data(), t.ntaps * sizeof(int), cudaMemcpyHostToDevice));
@@ -48,9 +48,9 @@ int upload_taps(TapList& t) {
 }
 
 void free_taps(TapList& t) {
-    if (t.d_w) cudaFree(t.d_w);
-    if (t.d_dy) cudaFree(t.d_dy);
-    if (t.d_dx) cudaFree(t.d_dx);
+    if (t.d_w) gfree(t.d_w);
+    if (t.d_dy) gfree(t.d_dy);
+    if (t.d_dx) gfree(t.d_dx);
     t.d_w = nullptr; t.d_dy = nullptr; t.d_dx = nullptr;
 }
 

@@ -588,7 +588,7 @@ int lat_create(LatPlan** out, const double* psf, int kh, int kw) {
         for (int v = 0; v < kw; ++v) L->psfP[(size_t)(u + L->RT - rh) * K + (v + L->RT - rw)] = (float)psf[(size_t)u * kw + v];
     if (L->NT == 16) { build_tab<16>(L->psfP, true, L->f16); build_tab<16>(L->psfP, false, L->b16); }
     else             { build_tab<8>(L->psfP, true, L->f8);   build_tab<8>(L->psfP, false, L->b8); }
-    if (cudaMalloc((void**)&L->d_psf, sizeof(float) * K * K) != cudaSuccess ||
+    if (gmalloc((void**)&L->d_psf, sizeof(float) * K * K) != cudaSuccess ||
         cudaMemcpy(L->d_psf, L->psfP.data(), sizeof(float) * K * K, cudaMemcpyHostToDevice) != cudaSuccess) {
         set_error("lat_create: device allocation failed"); delete L; return SR459_ECUDA;
     }
@@ -596,7 +596,7 @@ int lat_create(LatPlan** out, const double* psf, int kh, int kw) {
     const void* hf = L->NT == 16 ? (const void*)&L->f16 : (const void*)&L->f8;
     const void* hb = L->NT == 16 ? (const void*)&L->b16 : (const void*)&L->b8;
     const size_t tb = L->NT == 16 ? sizeof(LatTab<16>) : sizeof(LatTab<8>);
-    if (cudaMalloc(&L->d_tabf, tb) != cudaSuccess || cudaMalloc(&L->d_tabb, tb) != cudaSuccess ||
+    if (gmalloc(&L->d_tabf, tb) != cudaSuccess || gmalloc(&L->d_tabb, tb) != cudaSuccess ||
         cudaMemcpy(L->d_tabf, hf, tb, cudaMemcpyHostToDevice) != cudaSuccess ||
         cudaMemcpy(L->d_tabb, hb, tb, cudaMemcpyHostToDevice) != cudaSuccess) {
         set_error("lat_create: device allocation failed"); lat_destroy(L); return SR459_ECUDA;
@@ -608,20 +608,20 @@ int lat_create(LatPlan** out, const double* psf, int kh, int kw) {
 
 static void lat_free_planes(LatPlan* L) {
     for (int s = 0; s < kMaxSlots; ++s) {
-        if (L->d_bl[s]) cudaFree(L->d_bl[s]);
-        if (L->d_A[s]) cudaFree(L->d_A[s]);
+        if (L->d_bl[s]) gfree(L->d_bl[s]);
+        if (L->d_A[s]) gfree(L->d_A[s]);
         L->d_bl[s] = L->d_A[s] = nullptr;
     }
-    for (float** p : {&L->d_btop, &L->d_bleft, &L->d_arow, &L->d_acol}) { if (*p) cudaFree(*p); *p = nullptr; }
+    for (float** p : {&L->d_btop, &L->d_bleft, &L->d_arow, &L->d_acol}) { if (*p) gfree(*p); *p = nullptr; }
     L->rows = 0;
 }
 
 void lat_destroy(LatPlan* L) {
     if (!L) return;
     lat_free_planes(L);
-    if (L->d_psf) cudaFree(L->d_psf);
-    if (L->d_tabf) cudaFree(L->d_tabf);
-    if (L->d_tabb) cudaFree(L->d_tabb);
+    if (L->d_psf) gfree(L->d_psf);
+    if (L->d_tabf) gfree(L->d_tabf);
+    if (L->d_tabb) gfree(L->d_tabb);
     delete L;
 }
 
@@ -662,14 +662,14 @@ static int lat_ensure_planes(LatPlan* L, const LatGeom& g) {
     lat_free_planes(L);
     const size_t cnt = (size_t)rows * g.pitch;
     for (int s = 0; s < g.nslot; ++s) {
-        SR_CUDA(cudaMalloc((void**)&L->d_bl[s], cnt * sizeof(float)));
-        SR_CUDA(cudaMalloc((void**)&L->d_A[s], cnt * sizeof(float)));
+        SR_CUDA(gmalloc((void**)&L->d_bl[s], cnt * sizeof(float)));
+        SR_CUDA(gmalloc((void**)&L->d_A[s], cnt * sizeof(float)));
         L->bytes += 2 * (int64_t)cnt * 4;
     }
-    SR_CUDA(cudaMalloc((void**)&L->d_btop, sizeof(float) * g.W));
-    SR_CUDA(cudaMalloc((void**)&L->d_arow, sizeof(float) * g.W));
-    SR_CUDA(cudaMalloc((void**)&L->d_bleft, sizeof(float) * g.H));
-    SR_CUDA(cudaMalloc((void**)&L->d_acol, sizeof(float) * g.H));
+    SR_CUDA(gmalloc((void**)&L->d_btop, sizeof(float) * g.W));
+    SR_CUDA(gmalloc((void**)&L->d_arow, sizeof(float) * g.W));
+    SR_CUDA(gmalloc((void**)&L->d_bleft, sizeof(float) * g.H));
+    SR_CUDA(gmalloc((void**)&L->d_acol, sizeof(float) * g.H));
     SR_CUDA(cudaMemset(L->d_btop, 0, sizeof(float) * g.W));
     SR_CUDA(cudaMemset(L->d_arow, 0, sizeof(float) * g.W));
     SR_CUDA(cudaMemset(L->d_bleft, 0, sizeof(float) * g.H));

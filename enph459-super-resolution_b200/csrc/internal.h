@@ -14,6 +14,10 @@ void set_error(const char* fmt, ...);
 extern std::atomic<uint64_t> g_launches;
 inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
+// every device allocation of the library goes through these (alloc.cu: optional guard bands)
+cudaError_t gmalloc(void** p, size_t bytes);
+void gfree(void* p);
+
 #define SR_CUDA(call)                                                                       \
     do {                                                                                    \
         cudaError_t _e = (call);                                                            \

@@ -52,6 +52,14 @@ const char* sr459_source_stamp(void);
  * bench.py reports the delta over its timed region as gpu_launches.          */
 uint64_t    sr459_launch_count(void);
 
+/* Debugging aid (alloc.cu): pad every later device allocation of the library with `bytes` of a fixed pattern on
+ * both sides (0 = off; also SR459_GUARD=<bytes> in the environment at load time).  sr459_debug_check_guards()
+ * synchronises, reads the bands back and returns how many allocations had theirs overwritten (0 = clean). */
+int sr459_debug_guard_bands(int bytes);
+int sr459_debug_check_guards(void);
+int sr459_debug_live_allocations(void);
+int sr459_debug_poke_guard(int restore);   /* checker self-test: damage / repair one guard byte */
+
 /* ---- PSF construction ------------------------------------------------- */
 /* make_gaussian_psf(size, sigma)                     run_sr.py:104-111.
  * out must hold (2*(size/2)+1)^2 doubles (the reference builds mgrid[-hw:hw+1]). */

@@ -758,10 +758,17 @@ def test_fused_ingest_matches_numpy_order_of_operations(sr):
             assert np.array_equal(f.cpu().numpy(), r.astype(np.float32))
         assert np.array_equal(mean.cpu().numpy(), ref_mean.astype(np.float32))
         assert np.array_equal(mean_u8.cpu().numpy(), O.to_uint8(ref_mean))
+    # unequal repetition counts per corner and more than 32 files in one set: the reference's per-corner
+    # np.stack(...).mean(axis=0) takes both (rgb_cal_target/run_sr.py:100-108)
+    for counts in ([1, 2], [5, 9, 3, 7], [6] * 8):
+        groups = [[rng.integers(0, 256, (20, 28), dtype=np.uint8) for _ in range(c)] for c in counts]
+        frames, mean, mean_u8 = sr.ingest_groups(groups, red=True)
+        ref = [np.stack([O.extract_red(x.astype(np.float64)) for x in g]).mean(axis=0) for g in groups]
+        for f, r in zip(frames, ref):
+            assert np.array_equal(f.cpu().numpy(), r.astype(np.float32))
+        assert np.array_equal(mean_u8.cpu().numpy(), O.to_uint8(np.mean(ref, axis=0)))
     with pytest.raises(ValueError):
-        sr.ingest_groups([[np.zeros((4, 4), np.uint8)], [np.zeros((4, 4), np.uint8)] * 2])
-    with pytest.raises(sr.Sr459Error):
-        sr.ingest_groups([[np.zeros((4, 4), np.uint8)] * 5] * 8)
+        sr.ingest_groups([[np.zeros((4, 4), np.uint8)], []])
 
 
 def test_run_sr_cli_errors(sr, tmp_path):
