@@ -13,15 +13,19 @@ iterations, on synthetic S1-noise frames (np.random.default_rng(459), SURVEY.md 
   e2e      the same jobs through the public host API (FrameSetPipeline) in the formats run_sr.py moves: pinned host
            uint8 frames (what load_gray reads, run_sr.py:73-75) -> H2D -> u8->f32, SAA+IBP, clip + truncation ->
            D2H of the uint8 HR image (what run_sr.py:303 writes), copies inside the timed region.
-  e2e_f32  the same with float32 frames in and the float32 HR image out (4x the PCIe bytes: 100 MB per job, which
-           saturates the host side beyond 2 GPUs; reported beside e2e, not instead of it).
   roofline the fused IBP-iteration kernel: algorithmic bytes (8+n)*H*W per launch divided by its
            mean duration, measured live with CUDA events around the IBP loop of every timed step.
   cpu_baseline  the reference's CPU path (oracle/scipy_port.py: the same scipy calls the reference
-           makes) on the host cores, on a bounded sample, rank 0 at N=1 only.
+           makes) on the host cores, rank 0 at N=1 only: one sample of the work of ONE FRAME at the
+           job's FULL size (4x1536x2048 -> 3072x4096) on every core at once.
+  configs  the other BASELINE.json configurations, measured in the same run (device-resident, CUDA
+           graphs, CUDA events): c2 (fractional shifts + measured 7x7), monocal5, c1_measured7,
+           c4 (31x31 measured PSF, 200 iterations), c5 (streaming burst); N > 1 adds `bands`
+           (config 4 as row bands with the halo exchange).
 
 Multi-GPU: independent frame sets per rank (weak scaling, no data-path collective), launched by
-torchrun; barrier + max-over-ranks timing.  --impl reference times the CPU port only.
+torchrun; barrier + max-over-ranks timing.  --impl reference times the CPU port only: every step is
+one frame-iteration of the job at full size on every host core at once (see run_reference_arm).
 """
 from __future__ import annotations
 
@@ -145,55 +149,100 @@ class ClockSampler:
 
 
 # ------------------------------------------------------------------------------------------------
+# workload description shared by both arms (the driver compares the `config` of the two lines)
+# ------------------------------------------------------------------------------------------------
+def workload_config(n, h, w, iters, world):
+    H, W = 2 * h, 2 * w
+    ring = 4
+    return {
+        "workload": f"config1: {n}x{h}x{w} mono frames -> {H}x{W}, Gaussian 7x7 PSF, nominal +-0.5 px shifts, "
+                    f"SAA + {iters} IBP iterations per job; one independent frame set per job per GPU",
+        "n_frames": n, "lr_shape": [h, w], "hr_shape": [H, W], "ibp_iterations": iters, "psf": "gaussian7",
+        "shifts_lr_px": [list(s) for s in NOMINAL],
+        "parallelism": f"batch-dp{world}",
+        "b200_arm": {
+            "step": "one whole job; each stage replayed as a CUDA graph",
+            "cache": f"ring of {ring} distinct frame sets ({ring * n * h * w * 4 >> 20} MiB LR) + {3 * H * W * 4 >> 20} MiB HR "
+                     "working set per job, larger than the 126 MB L2; no explicit flush",
+        },
+        "reference_arm": {
+            "step": "bounded sample of the same job AT ITS FULL SIZE: every host core at once runs the reference's scipy "
+                    f"calls for ONE frame of ONE iteration (forward_model + residual + back_project on {H}x{W} float64); "
+                    "the SAA part (zoom + shift of one frame) is sampled once before the timed steps",
+            "job_time_model": "t_job = n*t_saa_frame + K*(n*t_frame_iteration + t_update): identical scipy calls on identical "
+                              "shapes repeated n*K times, nothing extrapolated across image sizes",
+            "extrapolated_over": "frame and iteration count only",
+        },
+    }
+
+
+# ------------------------------------------------------------------------------------------------
 # CPU baseline (reference's path on scipy, host cores)
 # ------------------------------------------------------------------------------------------------
-def cpu_sample(n, h, w, k_iter, cores, seed0=459):
-    """Run `cores` concurrent single-threaded copies of the scipy port; returns aggregate HR Mpix/s
-    extrapolated to the K=50 job (per-iteration cost is constant), plus details."""
+def cpu_procs(cores, per_proc_gb=1.6):
+    """Concurrent full-size workers the host memory allows (each holds ~12 float64 HR-sized arrays)."""
+    try:
+        import psutil
+        avail = psutil.virtual_memory().available / 2 ** 30
+        return max(1, min(cores, int(avail / per_proc_gb)))
+    except Exception:
+        return cores
+
+
+def cpu_full_size_step(n, h, w, iters, procs, with_saa, seed0, t_saa_frame=None):
+    """One bounded sample at the job's full size on `procs` cores at once (see workload_config.reference_arm).
+    Returns dict(rate HR Mpix/s summed over the workers, wall, per-piece mean times)."""
     import multiprocessing as mp
     from oracle import scipy_port, sr_oracle
     psf = sr_oracle.make_gaussian_psf()
-    args = [(seed0 + i, n, h, w, NOMINAL, psf, k_iter) for i in range(cores)]
+    args = [(seed0 + i, h, w, NOMINAL[i % len(NOMINAL)], psf, with_saa) for i in range(procs)]
     t0 = time.perf_counter()
-    if cores == 1:
-        res = [scipy_port.timed_sample(args[0])]
+    if procs == 1:
+        res = [scipy_port.full_size_frame_sample(args[0])]
     else:
-        ctx = mp.get_context("fork")
-        with ctx.Pool(cores) as pool:
-            res = pool.map(scipy_port.timed_sample, args)
+        with mp.get_context("fork").Pool(procs) as pool:
+            res = pool.map(scipy_port.full_size_frame_sample, args)
     wall = time.perf_counter() - t0
-    hr_px = 4.0 * h * w
-    rate = 0.0
-    for t_saa, t_iter in res:
-        rate += hr_px / (t_saa + 50.0 * t_iter) / 1e6
-    return rate, wall, res
+    if with_saa:
+        t_saa_frame = statistics.mean(r[0] for r in res)
+    hr_mpix = 4.0 * h * w / 1e6
+    rate = sum(hr_mpix / (n * t_saa_frame + iters * (n * r[1] + r[2])) for r in res)
+    return {"rate": rate, "wall": wall, "t_saa_frame": t_saa_frame, "t_frame_iteration": statistics.mean(r[1] for r in res),
+            "t_update": statistics.mean(r[2] for r in res), "procs": procs}
 
 
 def run_reference_arm(args):
-    """--impl reference: the CPU port with all host threads, each step a bounded sample."""
+    """--impl reference: the reference's CPU path (oracle/scipy_port.py: the scipy calls of mono_cal_target/run_sr.py:157-209)
+    on all host cores.  Every step runs, on every core at once, the work of one frame of one IBP iteration at the FULL
+    4x1536x2048 -> 3072x4096 size; value = sum over the cores of H*W / (n*t_saa_frame + K*(n*t_frame_iteration + t_update))."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return 0
     os.environ.setdefault("OMP_NUM_THREADS", "1")
     n, h, w, iters = WORKLOADS[args.workload]
     cores = os.cpu_count() or 1
-    sh, sw, k_iter = 384, 512, 2
-    vals, walls = [], []
-    for i in range(args.warmup + args.steps):
-        rate, wall, _ = cpu_sample(n, sh, sw, k_iter, cores, seed0=459 + 100 * i)
-        if i >= args.warmup:
-            vals.append(rate)
-            walls.append(wall)
-    value = statistics.mean(vals)
-    sample = (f"each step: {cores} concurrent single-threaded processes, each SAA + {k_iter} IBP iterations on "
-              f"{n}x{sh}x{sw} S1-noise frames (float64, scipy); per-iteration cost extrapolated to the 50-iteration job")
+    procs = cpu_procs(cores)
+    calib = cpu_full_size_step(n, h, w, iters, procs, True, 459)            # SAA piece + first warm-up
+    log(f"reference arm: {procs} workers, t_saa_frame {calib['t_saa_frame']:.2f} s, t_frame_iteration {calib['t_frame_iteration']:.2f} s")
+    steps = []
+    for i in range(max(args.warmup - 1, 0) + args.steps):
+        r = cpu_full_size_step(n, h, w, iters, procs, False, 1000 + 100 * i, calib["t_saa_frame"])
+        if i >= max(args.warmup - 1, 0):
+            steps.append(r)
+    value = statistics.mean(r["rate"] for r in steps)
+    t_fi = statistics.mean(r["t_frame_iteration"] for r in steps)
+    t_up = statistics.mean(r["t_update"] for r in steps)
+    sample = (f"each step: {procs} concurrent single-threaded processes (host has {cores} cores), each the scipy calls of ONE frame of ONE "
+              f"IBP iteration on full-size arrays ({2*h}x{2*w} float64 HR, {h}x{w} LR): {t_fi:.2f} s per frame-iteration, "
+              f"{calib['t_saa_frame']:.2f} s per SAA frame (sampled once), {t_up:.3f} s per update; job = {n}*t_saa + {iters}*({n}*t_fi + t_upd) "
+              f"= {n * calib['t_saa_frame'] + iters * (n * t_fi + t_up):.0f} s per core")
     line = {
         "impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-        "warmup": args.warmup, "ms_per_step": 1e3 * statistics.mean(walls), "higher_is_better": True, "scaling": "weak",
+        "warmup": args.warmup, "ms_per_step": 1e3 * statistics.mean(r["wall"] for r in steps), "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"config1: {n}x{h}x{w} mono frames -> {2*h}x{2*w}, Gaussian 7x7 PSF, SAA + {iters} IBP iterations",
-                   "n_frames": n, "lr_shape": [h, w], "hr_shape": [2 * h, 2 * w], "ibp_iterations": iters, "psf": "gaussian7"},
-        "cpu_baseline": {"value": value, "unit": UNIT, "cores": cores, "kind": "port", "sample": sample},
+        "config": workload_config(n, h, w, iters, args.gpus),
+        "cpu_baseline": {"value": value, "unit": UNIT, "cores": procs, "kind": "port", "sample": sample,
+                         "one_core_job_seconds_under_load": n * calib["t_saa_frame"] + iters * (n * t_fi + t_up)},
         "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -204,6 +253,142 @@ def run_reference_arm(args):
 # ------------------------------------------------------------------------------------------------
 # B200 arm
 # ------------------------------------------------------------------------------------------------
+CALIBRATED = [(0.47225, -0.43385), (0.4897, 0.4641), (-0.4798, -0.4553), (-0.4856, 0.4369)]   # rgb_cal_target/results/*/shifts.json
+MONOCAL = [(0.0, 0.0)] + NOMINAL                                                              # mono_cal_target/run_sr.py:60-66
+FFMA2_PEAK_TMAC = 35.7      # tools/probes/ffma2_probe.cu on B200: packed fma.rn.f32x2 issue ceiling
+
+
+def committed_psfs():
+    """The reference-generated measured PSFs (load_measured_psf on the shipped pinhole crops, PSF_HALFWIDTH 3 and 15),
+    committed under tests/golden by tests/golden/make_golden.py."""
+    g = np.load(os.path.join(ROOT, "tests", "golden", "g_psf.npz"))
+    return g["k7"], g["k31"]
+
+
+def time_config(sr459, torch, name, h, w, shifts, psf, iters, reps, peak, seed, desc):
+    """SAA + K iterations of one configuration, device-resident, each stage one CUDA-graph replay, CUDA events."""
+    n, H, W = len(shifts), 2 * h, 2 * w
+    rng = np.random.default_rng(seed)
+    frames = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in range(n)]
+    plan = sr459.Plan(n, h, w, shifts, psf)
+    hr = torch.empty((H, W), dtype=torch.float32, device="cuda")
+    lib = sr459._lib.load()
+    plan.saa(frames, out=hr); plan.ibp_(frames, hr, min(iters, 2), want_errors=False)      # lazy scratch, outside capture
+    torch.cuda.synchronize()
+    cap = torch.cuda.Stream()
+    g_saa, g_ibp = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+    c0 = lib.sr459_launch_count()
+    with torch.cuda.graph(g_saa, stream=cap):
+        plan.saa(frames, out=hr)
+    c1 = lib.sr459_launch_count()
+    with torch.cuda.graph(g_ibp, stream=cap):
+        plan.ibp_(frames, hr, iters, want_errors=False)
+    c2 = lib.sr459_launch_count()
+    ev = [torch.cuda.Event(enable_timing=True) for _ in range(3)]
+    saa_ms, ibp_ms = [], []
+    for r in range(reps + 1):
+        ev[0].record(); g_saa.replay(); ev[1].record(); g_ibp.replay(); ev[2].record()
+        torch.cuda.synchronize()
+        if r:                                        # replay 0 is the warm-up
+            saa_ms.append(ev[0].elapsed_time(ev[1])); ibp_ms.append(ev[1].elapsed_time(ev[2]))
+    errs = plan.errors(iters)
+    plan.close()
+    t_saa, t_ibp = statistics.median(saa_ms), statistics.median(ibp_ms)
+    us_iter = 1e3 * t_ibp / iters
+    alg_iter = (8 + n) * H * W
+    return {
+        "workload": desc, "n_frames": n, "hr_shape": [H, W], "ibp_iterations": iters, "integer_hr_shifts": bool(sr459.Plan.shifts_are_integer(shifts)),
+        "saa_us": 1e3 * t_saa, "us_per_iteration": us_iter, "job_ms": t_saa + t_ibp,
+        "hr_mpix_per_s": H * W / 1e6 / ((t_saa + t_ibp) / 1e3),
+        "launches_per_iteration": (c2 - c1 - 1) / iters, "launches_saa": c1 - c0,
+        "roofline": {"bound": "hbm", "algorithmic_bytes_per_iteration": alg_iter, "achieved": alg_iter / (us_iter * 1e-6) / 1e9,
+                     "peak": peak, "unit": "GB/s", "frac": alg_iter / (us_iter * 1e-6) / 1e9 / peak},
+        "final_mse": errs[-1], "mse_monotone": all(b <= a for a, b in zip(errs, errs[1:])),
+    }
+
+
+def stream_record(sr459, torch, n, h, w, psf, iters):
+    """Config 5: streaming burst mode through driver.BurstStream (uint8 frames in, uint8 HR image out, PCIe both ways)."""
+    from sr459.driver import BurstStream, play_camera
+    rng = np.random.default_rng(4595)
+    pool = [rng.integers(0, 256, (h, w), dtype=np.uint8) for _ in range(8)]
+    bs = BurstStream(n, h, w, NOMINAL, psf, iters, depth=3, use_graph=True)
+    for _ in range(3):
+        for k in range(n):
+            bs.push_frame(pool[k])
+        bs.wait_result()
+    out = {"workload": f"config5: continuous {n}-frame uint8 sets {h}x{w} -> {2*h}x{2*w} uint8, Gaussian 7x7, SAA + {iters} IBP iterations; "
+                       "latency = commit of a set's last frame -> uint8 HR image on the host",
+           "h2d_bytes_per_set": bs.h2d_bytes, "d2h_bytes_per_set": bs.d2h_bytes}
+    for tag, sets, fps in (("free_running", 100, 0.0), ("camera_48fps", 16, 48.0)):
+        lat, wall = play_camera(bs, pool, sets, fps)
+        ms = sorted(1e3 * x for x in lat)
+        out[tag] = {"sets": sets, "latency_ms_p50": statistics.median(ms), "latency_ms_p99": ms[min(len(ms) - 1, int(0.99 * len(ms)))],
+                    "hr_frames_per_s": sets / wall, "hr_mpix_per_s": sets * 4.0 * h * w / 1e6 / wall}
+    bs.close()
+    return out
+
+
+def parity_spot_check(sr459, iters):
+    """Outside every timed region: the kernels the bench runs (auto path) against the float64 oracle at the benchmarked
+    iteration count on a small frame set.  The oracle is the checker here, never the thing measured."""
+    from oracle import sr_oracle as O
+    rng = np.random.default_rng(459)
+    lrs = [rng.uniform(0, 255, (96, 128)) for _ in NOMINAL]
+    psf = O.make_gaussian_psf()
+    saa_o = O.shift_and_add_integer(lrs, NOMINAL)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=iters)
+    hr, errs = sr459.ibp(lrs, NOMINAL, sr459.make_gaussian_psf(), sr459.shift_and_add(lrs, NOMINAL), n_iter=iters)
+    d = float(np.max(np.abs(hr - hr_o)))
+    rel = float(np.max(np.abs(np.array(errs) / np.array(e_o) - 1.0)))
+    return {"shape": "4x96x128 S1 noise", "iterations": iters, "max_abs_vs_oracle_dn": d, "mse_rel_vs_oracle": rel,
+            "ok": bool(d <= 0.0255 and rel <= 1e-4)}
+
+
+def bands_record(sr459, torch, dist, world, rank, peak, k31):
+    """Config 4 under torchrun: ONE 3072x4096 HR image as `world` row bands, 31x31 measured PSF, 200 iterations, against the
+    same job on one GPU (every rank runs that too, to check its own band bit for bit)."""
+    from sr459.bands import BandPlan
+    h, w, K = 1536, 2048, 200
+    rng = np.random.default_rng(4594)                       # identical on every rank
+    lrs = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in NOMINAL]
+    out = {}
+    for tag, psf in (("measured31", k31), ("gaussian7", sr459.make_gaussian_psf())):
+        full = sr459.Plan(4, h, w, NOMINAL, psf)
+        saa = full.saa(lrs)
+        ref = saa.clone()
+        full.ibp_(lrs, ref, 2, want_errors=False)
+        ref.copy_(saa)
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        torch.cuda.synchronize()
+        e0.record(); ref_errs = full.ibp_(lrs, ref, K); e1.record()
+        torch.cuda.synchronize()
+        single_ms = e0.elapsed_time(e1)
+        bp = BandPlan(4, h, w, NOMINAL, psf, rank, world)
+        lay = bp.layout
+        lr_local = [f[lay.lr_lo:lay.lr_hi].contiguous() for f in lrs]
+        res = errs = None
+        for k_iter in (4, K):                               # warm-up (NCCL channels, plan scratch), then the measurement
+            hr_local = saa[lay.hr_lo:lay.hr_hi].clone()
+            dist.barrier(); torch.cuda.synchronize()
+            res, errs = bp.run(lr_local, hr_local, k_iter, graph=True)
+            torch.cuda.synchronize()
+        d = float((res[lay.owned] - ref[lay.own_y0:lay.own_y1]).abs().max().item())
+        t = torch.tensor([bp.last_loop_ms, d, single_ms], dtype=torch.float64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        ms, dmax, single = [float(x) for x in t.tolist()]
+        out[tag] = {
+            "workload": f"config4: one {2*h}x{2*w} HR image, 4 frames, {tag} PSF, {K} IBP iterations, {world} row bands, "
+                        f"halo {lay.halo} rows, {bp.exchange_kind}",
+            "us_per_iteration": 1e3 * ms / K, "single_gpu_us_per_iteration": 1e3 * single / K,
+            "speedup_vs_single_gpu": single / ms, "efficiency": single / ms / world,
+            "max_abs_vs_single_gpu": dmax, "mse_rel_vs_single_gpu": float(np.max(np.abs(np.array(errs) / np.array(ref_errs) - 1.0))),
+            "halo_bytes_per_iteration_per_neighbour": lay.halo * lay.W * 4, "hr_mpix_per_s": 4.0 * h * w / 1e6 / (ms / 1e3),
+        }
+        bp.close(); full.close()
+    return out
+
+
 def run_b200_arm(args):
     import torch
     import torch.distributed as dist
@@ -226,8 +411,7 @@ def run_b200_arm(args):
     psf = sr459.make_gaussian_psf()
     ring = 4
     rng = np.random.default_rng(459 + 1000 * rank)
-    host_sets = [torch.from_numpy(rng.uniform(0, 255, (n, h, w)).astype(np.float32)).pin_memory() for _ in range(ring)]
-    dev_sets = [hs.cuda() for hs in host_sets]
+    dev_sets = [torch.from_numpy(rng.uniform(0, 255, (n, h, w)).astype(np.float32)).cuda() for _ in range(ring)]
     plan = sr459.Plan(n, h, w, NOMINAL, psf)
     hr = torch.empty((H, W), dtype=torch.float32, device="cuda")
 
@@ -236,7 +420,7 @@ def run_b200_arm(args):
         plan.saa(frames, out=hr)
         plan.ibp_(frames, hr, iters, want_errors=False)
 
-    # One captured launch sequence per stage and ring slot (CUDA graphs: the 55 launches of a job replay without
+    # One captured launch sequence per stage and ring slot (CUDA graphs: the launches of a job replay without
     # host launch gaps); the stage events are recorded between the replays, on the same stream.
     graphs = []
 
@@ -289,105 +473,133 @@ def run_b200_arm(args):
     ibp_ms = sum(e[1].elapsed_time(e[2]) for e in evs) / args.steps
     errs = plan.errors(iters)
 
-    # ---- e2e through the host API ------------------------------------------------------------
-    pipe = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="f32", out_dtype="f32", use_graph=True)
-    sets = [host_sets[i % ring] for i in range(args.steps)]
-    pipe.run([host_sets[i % ring] for i in range(max(args.warmup, 3))])
-    barrier()
-    t0 = time.perf_counter()
-    pipe.run(sets)
-    torch.cuda.synchronize()
-    e2e_s = time.perf_counter() - t0
-    lat = pipe.run_latency(sets[: min(5, len(sets))])
-    barrier()
-    # the headline e2e: the same jobs in run_sr.py's file formats, uint8 frames in (load_gray, :73-75), uint8 HR image out (:303)
+    # ---- e2e through the host API: run_sr.py's file formats, uint8 frames in (load_gray, :73-75), uint8 HR image out (:303) ----
     pipe8 = FrameSetPipeline(n, h, w, NOMINAL, psf, iters, depth=3, in_dtype="u8", out_dtype="u8", use_graph=True)
     sets8 = [torch.from_numpy(rng.integers(0, 256, (n, h, w), dtype=np.uint8)).pin_memory() for _ in range(ring)]
     pipe8.run([sets8[i % ring] for i in range(max(args.warmup, 3))])
-    barrier()
-    t0 = time.perf_counter()
-    pipe8.run([sets8[i % ring] for i in range(args.steps)])
-    torch.cuda.synchronize()
-    e2e8_s = time.perf_counter() - t0
+    e2e_runs = []
+    for rep in range(3):                              # median of three timed runs of `steps` jobs each
+        barrier()
+        t0 = time.perf_counter()
+        pipe8.run([sets8[i % ring] for i in range(args.steps)])
+        torch.cuda.synchronize()
+        e2e_runs.append(time.perf_counter() - t0)
+    e2e8_s = statistics.median(e2e_runs)
     lat8 = pipe8.run_latency([sets8[i % ring] for i in range(min(5, args.steps))])
     barrier()
     clocks = sampler.stop() if rank == 0 else None
 
-    t = torch.tensor([total_ms, e2e_s * 1e3, ibp_ms, e2e8_s * 1e3], dtype=torch.float64, device="cuda")
+    t = torch.tensor([total_ms, ibp_ms, e2e8_s * 1e3, max(e2e_runs) * 1e3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    total_ms, e2e_ms, ibp_ms_max, e2e8_ms = [float(x) for x in t.tolist()]
+    total_ms, ibp_ms_max, e2e8_ms, e2e8_worst_ms = [float(x) for x in t.tolist()]
 
     hr_mpix = H * W / 1e6
     value = world * args.steps * hr_mpix / (total_ms / 1e3)
-    e2e_value = world * args.steps * hr_mpix / (e2e_ms / 1e3)
 
     peak, peak_src = measured_peak()
     alg_iter = (8 + n) * H * W                       # bytes: hr in 4 + hr out 4 + n LR frames at 1/4 density
     k_ms = ibp_ms / iters
     achieved = alg_iter / (k_ms * 1e-3) / 1e9
-    traffic = None
+    traffic, traffic_src = None, None
     try:
         with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
-            traffic = json.load(f).get("k_ibp_stream_bytes_per_launch")
+            tj = json.load(f)
+            traffic, traffic_src = tj.get("k_ibp_stream_bytes_per_launch"), tj.get("source")
     except Exception:
         pass
     alg_job = ((n + 4) + iters * (8 + n)) * H * W
+    kernel_bytes = 9 * H * W
 
     line = {
         "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
-        "config": {"workload": f"config1: {n}x{h}x{w} mono frames -> {H}x{W}, Gaussian 7x7 PSF, nominal +-0.5 px shifts, "
-                               f"SAA + {iters} IBP iterations per step; one independent frame set per step per GPU; each stage replayed as a CUDA graph",
-                   "n_frames": n, "lr_shape": [h, w], "hr_shape": [H, W], "ibp_iterations": iters, "psf": "gaussian7",
-                   "cache": f"ring of {ring} distinct frame sets ({ring * n * h * w * 4 >> 20} MiB LR) + {3 * H * W * 4 >> 20} MiB HR "
-                            "working set per job, larger than the 126 MB L2; no explicit flush",
-                   "parallelism": f"batch-dp{world}"},
+        "config": workload_config(n, h, w, iters, world),
         "stage_ms": {"saa": saa_ms, "ibp": ibp_ms, "ibp_per_iteration": k_ms},
         "job_hbm_frac": alg_job / (total_ms / args.steps * 1e-3) / 1e9 / peak,
         "roofline": {"bound": "hbm", "kernel": "k_ibp_stream (fused IBP iteration: register-streaming warps, TMA row ring; rank-1 PSF, integer HR shifts)",
-                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                     "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic, "traffic_source": traffic_src,
                      "algorithmic_bytes_per_launch": alg_iter, "peak_source": peak_src, "launch_ms": k_ms,
                      "dram_achieved": (traffic / (k_ms * 1e-3) / 1e9) if traffic else None,
-                     "kernel_bytes_per_launch": 9 * H * W,
+                     "kernel_bytes_per_launch": kernel_bytes, "kernel_bytes_frac": kernel_bytes / (k_ms * 1e-3) / 1e9 / peak,
                      "note": "frac is SURVEY 8(d)'s algorithmic bytes, (8 + n) per HR pixel, over the measured DRAM copy peak; it can exceed 1 "
                              "because the kernel reads ONE pre-summed LR plane instead of the n frames (kernel_bytes_per_launch = 9 per HR "
-                             "pixel) and part of the hr ping-pong pair (96 MiB) stays in the 126 MB L2: ncu counts `traffic` DRAM bytes per "
-                             "launch (cold L2), dram_achieved = traffic / launch time"},
+                             "pixel; kernel_bytes_frac is the same fraction on those bytes) and part of the hr ping-pong pair (96 MiB) stays "
+                             "in the 126 MB L2: ncu counts `traffic` DRAM bytes per launch (cold L2), dram_achieved = traffic / launch time"},
         "e2e": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
                 "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat8),
+                "runs": 3, "worst_run_value": world * args.steps * hr_mpix / (e2e8_worst_ms / 1e3),
                 "api": "sr459.driver.FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): run_sr.py's own I/O formats -- pinned uint8 frames in "
                        "(load_gray, :73-75), uint8 HR image out (clip + truncation, :303), conversions on the device; 3 jobs in flight, "
-                       "one CUDA-graph replay per job"},
-        "e2e_f32": {"value": e2e_value, "unit": UNIT, "h2d_bytes_per_step": pipe.h2d_bytes, "d2h_bytes_per_step": pipe.d2h_bytes,
-                    "ms_per_step": e2e_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat),
-                    "api": "the same pipeline with pinned float32 frames in and the float32 HR image out (100 MB of PCIe traffic per job)"},
+                       "one CUDA-graph replay per job; median of 3 runs of `steps` jobs (max over ranks of each rank's median)"},
         "gpu_launches": int(launches),
         "final_mse": errs[-1],
+        "mse_monotone": all(b < a for a, b in zip(errs, errs[1:])),
         "clocks": clocks,
     }
+    pipe8.close()
+    plan.close()
+    del graphs, dev_sets, sets8, hr
+    torch.cuda.empty_cache()
 
+    # ---- the other BASELINE configurations, same run (rank 0 measures the single-GPU ones) -------------------
+    if not args.no_configs:
+        k7, k31 = committed_psfs()
+        cfg = {}
+        if rank == 0:
+            cfg["c2"] = time_config(sr459, torch, "c2", 768, 1024, CALIBRATED, k7, 50, 5, peak, 4592,
+                                    "config2: rgb_cal_target red-Bayer 4x768x1024 -> 1536x2048, calibrated fractional shifts, measured 7x7 PSF "
+                                    "(tests/golden/g_psf.npz k7, generated by the reference's load_measured_psf), SAA + 50 iterations")
+            cfg["monocal5"] = time_config(sr459, torch, "monocal5", 1536, 2048, MONOCAL, psf, 80, 3, peak, 4596,
+                                          "mono_cal_target's own geometry: centre + 4 shifted frames (two parity lattices) 5x1536x2048 -> 3072x4096, "
+                                          "Gaussian 7x7, SAA + 80 iterations (run_sr.py:56-66)")
+            cfg["c1_measured7"] = time_config(sr459, torch, "c1_measured7", 1536, 2048, NOMINAL, k7, 50, 3, peak, 4597,
+                                              "config1 with --psf measured: 4x1536x2048 -> 3072x4096, nominal shifts, measured 7x7 PSF (19 non-zero taps), SAA + 50 iterations")
+            c4 = time_config(sr459, torch, "c4", 1536, 2048, NOMINAL, k31, 200, 2, peak, 4594,
+                             "config4 on ONE GPU: 4x1536x2048 -> 3072x4096, measured 31x31 PSF (tests/golden/g_psf.npz k31: 830 non-zero taps), 200 iterations")
+            macs = 2.0 * 961 * (H * W / 4)                 # forward blur at the sampled sites + transposed blur of the site plane
+            c4["fma"] = {"bound": "fp32-fma", "useful_mac_per_iteration": macs, "achieved_tmac_s": macs / (c4["us_per_iteration"] * 1e-6) / 1e12,
+                         "peak_tmac_s": FFMA2_PEAK_TMAC, "frac": macs / (c4["us_per_iteration"] * 1e-6) / 1e12 / FFMA2_PEAK_TMAC,
+                         "peak_source": "tools/probes/ffma2_probe.cu (packed fma.rn.f32x2 issue ceiling measured on B200)"}
+            cfg["c4"] = c4
+            cfg["c5"] = stream_record(sr459, torch, n, h, w, psf, iters)
+            cfg["c3"] = {"workload": "config3: 64 independent config-1 frame sets, data-parallel: this line's own `value` / `e2e` "
+                                     "(one set per step per GPU, no data-path collective)", "see": "value, e2e, n_gpus"}
+        if world > 1:
+            barrier()
+            b = bands_record(sr459, torch, dist, world, rank, peak, k31)
+            if rank == 0:
+                cfg["bands"] = b
+        line["configs"] = cfg
+
+    if rank == 0 and not args.no_cpu:
+        line["parity"] = parity_spot_check(sr459, iters)
+        line["parity_checked"] = bool(line["parity"]["ok"] and line["mse_monotone"])
     if rank == 0 and world == 1 and not args.no_cpu:
         cores = os.cpu_count() or 1
         os.environ.setdefault("OMP_NUM_THREADS", "1")
-        sh, sw, k_iter = 768, 1024, 2
-        rate1, wall1, res1 = cpu_sample(n, sh, sw, k_iter, 1)
-        rate_all, wall_all, _ = cpu_sample(n, 384, 512, k_iter, cores)
+        one = cpu_full_size_step(n, h, w, iters, 1, True, 459)
+        procs = cpu_procs(cores)
+        allc = cpu_full_size_step(n, h, w, iters, procs, True, 4590)
         line["cpu_baseline"] = {
-            "value": rate_all, "unit": UNIT, "cores": cores, "kind": "port",
-            "one_core_value": rate1,
-            "sample": (f"all-core: {cores} concurrent single-threaded processes, each SAA + {k_iter} IBP iterations on {n}x384x512 "
-                       f"S1-noise frames; one-core: the same on {n}x{sh}x{sw} frames ({res1[0][0]:.1f} s SAA, {res1[0][1]:.1f} s/iteration); "
-                       "float64 scipy calls identical to the reference's; per-iteration cost extrapolated to the 50-iteration job"),
+            "value": allc["rate"], "unit": UNIT, "cores": procs, "kind": "port",
+            "one_core_value": one["rate"],
+            "one_core_job_seconds": n * one["t_saa_frame"] + iters * (n * one["t_frame_iteration"] + one["t_update"]),
+            "sample": (f"FULL-SIZE sample ({n}x{h}x{w} -> {H}x{W}, float64, the reference's scipy calls): the work of ONE frame -- zoom + shift "
+                       f"(SAA) and forward_model + residual + back_project (one IBP iteration) -- on 1 core alone ({one['t_saa_frame']:.2f} s + "
+                       f"{one['t_frame_iteration']:.2f} s) and on {procs} cores at once ({allc['t_saa_frame']:.2f} s + {allc['t_frame_iteration']:.2f} s each; "
+                       f"host has {cores}); job = {n}*t_saa + {iters}*({n}*t_iter + t_update), nothing extrapolated across image sizes"),
         }
     if rank == 0:
         emit(line)
-    pipe.close()
-    pipe8.close()
-    plan.close()
     if world > 1:
-        dist.destroy_process_group()
+        # NCCL work captured in CUDA graphs (the band loop) keeps destroy_process_group from returning: everything is
+        # measured and printed, so synchronise and leave
+        torch.cuda.synchronize()
+        dist.barrier()
+        sys.stdout.flush(); sys.stderr.flush()
+        os._exit(0)
     return 0
 
 
@@ -398,7 +610,8 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c1")
-    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and oracle spot-check legs")
+    ap.add_argument("--no-configs", action="store_true", help="skip the `configs` object (other BASELINE configurations)")
     args = ap.parse_args()
     guard_stdout()
     if args.impl == "reference":

@@ -119,6 +119,7 @@ class BandPlan:
                                                     sh.ctypes.data_as(C.POINTER(C.c_double)), kp, kh, kw,
                                                     float(step), float(clip_lo), float(clip_hi), int(rank), int(world)))
         self._h = handle
+        self.exchange_kind = "halo rows exchanged by NCCL send/recv after every iteration (kernels + send/recv captured in one CUDA graph)"
         out = (C.c_int * 8)()
         _lib.check(self._lib.sr459_band_layout(self._h, out))
         self.layout = BandLayout(self.h, self.w, (int(out[6]) - 2) // 2, int(rank), int(world), int(factor))

@@ -292,3 +292,43 @@ class BurstStream:
         idx = self.sets_out
         self.sets_out += 1
         return idx, slot["host_out"], lat
+
+
+def play_camera(bs: "BurstStream", frame_pool: Sequence[np.ndarray], n_sets: int, fps: float = 0.0, on_result=None):
+    """Drive a BurstStream like a camera would (api/allied_vision_camera.py:90-115): a producer thread writes one uint8
+    frame per 1/fps seconds (fps 0 = as fast as the consumer drains) into the pinned ring and commits it; the calling
+    thread collects the HR images.  Returns (latencies in seconds -- commit of a set's LAST frame to its uint8 HR image
+    being on the host --, wall seconds for all sets)."""
+    import threading
+    n = bs.n
+    sem = threading.Semaphore(bs.depth - 1)              # the producer may run depth-1 sets ahead of the consumer
+    period = 1.0 / fps if fps and fps > 0 else 0.0
+
+    def producer():
+        t_next = time.perf_counter()
+        for f in range(n_sets * n):
+            if f % n == 0:
+                sem.acquire()
+            if period:
+                t_next += period
+                while time.perf_counter() < t_next:
+                    time.sleep(0.0002)
+            bs.frame_buffer().numpy()[...] = frame_pool[f % len(frame_pool)]   # the camera's DMA into the pinned buffer
+            bs.commit_frame()
+
+    base = bs.sets_out
+    lat = []
+    th = threading.Thread(target=producer, daemon=True)
+    t0 = time.perf_counter()
+    th.start()
+    for s in range(n_sets):
+        while bs.sets_out >= bs.sets_committed:          # the set has not been committed yet
+            time.sleep(0.0001)
+        idx, img, l = bs.wait_result()
+        lat.append(l)
+        if on_result:
+            on_result(idx - base, img)
+        sem.release()
+    wall = time.perf_counter() - t0
+    th.join()
+    return lat, wall

@@ -366,6 +366,12 @@ class Plan:
 
     __del__ = close
 
+    @staticmethod
+    def shifts_are_integer(shifts_yx, factor=UPSAMPLE_FACTOR) -> bool:
+        """True if every shift is a whole number of HR pixels (the fused integer kernels apply)."""
+        s = np.asarray(shifts_yx, dtype=np.float64) * factor
+        return bool(np.all(s == np.rint(s)))
+
     @property
     def is_integer(self) -> bool:
         return bool(self._lib.sr459_plan_is_integer(self._h))

@@ -88,3 +88,34 @@ def timed_sample(args):
         hr, _ = pipe.iterate(frames, hr)
     t2 = time.perf_counter()
     return (t1 - t0, (t2 - t1) / max(k_iter, 1))
+
+
+def full_size_frame_sample(args):
+    """Worker for bench.py: the reference's work for ONE FRAME of a job at the job's FULL size, timed piecewise.
+
+    A job is n * [zoom + shift] (SAA, run_sr.py:181-187) followed by K * (n * [forward_model + residual +
+    back_project] + update/clip) (run_sr.py:197-208); every frame and every iteration repeats the same scipy calls on
+    arrays of the same shape, so   t_job = n * t_saa_frame + K * (n * t_frame_iter + t_update)   with nothing
+    extrapolated across image sizes (scipy's cost per pixel grows with the working set, which is why the size must be
+    the real one).
+
+    args = (seed, h, w, shift_yx, psf, do_saa); returns (t_saa_frame or None, t_frame_iter, t_update)."""
+    seed, h, w, s, psf, do_saa = args
+    rng = np.random.default_rng(seed)
+    frame = rng.uniform(0, 255, (h, w))
+    pipe = ScipyPipeline([s], psf)
+    t_saa = None
+    if do_saa:
+        t0 = time.perf_counter()
+        hr = _ndi.shift(_ndi.zoom(frame, pipe.f, order=3), (s[0] * pipe.f, s[1] * pipe.f), order=3, mode="nearest")
+        t_saa = time.perf_counter() - t0
+    else:
+        hr = rng.uniform(0, 255, (pipe.f * h, pipe.f * w))
+    t0 = time.perf_counter()
+    err = frame - pipe.simulate(hr, s)
+    mse = float(np.mean(err * err))
+    corr = pipe.project_back(err, s, hr.shape)
+    t1 = time.perf_counter()
+    hr = np.clip(hr + pipe.step * corr / 4.0, *pipe.clip)
+    t2 = time.perf_counter()
+    return (t_saa, t1 - t0, t2 - t1, mse)

@@ -15,8 +15,6 @@ import json
 import os
 import statistics
 import sys
-import threading
-import time
 
 import numpy as np
 
@@ -39,46 +37,23 @@ def main():
 
     import torch
     import sr459
-    from sr459.driver import BurstStream
+    from sr459.driver import BurstStream, play_camera
     n, h, w = 4, args.h, args.w
     psf = sr459.make_gaussian_psf()
     rng = np.random.default_rng(459)
     pool = [rng.integers(0, 256, (h, w), dtype=np.uint8) for _ in range(8)]      # the "camera" cycles through 8 frames
     bs = BurstStream(n, h, w, NOMINAL, psf, args.iters, depth=args.depth, use_graph=args.graph)
-    sem = threading.Semaphore(args.depth - 1)            # the producer may run depth-1 sets ahead of the consumer
-    period = 1.0 / args.fps if args.fps > 0 else 0.0
-    total_frames = args.sets * n
-
-    def producer():
-        t_next = time.perf_counter()
-        for f in range(total_frames):
-            if f % n == 0:
-                sem.acquire()
-            if period:
-                t_next += period
-                while time.perf_counter() < t_next:
-                    time.sleep(0.0002)
-            bs.frame_buffer().numpy()[...] = pool[f % len(pool)]      # the camera's DMA into the pinned buffer
-            bs.commit_frame()
-
     for warm in range(2):                                # warm-up sets
         for k in range(n):
             bs.push_frame(pool[k])
         bs.wait_result()
-    lat, keep = [], {}
-    th = threading.Thread(target=producer, daemon=True)
-    t0 = time.perf_counter()
-    th.start()
-    for s in range(args.sets):
-        while bs.sets_out >= bs.sets_committed:           # the set has not been committed yet
-            time.sleep(0.0001)
-        idx, img, l = bs.wait_result()
-        lat.append(l)
+    keep = {}
+
+    def on_result(s, img):
         if args.check and s < 2:
             keep[s] = img.clone().numpy()
-        sem.release()
-    wall = time.perf_counter() - t0
-    th.join()
+
+    lat, wall = play_camera(bs, pool, args.sets, args.fps, on_result)
     lat_ms = sorted(1e3 * x for x in lat)
     line = {
         "workload": f"config5: continuous {n}-frame uint8 sets {h}x{w} -> {2*h}x{2*w} uint8, Gaussian 7x7 PSF, SAA + {args.iters} IBP iterations",
