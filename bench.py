@@ -273,7 +273,7 @@ def time_config(sr459, torch, name, h, w, shifts, psf, iters, reps, peak, seed, 
     plan = sr459.Plan(n, h, w, shifts, psf)
     hr = torch.empty((H, W), dtype=torch.float32, device="cuda")
     lib = sr459._lib.load()
-    plan.saa(frames, out=hr); plan.ibp_(frames, hr, min(iters, 2), want_errors=False)      # lazy scratch, outside capture
+    plan.saa(frames, out=hr); plan.ibp_(frames, hr, iters, want_errors=False)      # lazy scratch (sized by K), outside capture
     torch.cuda.synchronize()
     cap = torch.cuda.Stream()
     g_saa, g_ibp = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
@@ -357,7 +357,7 @@ def bands_record(sr459, torch, dist, world, rank, peak, k31):
         full = sr459.Plan(4, h, w, NOMINAL, psf)
         saa = full.saa(lrs)
         ref = saa.clone()
-        full.ibp_(lrs, ref, 2, want_errors=False)
+        full.ibp_(lrs, ref, K, want_errors=False)               # warm-up: lazy scratch sized by K
         ref.copy_(saa)
         e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
         torch.cuda.synchronize()
