@@ -73,6 +73,13 @@ _SIGNATURES = {
     "sr459_saa_ibp": (_I, [_P, _PP, _P, _P, _I, _PD, _P]),
     "sr459_band_plan_create": (_I, [_PP, _I, _I, _I, _I, _I, _PD, _PD, _I, _I, _D, _D, _D, _I, _I]),
     "sr459_band_layout": (_I, [_P, _PI]),
+    "sr459_band_layout_ext": (_I, [_P, _PI]),
+    "sr459_band_buffers": (_I, [_P, _PP, _PP, C.POINTER(C.c_int64)]),
+    "sr459_band_export": (_I, [_P, C.c_char_p, _PP]),
+    "sr459_band_attach": (_I, [_P, C.c_char_p, _P, _I, C.c_char_p, _P, _I]),
+    "sr459_band_current": (_I, [_P, _I]),
+    "sr459_band_saa": (_I, [_P, _PP, _P]),
+    "sr459_band_run": (_I, [_P, _PP, _I, _P]),
     "sr459_band_begin": (_I, [_P, _PP, _I, _P]),
     "sr459_band_iterate": (_I, [_P, _PP, _P, _P, _I, _P]),
     "sr459_band_errors": (_I, [_P, _I, _PD, _P]),

@@ -1,5 +1,5 @@
 // api.cu -- the C ABI of include/sr459.h: plans, stage scheduling, stand-alone operators.
-#include "internal.h"
+#include "plan.h"
 
 #include <math.h>
 #include <stdarg.h>
@@ -45,42 +45,6 @@ static double np_pairwise_sum(const double* a, size_t n) {
     return np_pairwise_sum(a, n2) + np_pairwise_sum(a + n2, n - n2);
 }
 
-// The caller's current device is restored when an entry point returns: a plan may live on any device of the
-// process, and plan_free is reached from Python's garbage collector at arbitrary times.
-struct DeviceGuard {
-    int prev = -1;
-    bool ok = true;
-    explicit DeviceGuard(int dev) {
-        if (cudaGetDevice(&prev) != cudaSuccess) prev = -1;
-        if (prev == dev) prev = -1;                       // nothing to switch, nothing to restore
-        else ok = (cudaSetDevice(dev) == cudaSuccess);
-    }
-    ~DeviceGuard() { if (prev >= 0) cudaSetDevice(prev); }
-    DeviceGuard(const DeviceGuard&) = delete;
-    DeviceGuard& operator=(const DeviceGuard&) = delete;
-};
-#define SR_DEVICE(dev)                                                                      \
-    sr459::DeviceGuard _device_guard(dev);                                                  \
-    if (!_device_guard.ok) { sr459::set_error("cudaSetDevice(%d) failed", (int)(dev)); return SR459_ECUDA; }
-
-template <typename T>
-static int dev_alloc(T** p, size_t count) {
-    if (*p) return SR459_OK;
-    cudaError_t e = gmalloc((void**)p, std::max<size_t>(count, 1) * sizeof(T));
-    if (e != cudaSuccess) {
-        set_error("cudaMalloc of %zu bytes failed: %s", count * sizeof(T), cudaGetErrorString(e));
-        *p = nullptr;
-        return SR459_ENOMEM;
-    }
-    return SR459_OK;
-}
-
-static int upload_taps_tbl(const std::vector<AxisTap>& v, AxisTap** d) {
-    SR_TRY(dev_alloc(d, v.size()));
-    SR_CUDA(cudaMemcpy(*d, v.data(), v.size() * sizeof(AxisTap), cudaMemcpyHostToDevice));
-    return SR459_OK;
-}
-
 }  // namespace sr459
 
 using namespace sr459;
@@ -88,68 +52,7 @@ using namespace sr459;
 // =================================================================================================
 // plan
 // =================================================================================================
-struct sr459_plan {
-    int device = 0, n = 0, h = 0, w = 0, factor = 2, H = 0, W = 0;
-    double shifts[2 * kMaxFrames] = {0};
-    std::vector<double> psf; int kh = 0, kw = 0;
-    double step = 0.5, lo = 0.0, hi = 255.0;
-    bool is_int = false; int isy[kMaxFrames] = {0}, isx[kMaxFrames] = {0}, smax = 0;
-    int path = 0;
-    int64_t scratch = 0;
-
-    // band geometry (whole image when not a band plan)
-    bool band = false;
-    int own_i0 = 0, own_i1 = 0;       // owned LR rows
-    int hr_lo = 0, hr_hi = 0, lr_lo = 0, lr_hi = 0, halo = 0;
-    int rank = 0, nranks = 1;
-    bool band_recipe_valid = false, band_uses_vsum = false; int band_iters = 0;
-
-    // tables
-    AxisTap *d_zoom_y = nullptr, *d_zoom_x = nullptr;
-    AxisTap *d_saa_ty = nullptr, *d_saa_tx = nullptr;
-    AxisTap *d_fwd_ty = nullptr, *d_fwd_tx = nullptr, *d_bwd_ty = nullptr, *d_bwd_tx = nullptr;
-    int *d_fir_iy0 = nullptr, *d_fir_ix0 = nullptr; float *d_fir_wy = nullptr, *d_fir_wx = nullptr; bool fir_ok = false;   // fir.cu
-    FirPolyArgs fir_poly{}; bool fir_poly_ok = false;                      // interior polyphase form of the same tables
-    cudaStream_t side = nullptr; cudaEvent_t ev_fork = nullptr, ev_join = nullptr;   // k_fir_poly runs beside k_fir_bp's border tiles
-    TapList taps_f, taps_b;
-    float psf7[49] = {0};
-    bool  separable = false;          // psf7[u][v] == acol[u] * brow[v]
-    float acol[7] = {0}, brow[7] = {0};
-
-    // separable fused path: pre-summed frames per parity lattice (ibp_sep.cu)
-    int   nslot = 0, slot_pq[kMaxSlots] = {0};
-    int   slot_n[kMaxSlots] = {0}, slot_k[kMaxSlots][kMaxFrames] = {{0}};
-    float mtab[kMaxSlots][4] = {{0}};
-    float* d_s1[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
-    int   s1_rows = 0, s1_pitch = 0;
-    CUtensorMap tm_s1[kMaxSlots];     // box of ibp_sep.cu
-    CUtensorMap tm_s1w[kMaxSlots];    // box of ibp_ws.cu
-    double* d_vsum = nullptr;
-    float* d_edge = nullptr;          // ibp_stream.cu edge vectors: colS1[h], leftS1[h], rowS1[w], topS1[w], scal[4]
-    CUtensorMap tm_s1s;               // box of ibp_stream.cu (single lattice)
-    int*  d_counters = nullptr; int counters_cap = 0;   // per-iteration tile counters of the pipelined kernel
-    LatPlan* lat = nullptr;           // ibp_lat.cu: large / non-separable PSFs
-    int   n_sm = 0;
-
-    // scratch
-    float *d_coef_lr = nullptr, *d_zoomed = nullptr, *d_coef_pad = nullptr;
-    float *d_B = nullptr, *d_acc = nullptr, *d_err = nullptr, *d_hr2 = nullptr;
-    double *d_partial = nullptr; size_t partial_cap = 0;
-    double *d_errors = nullptr; int errors_cap = 0;
-
-    // per-iteration partial-sum bookkeeping of the last ibp call
-    int per_iter = 0;
-};
-
-template <typename T>
-static int plan_alloc(sr459_plan* p, T** ptr, size_t count) {
-    if (*ptr) return SR459_OK;
-    SR_TRY(dev_alloc(ptr, count));
-    p->scratch += (int64_t)(count * sizeof(T));
-    return SR459_OK;
-}
-
-static int plan_ensure_partial(sr459_plan* p, size_t count) {
+int plan_ensure_partial(sr459_plan* p, size_t count) {
     if (count <= p->partial_cap) return SR459_OK;
     if (p->d_partial) { gfree(p->d_partial); p->scratch -= (int64_t)(p->partial_cap * sizeof(double)); p->d_partial = nullptr; }
     SR_TRY(plan_alloc(p, &p->d_partial, count));
@@ -157,7 +60,7 @@ static int plan_ensure_partial(sr459_plan* p, size_t count) {
     return SR459_OK;
 }
 
-static int plan_ensure_errors(sr459_plan* p, int n_iter) {
+int plan_ensure_errors(sr459_plan* p, int n_iter) {
     if (n_iter <= p->errors_cap) return SR459_OK;
     if (p->d_errors) { gfree(p->d_errors); p->scratch -= (int64_t)(p->errors_cap * sizeof(double)); p->d_errors = nullptr; }
     SR_TRY(plan_alloc(p, &p->d_errors, (size_t)n_iter));
@@ -165,16 +68,14 @@ static int plan_ensure_errors(sr459_plan* p, int n_iter) {
     return SR459_OK;
 }
 
-static bool fused_supported(const sr459_plan* p);
-
-static int plan_args_check(int n_frames, int h, int w, int factor, const double* shifts, const double* psf, int kh, int kw) {
+int plan_args_check(int n_frames, int h, int w, int factor, const double* shifts, const double* psf, int kh, int kw) {
     if (n_frames < 1 || n_frames > kMaxFrames) { set_error("n_frames must be 1..%d, got %d", kMaxFrames, n_frames); return SR459_EINVAL; }
     if (h < 1 || w < 1 || factor < 1) { set_error("bad geometry h=%d w=%d factor=%d", h, w, factor); return SR459_EINVAL; }
     if (!shifts || !psf || kh < 1 || kw < 1) { set_error("null shifts/psf or empty kernel"); return SR459_EINVAL; }
     return SR459_OK;
 }
 
-static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int w, int factor,
+int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int w, int factor,
                             const double* shifts, const double* psf, int kh, int kw, double step,
                             double lo, double hi) {
     SR_TRY(plan_args_check(n_frames, h, w, factor, shifts, psf, kh, kw));
@@ -247,7 +148,7 @@ static int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int 
     return SR459_OK;
 }
 
-static void plan_free(sr459_plan* p) {
+void plan_free(sr459_plan* p) {
     if (!p) return;
     DeviceGuard guard(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
@@ -257,6 +158,7 @@ static void plan_free(sr459_plan* p) {
     free_taps(p->taps_f);
     free_taps(p->taps_b);
     lat_destroy(p->lat);
+    band_state_free(p->bs);
     if (p->ev_fork) cudaEventDestroy(p->ev_fork);
     if (p->ev_join) cudaEventDestroy(p->ev_join);
     if (p->side) cudaStreamDestroy(p->side);
@@ -391,7 +293,7 @@ static int run_saa(sr459_plan* p, const float* const* lr, float* d_hr, cudaStrea
 }
 
 // generic (stage-by-stage) IBP iteration: any shifts, any PSF, any integer factor
-static int iterate_generic(sr459_plan* p, const float* const* lr, const float* cur, float* nxt, int it, cudaStream_t st) {
+int iterate_generic(sr459_plan* p, const float* const* lr, const float* cur, float* nxt, int it, cudaStream_t st) {
     const size_t lpx = (size_t)p->h * p->w, hpx = (size_t)p->H * p->W;
     const int PH = p->H + 2 * kPad, PW = p->W + 2 * kPad;
     SR_TRY(plan_generic_tables(p));
@@ -408,6 +310,7 @@ static int iterate_generic(sr459_plan* p, const float* const* lr, const float* c
     e.coef = p->d_coef_pad; e.cpitch = PW; e.n = p->n; e.ty = p->d_fwd_ty; e.tx = p->d_fwd_tx; e.h = p->h; e.w = p->w;
     for (int k = 0; k < p->n; ++k) { e.lr[k] = lr[k]; e.out[k] = p->d_err + k * lpx; }
     e.partial = p->d_partial + (size_t)it * p->per_iter;
+    e.mse_i0 = p->mse_i0 < 0 ? 0 : p->mse_i0; e.mse_i1 = p->mse_i1 < 0 ? p->h : p->mse_i1;
     SR_TRY(launch_resample_err(e, st, nullptr));
     // backward: zero-insert + pad + prefilter per frame, evaluate at -s, sum, transposed blur + update
     if (p->fir_ok && p->path == 0) {                        // the same linear map as ONE table-driven FIR kernel (fir.cu)
@@ -432,6 +335,7 @@ static int iterate_generic(sr459_plan* p, const float* const* lr, const float* c
             SR_TRY(launch_fir_bp(fb, st));
         }
         CorrArgs u2{p->d_acc, p->H, p->W, &p->taps_b, nxt, 1, cur, (float)(p->step / p->n), (float)p->lo, (float)p->hi};
+        if (p->store_y0 >= 0) { u2.y0 = p->store_y0; u2.y1 = p->store_y1; }
         return launch_corr2d(u2, st);
     }
     PrefilterJob jobs[kMaxFrames];
@@ -443,13 +347,14 @@ static int iterate_generic(sr459_plan* p, const float* const* lr, const float* c
     for (int k = 0; k < p->n; ++k) { s.coef[k] = p->d_coef_pad + (size_t)k * PH * PW; s.cpitch[k] = PW; }
     SR_TRY(launch_resample_sum(s, st));
     CorrArgs u{p->d_acc, p->H, p->W, &p->taps_b, nxt, 1, cur, (float)(p->step / p->n), (float)p->lo, (float)p->hi};
+    if (p->store_y0 >= 0) { u.y0 = p->store_y0; u.y1 = p->store_y1; }
     return launch_corr2d(u, st);
 }
 
-static int generic_per_iter(const sr459_plan* p) { return p->n * ((p->h + 7) / 8) * ((p->w + 31) / 32); }
+int generic_per_iter(const sr459_plan* p) { return p->n * ((p->h + 7) / 8) * ((p->w + 31) / 32); }
 
 // ---- fused integer path ------------------------------------------------------------------------------
-static bool fused_supported(const sr459_plan* p) {
+bool fused_supported(const sr459_plan* p) {
     return p->is_int && p->factor == 2 && p->smax <= kMaxIntShift && std::max(p->taps_f.reach, p->taps_b.reach) <= 16;
 }
 
@@ -462,7 +367,6 @@ static void fill_geom(const sr459_plan* p, IbpGeom& g, int uy0, int uy1) {
     g.upd_y0 = uy0; g.upd_y1 = uy1; g.own_i0 = p->own_i0; g.own_i1 = p->own_i1;
 }
 
-struct DensePass { Rect rects[4]; int nrect; int tile_h, tile_w; };
 
 static int dense_launch(const sr459_plan* p, const IbpGeom& g, const float* const* lr, const float* cur, float* nxt,
                         const DensePass& dp, double* partial, int* ntiles_out, cudaStream_t st) {
@@ -499,19 +403,8 @@ static void fill_lat_call(const sr459_plan* p, LatCall& c, int uy0, int uy1) {
 }
 
 // number of partial-sum slots one fused iteration writes, and the launch recipe
-struct FusedRecipe {
-    bool use_fast;
-    bool use_sep;
-    bool use_ws;
-    bool use_stream;
-    bool use_lat;
-    int st_nit, st_seg, st_nseg, st_nstrip;
-    int fast_tx, fast_ty;
-    DensePass all;
-    int n_fast, n_all, per_iter;
-};
 
-static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
+FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     FusedRecipe r{};
     const int W = p->W;
     int fth, ftw;
@@ -520,13 +413,16 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || (p->path >= 4 && p->path <= 7));
     bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
     const bool lat_ok = p->lat != nullptr && (p->path == 0 || p->path == 8);
-    const bool stream_ok = sep_ok && !p->band && uy0 == 0 && uy1 == p->H && (p->path == 0 || p->path == 7) &&
+    // the streaming kernel treats the local buffer (a row band with its halo) as an image of its own: what the
+    // artificial cuts get wrong stays inside the halo rows, which the launch does not store (segments cover uy0..uy1)
+    const bool stream_ok = sep_ok && (p->path == 0 || p->path == 7) && (p->hr_lo % 2 == 0) && 2 * p->lr_lo == p->hr_lo &&
+                           (!p->band || (uy0 - p->hr_lo >= 8 || uy0 == 0) && (p->hr_hi - uy1 >= 8 || uy1 == p->H)) &&
                            ibp_stream_supported(p->kh, p->kw, p->smax, p->separable, W, p->nslot);
     if (stream_ok && (big || p->path == 7)) {
         r.use_stream = true;
         int n_sm = p->n_sm;
         if (!n_sm) { cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, p->device); }
-        stream_geometry(p->H, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
+        stream_geometry(uy1 - uy0, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
         r.n_fast = r.st_nseg * r.st_nstrip;
     } else if (sep_ok && p->path != 7 && (big || p->path >= 4)) {
         r.use_ws = (p->path == 0 || p->path == 4);
@@ -554,7 +450,7 @@ static FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
 }
 
 // S1 planes + sum of V for the frames of this call (ibp_sep.cu restructuring (2))
-static int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaStream_t st) {
+int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaStream_t st) {
     const int rows = p->lr_hi - p->lr_lo;
     const int pitch = (p->w + 3) & ~3;
     if (p->s1_rows != rows || p->s1_pitch != pitch) {
@@ -590,13 +486,14 @@ static int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel
     if (stream_kernel) {                              // the streaming kernel's map and edge vectors (+ their variances)
         SR_TRY(stream_make_s1_map(&p->tm_s1s, p->d_s1[0], p->w, rows, pitch));
         SR_TRY(plan_alloc(p, &p->d_edge, (size_t)2 * p->h + 2 * p->w + 4));
-        SR_TRY(launch_stream_edge_sums(lr, p->n, p->h, p->w, p->isy, p->isx, p->slot_pq[0] >> 1, p->slot_pq[0] & 1,
-                                       p->d_edge, p->d_vsum, st));
+        const int h_loc = (p->hr_hi - p->hr_lo) / 2;     // the local image of a row band (whole image: h)
+        SR_TRY(launch_stream_edge_sums(lr, p->n, h_loc, p->w, p->isy, p->isx, p->slot_pq[0] >> 1, p->slot_pq[0] & 1,
+                                       p->d_edge, p->d_vsum, p->own_i0 - p->lr_lo, p->own_i1 - p->lr_lo, p->own_i0 == 0, st));
     }
     return SR459_OK;
 }
 
-static int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
+int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
     if (n_iter > p->counters_cap) {
         if (p->d_counters) { gfree(p->d_counters); p->d_counters = nullptr; p->scratch -= (int64_t)p->counters_cap * 4; }
         SR_TRY(plan_alloc(p, &p->d_counters, (size_t)n_iter));
@@ -606,16 +503,18 @@ static int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
     return SR459_OK;
 }
 
-static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, const float* cur, float* nxt,
-                         double* partial, int uy0, int uy1, cudaStream_t st, int it = -1) {
+int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, const float* cur, float* nxt,
+                  double* partial, int uy0, int uy1, cudaStream_t st, int it) {
     IbpGeom g;
     fill_geom(p, g, uy0, uy1);
     if (r.use_stream) {
         StreamArgs f{};
-        SR_TRY(stream_make_hr_map(&f.tm_hr, cur, p->W, p->H));
+        const int H_loc = p->hr_hi - p->hr_lo, h_loc = H_loc / 2;
+        SR_TRY(stream_make_hr_map(&f.tm_hr, cur, p->W, H_loc));
         f.tm_s1 = p->tm_s1s;
         f.hr_out = nxt;
-        f.H = p->H; f.W = p->W; f.h = p->h; f.w = p->w;
+        f.H = H_loc; f.W = p->W; f.h = h_loc; f.w = p->w;
+        f.y_base = uy0 - p->hr_lo; f.y_end = uy1 - p->hr_lo;
         f.nit = r.st_nit; f.seg_rows = r.st_seg; f.nseg = r.st_nseg; f.nstrip = r.st_nstrip;
         f.alpha = g.alpha; f.lo = g.lo; f.hi = g.hi;
         memcpy(f.acol, p->acol, sizeof(f.acol));
@@ -623,8 +522,8 @@ static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const
         memcpy(f.mtab, p->mtab[0], sizeof(f.mtab));
         const int P = p->slot_pq[0] >> 1, Q = p->slot_pq[0] & 1;
         f.has_left = (Q == 1);
-        f.colS1 = p->d_edge; f.leftS1 = p->d_edge + p->h; f.rowS1 = p->d_edge + 2 * p->h;
-        f.topS1 = p->d_edge + 2 * p->h + p->w; f.scal = p->d_edge + 2 * p->h + 2 * p->w;
+        f.colS1 = p->d_edge; f.leftS1 = p->d_edge + h_loc; f.rowS1 = p->d_edge + 2 * h_loc;
+        f.topS1 = p->d_edge + 2 * h_loc + p->w; f.scal = p->d_edge + 2 * h_loc + 2 * p->w;
         for (int k = 0; k < p->n; ++k) {
             const int oy = (P + p->isy[k]) >> 1, ox = (Q + p->isx[k]) >> 1;
             if (p->isx[k] == -1) { f.mc[0] += 1.f; if (oy == 0) f.mc[1] += 1.f; }
@@ -686,7 +585,7 @@ static int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const
     return dense_launch(p, g, lr, cur, nxt, r.all, partial, &nt, st);
 }
 
-static bool use_fused(const sr459_plan* p) {
+bool use_fused(const sr459_plan* p) {
     if (p->path == 1) return false;
     return fused_supported(p);
 }
@@ -722,7 +621,7 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
     return SR459_OK;
 }
 
-static int check_lr(const sr459_plan* p, const float* const* lr) {
+int check_lr(const sr459_plan* p, const float* const* lr) {
     if (!p) { set_error("null plan"); return SR459_EINVAL; }
     if (!lr) { set_error("null frame pointer array"); return SR459_EINVAL; }
     for (int k = 0; k < p->n; ++k) if (!lr[k]) { set_error("frame %d pointer is null", k); return SR459_EINVAL; }
@@ -1037,89 +936,6 @@ int sr459_saa_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, flo
     if (d_saa)
         SR_CUDA(cudaMemcpyAsync(d_saa, d_hr, sizeof(float) * (size_t)plan->H * plan->W, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
     return sr459_ibp(plan, h_d_lr, d_hr, n_iter, h_errors, stream);
-}
-
-// ---- row bands (one HR image split across GPUs; halo rows are exchanged by the host layer) -------------
-int sr459_band_plan_create(sr459_plan** out, int device, int n_frames, int h, int w, int factor, const double* h_shifts_yx,
-                           const double* h_psf, int kh, int kw, double step, double clip_lo, double clip_hi,
-                           int rank, int nranks) {
-    if (!out) { set_error("band_plan_create: null output"); return SR459_EINVAL; }
-    *out = nullptr;
-    if (nranks < 1 || rank < 0 || rank >= nranks) { set_error("band_plan_create: bad rank %d of %d", rank, nranks); return SR459_EINVAL; }
-    if (h < nranks) { set_error("band_plan_create: %d LR rows cannot be split into %d bands", h, nranks); return SR459_EINVAL; }
-    SR_TRY(plan_args_check(n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw));
-    SR_DEVICE(device);
-    sr459_plan* p = new (std::nothrow) sr459_plan();
-    if (!p) { set_error("out of host memory"); return SR459_ENOMEM; }
-    int rc = plan_common_init(p, device, n_frames, h, w, factor, h_shifts_yx, h_psf, kh, kw, step, clip_lo, clip_hi);
-    if (rc != SR459_OK) { plan_free(p); return rc; }
-    if (!fused_supported(p)) {
-        plan_free(p);
-        set_error("band plans need integer HR shifts (|shift| <= %d), factor 2 and a PSF reach <= 16", kMaxIntShift);
-        return SR459_EUNSUPPORTED;
-    }
-    p->band = true;
-    p->rank = rank; p->nranks = nranks;
-    const int reach = std::max(p->taps_f.reach, p->taps_b.reach);
-    p->halo = 2 * reach + 2;                              // hr' depends on hr within 2 r rows; +2 keeps it even with slack
-    p->own_i0 = (int)(((long long)rank * h) / nranks);
-    p->own_i1 = (int)(((long long)(rank + 1) * h) / nranks);
-    const int oy0 = 2 * p->own_i0, oy1 = 2 * p->own_i1;
-    p->hr_lo = std::max(0, oy0 - p->halo); p->hr_hi = std::min(p->H, oy1 + p->halo);
-    p->lr_lo = std::max(0, (oy0 - p->halo) / 2); p->lr_hi = std::min(h, (oy1 + p->halo) / 2 + 1);
-    *out = p;
-    return SR459_OK;
-}
-
-int sr459_band_layout(const sr459_plan* plan, int* h_out8) {
-    if (!plan || !h_out8 || !plan->band) { set_error("band_layout: not a band plan"); return SR459_EINVAL; }
-    h_out8[0] = 2 * plan->own_i0; h_out8[1] = 2 * plan->own_i1;
-    h_out8[2] = plan->hr_lo; h_out8[3] = plan->hr_hi;
-    h_out8[4] = plan->lr_lo; h_out8[5] = plan->lr_hi;
-    h_out8[6] = plan->halo;  h_out8[7] = plan->nranks;
-    return SR459_OK;
-}
-
-int sr459_band_begin(sr459_plan* plan, const float* const* h_d_lr_local, int n_iter, void* stream) {
-    SR_TRY(check_lr(plan, h_d_lr_local));
-    if (!plan->band || n_iter < 0) { set_error("band_begin: not a band plan or n_iter < 0"); return SR459_EINVAL; }
-    SR_DEVICE(plan->device);
-    cudaStream_t st = (cudaStream_t)stream;
-    plan->band_recipe_valid = false;
-    if (n_iter == 0) return SR459_OK;
-    FusedRecipe r = fused_recipe(plan, 2 * plan->own_i0, 2 * plan->own_i1);
-    plan->per_iter = r.per_iter;
-    SR_TRY(plan_ensure_errors(plan, n_iter));
-    SR_TRY(plan_ensure_partial(plan, (size_t)n_iter * r.per_iter));
-    plan->band_uses_vsum = false;
-    if (r.use_sep) { SR_TRY(sep_prepare(plan, h_d_lr_local, false, st)); SR_TRY(sep_counters(plan, n_iter, st)); plan->band_uses_vsum = true; }
-    plan->band_recipe_valid = true;
-    plan->band_iters = n_iter;
-    return SR459_OK;
-}
-
-int sr459_band_iterate(sr459_plan* plan, const float* const* h_d_lr_local, const float* d_cur, float* d_nxt, int it, void* stream) {
-    SR_TRY(check_lr(plan, h_d_lr_local));
-    if (!plan->band || !plan->band_recipe_valid || !d_cur || !d_nxt || it < 0 || it >= plan->band_iters) {
-        set_error("band_iterate: call sr459_band_begin first; it must be in [0, n_iter)"); return SR459_EINVAL;
-    }
-    SR_DEVICE(plan->device);
-    const int uy0 = 2 * plan->own_i0, uy1 = 2 * plan->own_i1;
-    FusedRecipe r = fused_recipe(plan, uy0, uy1);
-    return iterate_fused(plan, r, h_d_lr_local, d_cur, d_nxt, plan->d_partial + (size_t)it * r.per_iter, uy0, uy1,
-                         (cudaStream_t)stream, it);
-}
-
-int sr459_band_errors(sr459_plan* plan, int n_iter, double* h_sums, void* stream) {
-    if (!plan || !plan->band || !h_sums || n_iter < 0 || n_iter > plan->errors_cap) { set_error("band_errors: bad arguments"); return SR459_EINVAL; }
-    if (n_iter == 0) return SR459_OK;
-    cudaStream_t st = (cudaStream_t)stream;
-    SR_DEVICE(plan->device);
-    SR_TRY(launch_reduce_partials(plan->d_partial, plan->per_iter, n_iter, 1.0, plan->band_uses_vsum ? plan->d_vsum : nullptr,
-                                  plan->d_errors, st));
-    SR_CUDA(cudaMemcpyAsync(h_sums, plan->d_errors, sizeof(double) * n_iter, cudaMemcpyDeviceToHost, st));
-    SR_CUDA(cudaStreamSynchronize(st));
-    return SR459_OK;
 }
 
 }  // extern "C"

@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(256)
 k_corr2d(const float* __restrict__ in, int H, int W, const float* __restrict__ tw,
          const int* __restrict__ tdy, const int* __restrict__ tdx, int ntaps, int R,
          float* __restrict__ out, int mode, const float* __restrict__ base, float alpha,
-         float lo, float hi) {
+         float lo, float hi, int sy0, int sy1) {
     extern __shared__ float sm[];
     const int SW = CV_TW + 2 * R, SH = CV_TH + 2 * R;
     float* tile = sm;                                  // SH x SW
@@ -103,7 +103,7 @@ k_corr2d(const float* __restrict__ in, int H, int W, const float* __restrict__ t
             #pragma unroll
             for (int r = 0; r < 4; ++r) {
                 int gy = y0 + ly + r;
-                if (gy < H) {
+                if (gy < H && gy >= sy0 && gy < sy1) {
                     size_t o = (size_t)gy * W + gx;
                     float val = v[r];
                     if (mode == 1) val = fminf(fmaxf(fmaf(alpha, val, __ldg(base + o)), lo), hi);
@@ -124,7 +124,7 @@ int launch_corr2d(const CorrArgs& a, cudaStream_t st) {
     }
     dim3 grid((a.W + CV_TW - 1) / CV_TW, (a.H + CV_TH - 1) / CV_TH);
     k_corr2d<<<grid, 256, smem, st>>>(a.in, a.H, a.W, t.d_w, t.d_dy, t.d_dx, t.ntaps, R, a.out,
-                                      a.mode, a.base, a.alpha, a.lo, a.hi);
+                                      a.mode, a.base, a.alpha, a.lo, a.hi, a.y0, a.y1 < 0 ? a.H : a.y1);
     SR_LAUNCH_CHECK("k_corr2d");
     return SR459_OK;
 }

@@ -80,6 +80,8 @@ struct EdgeSumArgs {
     int oy[kMaxFrames], ox[kMaxFrames];
     float* colS1; float* leftS1; float* rowS1; float* topS1; float* scal;
     double* vsum;
+    int own_a0, own_a1;       // local site rows whose MSE-only column terms this launch counts (row bands)
+    int top_owned;            // the band holds LR row 0: the row vectors' and the corner's variances count
 };
 
 __global__ void __launch_bounds__(256) k_edge_sums(const __grid_constant__ EdgeSumArgs a) {
@@ -98,7 +100,7 @@ __global__ void __launch_bounds__(256) k_edge_sums(const __grid_constant__ EdgeS
             if (a.sx[k] == +1) { x[k] = v; s += v; m |= 1 << k; }
         }
         a.colS1[t] = dup; a.leftS1[t] = s;
-        if (m) { const float mu = s / (float)__popc(m);
+        if (m && t >= a.own_a0 && t < a.own_a1) { const float mu = s / (float)__popc(m);
             #pragma unroll
             for (int k = 0; k < kMaxFrames; ++k) if (m & (1 << k)) { const float d = x[k] - mu; var += (double)d * d; } }
     }
@@ -115,7 +117,7 @@ __global__ void __launch_bounds__(256) k_edge_sums(const __grid_constant__ EdgeS
             if (a.sy[k] == +1) { x[k] = v; s += v; m |= 1 << k; }
         }
         a.rowS1[t] = dup; a.topS1[t] = s;
-        if (m) { const float mu = s / (float)__popc(m);
+        if (m && a.top_owned) { const float mu = s / (float)__popc(m);
             #pragma unroll
             for (int k = 0; k < kMaxFrames; ++k) if (m & (1 << k)) { const float d = x[k] - mu; var += (double)d * d; } }
     }
@@ -128,7 +130,7 @@ __global__ void __launch_bounds__(256) k_edge_sums(const __grid_constant__ EdgeS
             if (a.sy[k] == +1 && a.sx[k] == +1) { s += v; m |= 1 << k; }
         }
         a.scal[0] = dup; a.scal[1] = s;
-        if (m) { const float mu = s / (float)__popc(m);
+        if (m && a.top_owned) { const float mu = s / (float)__popc(m);
             for (int k = 0; k < a.n; ++k) if (m & (1 << k)) { const float d = x[k] - mu; var += (double)d * d; } }
     }
     #pragma unroll
@@ -398,8 +400,8 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
 
     WarpCtx c;
     c.x0 = strip * SS_VALID;
-    c.ya = seg * a.seg_rows;
-    c.yb = min(c.ya + a.seg_rows, a.H);
+    c.ya = a.y_base + seg * a.seg_rows;                  // segments partition the rows this launch updates
+    c.yb = min(c.ya + a.seg_rows, a.y_end);
     c.h = a.h;
     c.top = (P == 1) && (c.ya == 0);
     const int ys0 = c.ya - 3 + (1 - P);                  // first site row the segment needs (parity P)
@@ -540,9 +542,10 @@ void stream_geometry(int H, int W, int n_sm, int* nit_out, int* seg_rows, int* n
 }
 
 int launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const int* sy, const int* sx, int P, int Q,
-                            float* buf, double* vsum, cudaStream_t st) {
+                            float* buf, double* vsum, int own_a0, int own_a1, int top_owned, cudaStream_t st) {
     EdgeSumArgs e{};
     e.n = n; e.h = h; e.w = w;
+    e.own_a0 = own_a0; e.own_a1 = own_a1; e.top_owned = top_owned;
     for (int k = 0; k < n; ++k) {
         e.lr[k] = lr[k]; e.sy[k] = sy[k]; e.sx[k] = sx[k];
         e.oy[k] = (P + sy[k]) >> 1; e.ox[k] = (Q + sx[k]) >> 1;

@@ -105,6 +105,7 @@ struct ResampleErrArgs {
     const float* lr[8];     // may be all null -> store sim
     float* out[8];
     double* partial;        // [gridDim.x*gridDim.y*n] or null
+    int mse_i0, mse_i1;     // LR rows whose squared residuals are counted (row bands: the owned ones)
 };
 int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_out);
 
@@ -183,6 +184,7 @@ struct CorrArgs {
     float* out;
     // epilogue: mode 0 -> out = v ; mode 1 -> out = clamp(base + alpha*v, lo, hi)
     int mode; const float* base; float alpha, lo, hi;
+    int y0 = 0, y1 = -1;    // rows stored (y1 < 0: all); row bands keep their halo rows untouched
 };
 int launch_corr2d(const CorrArgs& a, cudaStream_t st);
 
@@ -293,7 +295,8 @@ struct alignas(64) StreamArgs {
     CUtensorMap tm_hr;                  // hr_in as a {W, H} tensor, box 128 x 8
     CUtensorMap tm_s1;                  // the lattice's S1 plane {w, h}, box 64 x 4
     float* hr_out;
-    int H, W, h, w;
+    int H, W, h, w;                     // dims of the (local) image behind tm_hr / tm_s1
+    int y_base, y_end;                  // rows this launch updates, partitioned into segments (whole image: 0, H)
     int nit;                            // loop iterations (4 lattice rows each) per warp
     int seg_rows;                       // HR rows a warp updates = 8 nit - 6
     int nseg, nstrip;                   // warps = nseg * nstrip
@@ -315,7 +318,7 @@ int  stream_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, in
 void stream_geometry(int H, int W, int n_sm, int* nit, int* seg_rows, int* nseg, int* nstrip);
 // edge vectors + their variances (added to *vsum); buf holds 2h + 2w + 4 floats: colS1, leftS1, rowS1, topS1, scal
 int  launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const int* sy, const int* sx, int P, int Q,
-                             float* buf, double* vsum, cudaStream_t st);
+                             float* buf, double* vsum, int own_a0, int own_a1, int top_owned, cudaStream_t st);
 
 // ---- lattice form for large / non-separable PSFs (ibp_lat.cu): reach <= 15, |integer HR shift| <= 1 ---------
 struct LatPlan;                         // tables + site planes, owned by the plan

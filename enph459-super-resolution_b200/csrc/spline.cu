@@ -474,7 +474,7 @@ __global__ void __launch_bounds__(256) k_resample_err(ResampleErrArgs a) {
         if (a.lr[k]) {
             float e = __ldg(a.lr[k] + o) - sim;
             a.out[k][o] = e;
-            e2 = e * e;
+            e2 = (y >= a.mse_i0 && y < a.mse_i1) ? e * e : 0.0f;
         } else {
             a.out[k][o] = sim;
         }

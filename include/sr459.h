@@ -176,24 +176,50 @@ int sr459_saa_ibp(sr459_plan* plan, const float* const* h_d_lr, float* d_hr, flo
                   int n_iter, double* h_errors, void* stream);
 
 /* ---- row bands: ONE large HR image split across GPUs (BASELINE config 4) ---- */
-/* The reference has no multi-device path; a band plan runs ibp()'s iteration (run_sr.py:197-205)
- * on the HR rows [2a, 2b) that rank `rank` of `nranks` owns (LR rows [a, b) = an even split of h),
- * reading halo = 2*reach+2 further hr rows on each side that the host layer refreshes from the
- * neighbouring ranks after every iteration (bands.py: NCCL send/recv between the rank processes).
- * Needs integer HR shifts and factor 2 (SR459_EUNSUPPORTED otherwise).  All band buffers are LOCAL:
- * hr buffers hold global HR rows [hr_lo, hr_hi), frame buffers global LR rows [lr_lo, lr_hi).        */
+/* The reference has no multi-device path; a band plan runs shift_and_add (run_sr.py:181-187) and ibp()'s
+ * iteration (run_sr.py:197-205) on the HR rows [2a, 2b) that rank `rank` of `nranks` owns (LR rows [a, b) = an
+ * even split of h), keeping `halo` further hr rows on each side: 2*reach+2 for integer HR shifts (fused kernels),
+ * 2*(reach+19) rounded up to 16 for fractional shifts (rgb_cal_target/run_sr.py:88-96; stage-by-stage iteration on
+ * the local image).  Factor 2 only.  The band's two hr buffers and its flag words live in one device block ("arena")
+ * that the neighbouring ranks map, so the halo rows travel as peer-memory stores from a kernel (csrc/bands.cu) --
+ * there is no collective on the data path; the host layer (bands.py) only moves the 64-byte handles once and
+ * all-reduces the K squared-error sums at the end.
+ * Local buffers: hr buffers hold global HR rows [hr_lo, hr_hi); the caller's LR frames hold the global LR rows
+ * [lr_ext_lo, lr_ext_hi) = hr_lo/2 - 32 .. hr_hi/2 + 32 clipped to the image (the margin feeds zoom's prefilter). */
 int sr459_band_plan_create(sr459_plan** out, int device, int n_frames, int h, int w, int factor,
                            const double* h_shifts_yx, const double* h_psf, int kh, int kw,
                            double step, double clip_lo, double clip_hi, int rank, int nranks);
-/* h_out8 = { own_y0, own_y1, hr_lo, hr_hi, lr_lo, lr_hi, halo_rows, nranks } (global row numbers)   */
+/* h_out8 = { own_y0, own_y1, hr_lo, hr_hi, lr_lo, lr_hi, halo_rows, nranks } (global row numbers; lr_lo..lr_hi are
+ * the LR rows the two-call form below takes)                                                                      */
 int sr459_band_layout(const sr459_plan* plan, int* h_out8);
-/* once per ibp() call: per-call sums of the local frames, partial-sum storage for n_iter iterations */
+/* h_out4 = { lr_ext_lo, lr_ext_hi, fractional (0/1), lr_margin }                                                  */
+int sr459_band_layout_ext(const sr459_plan* plan, int* h_out4);
+/* device pointers of the band's current image buffer and of the other one ((hr_hi-hr_lo) x W float32 each); the
+ * current one is where sr459_band_saa writes, where a caller-made initial image goes (halo rows included) and where
+ * the result of sr459_band_run is found afterwards (ask again: the two swap with every iteration).                 */
+int sr459_band_buffers(sr459_plan* plan, void** d_cur, void** d_other, int64_t* arena_bytes);
+/* index (0/1) of the buffer holding the current image; set_to >= 0 sets it first (replaying a captured run)         */
+int sr459_band_current(sr459_plan* plan, int set_to);
+/* the arena's cudaIpcMemHandle_t (64 bytes; for a neighbour in another process) and/or its raw device pointer (for
+ * a neighbour in this process); either output may be NULL                                                          */
+int sr459_band_export(sr459_plan* plan, unsigned char* h_handle64, void** h_arena_ptr);
+/* map the arenas of the band above (rank-1) and below (rank+1): per direction EITHER a handle from another process
+ * OR the raw pointer + device of a plan in this process; NULL, NULL for a direction without a neighbour            */
+int sr459_band_attach(sr459_plan* plan, const unsigned char* up_handle64, void* up_arena, int up_device,
+                      const unsigned char* down_handle64, void* down_arena, int down_device);
+/* shift_and_add restricted to this band (halo rows included) from LR rows only -> the current buffer             */
+int sr459_band_saa(sr459_plan* plan, const float* const* h_d_lr_ext, void* stream);
+/* n_iter iterations on the current buffer; after each one a kernel stores the band's boundary rows into the
+ * neighbours' halo rows and waits for theirs.  Every rank must make the same calls.  Enqueues only (capturable).   */
+int sr459_band_run(sr459_plan* plan, const float* const* h_d_lr_ext, int n_iter, void* stream);
+/* two-call form with caller-owned buffers (LR rows [lr_lo, lr_hi)) and the exchange left to the host layer:
+ * once per ibp() call ...                                                                                          */
 int sr459_band_begin(sr459_plan* plan, const float* const* h_d_lr_local, int n_iter, void* stream);
-/* iteration `it`: d_nxt[owned rows] = update(d_cur); halo rows of d_nxt are NOT written             */
+/* ... then iteration `it`: d_nxt[owned rows] = update(d_cur); halo rows of d_nxt are NOT written                   */
 int sr459_band_iterate(sr459_plan* plan, const float* const* h_d_lr_local, const float* d_cur,
                        float* d_nxt, int it, void* stream);
-/* h_sums[it] = sum over the frames and the LR rows this rank owns of err^2 (un-normalised; the host
- * layer all-reduces and divides by n*h*w as run_sr.py:202,206 do).  Synchronises the stream.          */
+/* h_sums[it] = sum over the frames and the sites this rank owns of err^2 (un-normalised; the host layer all-reduces
+ * and divides by n*h*w as run_sr.py:202,206 do).  Synchronises the stream; SR459_ECUDA if an exchange timed out.   */
 int sr459_band_errors(sr459_plan* plan, int n_iter, double* h_sums, void* stream);
 
 #if defined(__GNUC__)

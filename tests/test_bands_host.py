@@ -112,3 +112,44 @@ def test_single_rank_exchange_is_a_no_op():
     exchange_halos(u, lay)
     assert torch.equal(t, u)
     assert reduce_errors([float(16 * 8 * 4 * 2)], 4, lay) == [2.0]
+
+
+def _handle_worker(rank, world, port, out_dir):
+    import torch.distributed as dist
+    from sr459.bands import exchange_handles
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        mine = bytes([rank]) * 64                             # stands in for a cudaIpcMemHandle_t
+        up, down = exchange_handles(mine, rank, world)
+        with open(os.path.join(out_dir, f"h{rank}.txt"), "w") as f:
+            f.write(f"{up[0] if up else -1} {down[0] if down else -1} {len(up or b'x' * 64)} {len(down or b'x' * 64)}")
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("world", [2, 3])
+def test_arena_handles_reach_the_right_neighbours_over_gloo(tmp_path, world):
+    """The only collective of the peer-memory band path besides the final error all-reduce: every rank must end up with the
+    handle of rank-1 (its upper neighbour) and rank+1 (its lower one), None at the image ends."""
+    import torch.multiprocessing as mp
+    mp.spawn(_handle_worker, args=(world, _free_port(), str(tmp_path)), nprocs=world, join=True)
+    for r in range(world):
+        up, down, lu, ld = map(int, (tmp_path / f"h{r}.txt").read_text().split())
+        assert up == (r - 1 if r > 0 else -1) and down == (r + 1 if r < world - 1 else -1)
+        assert lu == 64 and ld == 64
+
+
+def test_band_layout_extended_lr_rows_and_fractional_halo():
+    from sr459.bands import LR_MARGIN, band_halo
+    assert band_halo(3, True) == 8 and band_halo(15, True) == 32
+    assert band_halo(3, False) == 48 and band_halo(15, False) == 80     # 2 * (reach + 19), rounded up to 16
+    for h, world, reach, halo in [(1536, 8, 15, None), (768, 4, 3, 48), (100, 3, 3, None)]:
+        for r in range(world):
+            l = BandLayout(h, 40, reach, r, world, halo=halo)
+            assert l.lr_ext_lo == max(0, l.hr_lo // 2 - LR_MARGIN) and l.lr_ext_hi == min(h, l.hr_hi // 2 + LR_MARGIN)
+            assert l.lr_ext_lo <= l.lr_lo and l.lr_hi <= l.lr_ext_hi
+            # zoom's column prefilter: 16-sample tail + 3 taps beyond the rows the band's HR rows map to
+            assert l.lr_ext_lo == 0 or l.hr_lo // 2 - l.lr_ext_lo >= 19
+            assert l.lr_ext_hi == h or l.lr_ext_hi - l.hr_hi // 2 >= 19

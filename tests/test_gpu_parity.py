@@ -576,6 +576,93 @@ def test_row_bands_emulated_vs_oracle(sr, world, case):
     _errs_close(errs, e_o)
 
 
+@pytest.mark.parametrize("world", [2, 3])
+@pytest.mark.parametrize("case", ["gauss7", "measured31", "two_lattices", "fractional_k7", "measured7_int"])
+def test_row_bands_peer_memory_path_vs_oracle(sr, world, case):
+    """The product band path (csrc/bands.cu) with every band in this process: per-band SAA from LR rows only (e3), the
+    iteration kernels on the local buffers (streaming kernel for gauss7, lattice kernels for the 31x31 PSF, the
+    stage-by-stage iteration for fractional shifts) and the in-kernel halo exchange through peer pointers, against the
+    full-image float64 oracle; seams checked separately."""
+    from sr459.bands import BandPlan, run_emulated_peer
+    rng = np.random.default_rng(32)
+    g = golden("g_psf")
+    shifts = {"two_lattices": [(0.0, 0.0)] + NOMINAL, "fractional_k7": CALIBRATED}.get(case, NOMINAL)
+    if case == "measured31":
+        h, w, psf = 144, 80, g["k31"]
+    elif case == "fractional_k7":
+        h, w, psf = 240, 96, g["k7"]
+    else:
+        h, w = 150, 168
+        psf = g["k7"] if case == "measured7_int" else O.make_gaussian_psf()
+    lrs = [rng.uniform(0, 255, (h, w)).astype(np.float32).astype(np.float64) for _ in shifts]
+    integer = case != "fractional_k7"
+    saa_o = O.shift_and_add_integer(lrs, shifts) if integer else O.shift_and_add(lrs, shifts)
+    hr_o, e_o = (O.ibp_integer_shifts if integer else O.ibp)(lrs, shifts, psf, saa_o, n_iter=4)
+    plans = [BandPlan(len(shifts), h, w, shifts, psf, r, world) for r in range(world)]
+    assert plans[0].fractional == (not integer)
+    saa, _ = run_emulated_peer(plans, lrs, 0)                       # SAA only: every band from its own LR rows
+    _close(saa.cpu().numpy(), saa_o, what=f"banded SAA {case} world {world}")
+    hr, errs = run_emulated_peer(plans, lrs, 4)
+    seams = [p.layout.own_y0 for p in plans if p.layout.own_y0]
+    for p in plans:
+        p.close()
+    hr = hr.cpu().numpy()
+    _close(hr, hr_o, what=f"peer bands {case} world {world}")
+    for y in seams:
+        _close(hr[y - 8:y + 8], hr_o[y - 8:y + 8], what=f"seam at row {y}")
+    _errs_close(errs, e_o)
+
+
+def test_row_bands_peer_memory_graph_replay_and_reuse(sr):
+    """One band per rank is the same code with world 1; here two bands, the loop captured in a CUDA graph per band and
+    replayed twice (the second job re-uses plans, graphs and arenas), odd iteration counts refused for a second replay."""
+    import torch
+    from sr459.bands import BandPlan
+    rng = np.random.default_rng(33)
+    h, w, K = 128, 96, 6
+    psf = O.make_gaussian_psf()
+    plans = [BandPlan(4, h, w, NOMINAL, psf, r, 2) for r in range(2)]
+    plans[0].attach_local(None, plans[1]); plans[1].attach_local(plans[0], None)
+    streams = [torch.cuda.Stream() for _ in plans]
+    for job in range(2):
+        lrs = [rng.uniform(0, 255, (h, w)) for _ in NOMINAL]
+        saa_o = O.shift_and_add_integer(lrs, NOMINAL)
+        hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=K)
+        if job == 0:
+            exts = [[torch.from_numpy(l[p.layout.lr_ext_lo:p.layout.lr_ext_hi].astype(np.float32)).cuda() for l in lrs] for p in plans]
+        else:
+            for p, ext in zip(plans, exts):
+                for t, l in zip(ext, lrs):
+                    t.copy_(torch.from_numpy(l[p.layout.lr_ext_lo:p.layout.lr_ext_hi].astype(np.float32)))
+        torch.cuda.synchronize()
+        sums = []
+        for p, st, ext in zip(plans, streams, exts):
+            with torch.cuda.stream(st):
+                p.saa(ext)
+        torch.cuda.synchronize()
+        if job == 0:                                                # capture both loops before either replays
+            for p, st, ext in zip(plans, streams, exts):
+                with torch.cuda.stream(st):
+                    p.run_peer(ext, 0)                              # lazy scratch outside the capture
+        import threading
+        out = [None, None]
+
+        def go(i):
+            with torch.cuda.stream(streams[i]):
+                out[i] = plans[i].run_peer(exts[i], K, graph=(job == 1), reduce=False) if job == 1 else plans[i].run_peer(exts[i], K, reduce=False)
+        ths = [threading.Thread(target=go, args=(i,)) for i in range(2)]
+        [t.start() for t in ths]; [t.join() for t in ths]
+        torch.cuda.synchronize()
+        hr = np.zeros((2 * h, 2 * w), dtype=np.float32)
+        for p in plans:
+            lay = p.layout
+            hr[lay.own_y0:lay.own_y1] = p.current()[lay.owned].cpu().numpy()
+        _close(hr, hr_o, what=f"job {job}")
+        _errs_close(((out[0] + out[1]) / (4.0 * h * w)).tolist(), e_o)
+    for p in plans:
+        p.close()
+
+
 @pytest.mark.parametrize("use_graph", [False, True])
 def test_burst_stream_matches_oracle(sr, use_graph):
     """Streaming burst mode (config 5): frames committed one by one, uint8 HR images out, ring re-use."""
@@ -661,11 +748,13 @@ def test_mtf50_of_cuda_output_equals_mtf50_of_reference_output(sr):
         assert abs(a50 - b50) <= 1e-3 * b50 and abs(a10 - b10) <= 1e-3 * b10, (a50, b50, a10, b10)
 
 
-def test_band_plan_refuses_fractional_shifts(sr):
+def test_band_plan_fractional_shifts_get_the_wide_halo(sr):
     from sr459.bands import BandPlan
-    with pytest.raises(sr.Sr459Error) as ei:
-        BandPlan(4, 64, 64, CALIBRATED, O.make_gaussian_psf(), 0, 2)
-    assert ei.value.code == -4
+    p = BandPlan(4, 256, 64, CALIBRATED, O.make_gaussian_psf(), 0, 2)
+    assert p.fractional and p.layout.halo == 48          # 2 * (3 + 19) rounded up to 16
+    p.close()
+    with pytest.raises(sr.Sr459Error):                   # bands thinner than the halo
+        BandPlan(4, 64, 64, CALIBRATED, O.make_gaussian_psf(), 0, 4)
 
 
 # ---------------------------------------------------------------- run_sr.py-compatible CLI on synthetic session folders
