@@ -79,6 +79,9 @@ _SIGNATURES = {
     "sr459_band_attach": (_I, [_P, C.c_char_p, _P, _I, C.c_char_p, _P, _I]),
     "sr459_band_current": (_I, [_P, _I]),
     "sr459_band_saa": (_I, [_P, _PP, _P]),
+    "sr459_band_reserve": (_I, [_P, _PP, _I, _P]),
+    "sr459_band_run_range": (_I, [_P, _PP, _I, _I, _I, _P]),
+    "sr459_band_run_close": (_I, [_P, _P]),
     "sr459_band_run": (_I, [_P, _PP, _I, _P]),
     "sr459_band_begin": (_I, [_P, _PP, _I, _P]),
     "sr459_band_iterate": (_I, [_P, _PP, _P, _P, _I, _P]),

@@ -412,11 +412,24 @@ def run_emulated_peer(plans: Sequence[BandPlan], lr_full: Sequence, n_iter: int,
         with torch.cuda.device(p.device):
             torch.cuda.synchronize()
     arrs = []
-    for p, st, ext in zip(plans, streams, exts):          # enqueue every band's whole loop, then wait for all
+    for p, st, ext in zip(plans, streams, exts):          # allocations first: growing a buffer synchronises the device
         arr = (C.c_void_p * p.n)(*[t.data_ptr() for t in ext])
         arrs.append(arr)
         with torch.cuda.device(p.device):
-            _lib.check(p._lib.sr459_band_run(p._h, arr, int(n_iter), C.c_void_p(st.cuda_stream)))
+            _lib.check(p._lib.sr459_band_reserve(p._h, arr, int(n_iter), C.c_void_p(st.cuda_stream)))
+    for p in plans:
+        with torch.cuda.device(p.device):
+            torch.cuda.synchronize()
+    # iteration by iteration over the bands: a kernel only ever waits for kernels enqueued BEFORE it, so the emulation
+    # cannot deadlock even if the device runs the streams one after the other (they may share a hardware queue)
+    for it in range(int(n_iter)):
+        for p, st, arr in zip(plans, streams, arrs):
+            with torch.cuda.device(p.device):
+                _lib.check(p._lib.sr459_band_run_range(p._h, arr, it, it + 1, int(n_iter), C.c_void_p(st.cuda_stream)))
+    if n_iter > 0:
+        for p, st in zip(plans, streams):
+            with torch.cuda.device(p.device):
+                _lib.check(p._lib.sr459_band_run_close(p._h, C.c_void_p(st.cuda_stream)))
     total = np.zeros(max(int(n_iter), 0), dtype=np.float64)
     lay0 = plans[0].layout
     out = torch.empty((lay0.H, lay0.W), dtype=torch.float32, device=torch.device("cuda", plans[0].device))

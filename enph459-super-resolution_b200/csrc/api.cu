@@ -422,8 +422,13 @@ FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
         r.use_stream = true;
         int n_sm = p->n_sm;
         if (!n_sm) { cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, p->device); }
-        stream_geometry(uy1 - uy0, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
-        r.n_fast = r.st_nseg * r.st_nstrip;
+        // row bands: the rows a neighbour needs sit in short border segments that run first (ibp_stream.cu)
+        const int brows = 8 * kStreamBorderNit - 6;
+        if (p->band && p->nranks > 1 && uy1 - uy0 >= 4 * brows) {
+            r.st_bnit = kStreamBorderNit; r.st_btop = p->rank > 0; r.st_bbot = p->rank < p->nranks - 1;
+        }
+        stream_geometry(uy1 - uy0 - (r.st_btop + r.st_bbot) * brows, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
+        r.n_fast = (r.st_nseg + r.st_btop + r.st_bbot) * r.st_nstrip;
     } else if (sep_ok && p->path != 7 && (big || p->path >= 4)) {
         r.use_ws = (p->path == 0 || p->path == 4);
         if (r.use_ws) ibp_ws_tile(&fth, &ftw); else ibp_sep_tile(&fth, &ftw);
@@ -516,6 +521,7 @@ int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, c
         f.H = H_loc; f.W = p->W; f.h = h_loc; f.w = p->w;
         f.y_base = uy0 - p->hr_lo; f.y_end = uy1 - p->hr_lo;
         f.nit = r.st_nit; f.seg_rows = r.st_seg; f.nseg = r.st_nseg; f.nstrip = r.st_nstrip;
+        f.b_nit = r.st_bnit; f.b_top = r.st_btop; f.b_bot = r.st_bbot;
         f.alpha = g.alpha; f.lo = g.lo; f.hi = g.hi;
         memcpy(f.acol, p->acol, sizeof(f.acol));
         memcpy(f.brow, p->brow, sizeof(f.brow));
@@ -534,6 +540,7 @@ int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, c
             if (p->isy[k] == +1 && p->isx[k] == +1) f.m_msec += 1.f;
         }
         f.partial = partial;
+        if (p->kpush) f.bp = *p->kpush;                   // row bands: the kernel exchanges the halo rows itself
         return launch_ibp_stream(f, P, Q, st);
     }
     if (r.use_lat) {

@@ -28,7 +28,7 @@ using namespace sr459;
 namespace {
 constexpr int kLrMargin   = 32;          // extra LR rows beyond hr_lo/2 and hr_hi/2 the caller provides (SAA)
 constexpr int kFlagWords  = 64;          // 256 B at the head of the arena
-constexpr int F_FROM_UP = 0, F_FROM_DOWN = 1, F_ERROR = 2, F_EPOCH = 3, F_TICKET = 4;
+constexpr int F_FROM_UP = BF_FROM_UP, F_FROM_DOWN = BF_FROM_DOWN, F_ERROR = BF_ERROR, F_BASE = BF_BASE, F_TICKET = BF_TICKET;
 constexpr int kPushCtas   = 16;          // CTAs per direction
 }
 
@@ -82,6 +82,7 @@ struct PushArgs {
     unsigned* flags;               // my own flag words
     long long n4;                  // float4s per direction
     int has[2];
+    int it;                        // iteration within the run: publishes BASE + it + 1 and waits for the same from both neighbours
     unsigned long long timeout_ns;
 };
 
@@ -115,8 +116,7 @@ __global__ void __launch_bounds__(256) k_band_push(const __grid_constant__ PushA
     if (t != gridDim.x - 1) return;
     a.flags[F_TICKET] = 0;                                // re-armed for the next launch (stream order)
     __threadfence_system();
-    const unsigned epoch = a.flags[F_EPOCH] + 1u;
-    a.flags[F_EPOCH] = epoch;
+    const unsigned epoch = a.flags[F_BASE] + (unsigned)a.it + 1u;
     if (a.has[0]) st_release_sys(a.peer_flag[0], epoch);
     if (a.has[1]) st_release_sys(a.peer_flag[1], epoch);
     const unsigned long long t0 = globaltimer_ns();
@@ -130,15 +130,65 @@ __global__ void __launch_bounds__(256) k_band_push(const __grid_constant__ PushA
     }
 }
 
-static int band_push(sr459_plan* p, int buf, cudaStream_t st) {
+// end of a run of K iterations: wait until both neighbours' rows of the last iteration have arrived (so the halos are
+// valid and nobody still writes into this arena when the caller moves on), then advance the base of the arrival counts
+__global__ void k_band_advance(unsigned* flags, int K, int unit, int word_up, int has_up, int has_down, unsigned long long timeout_ns) {
+    const unsigned base = flags[F_BASE] + (unsigned)K;
+    const unsigned want = base * (unsigned)unit;          // arrivals are counted per pushing warp (in-kernel) or per launch (k_band_push)
+    const unsigned long long t0 = globaltimer_ns();
+    for (int d = 0; d < 2; ++d) {
+        if (!(d == 0 ? has_up : has_down)) continue;
+        const unsigned* f = flags + word_up + d;
+        while ((int)(ld_acquire_sys(f) - want) < 0) {
+            if (globaltimer_ns() - t0 > timeout_ns) { flags[F_ERROR] = 1u; break; }
+            __nanosleep(100);
+        }
+    }
+    flags[F_BASE] = base;
+}
+
+// what an iteration kernel needs to do the exchange itself (ibp_stream.cu); buf = the buffer the iteration writes
+static int band_fill_peer(sr459_plan* p, int buf, int it, const FusedRecipe& r, BandPeer* bp) {
+    BandState* bs = p->bs;
+    memset(bp, 0, sizeof(*bp));
+    const int W = p->W, R = p->halo;
+    const int o0 = 2 * p->own_i0 - p->hr_lo, o1 = 2 * p->own_i1 - p->hr_lo;
+    bp->flags = bs->flags; bp->it = it; bp->timeout_ns = 4000000000ull;
+    { static const int probe = getenv("SR459_BAND_PROBE") ? atoi(getenv("SR459_BAND_PROBE")) : 0; bp->probe = probe; }
+    for (int d = 0; d < 2; ++d) {
+        const bool has = d == 0 ? p->rank > 0 : p->rank < p->nranks - 1;
+        bp->has[d] = has ? 1 : 0;
+        bp->push_y0[d] = d == 0 ? o0 : o1 - R; bp->push_y1[d] = d == 0 ? o0 + R : o1;
+        if (!has) continue;
+        if (!bs->peer[d]) { set_error("band_run: neighbour %s is not attached (sr459_band_attach)", d == 0 ? "above" : "below"); return SR459_EINVAL; }
+        float* peer_buf = (float*)(bs->peer[d] + arena_off(buf, bs->peer_rows[d], W));
+        bp->peer_out[d] = peer_buf + ((ptrdiff_t)p->hr_lo - bs->peer_hr_lo[d]) * W;
+        bp->peer_flag[d] = (unsigned*)bs->peer[d] + (d == 0 ? BF_ARR_DOWN : BF_ARR_UP);
+        int segs = 0;                                     // segments of the streaming kernel with rows in the pushed range
+        if (r.st_bnit > 0) segs = 1;                      // the border segment (8 b_nit - 6 >= halo rows)
+        else
+            for (int sgm = 0; sgm < r.st_nseg; ++sgm) {
+                const int ya = o0 + sgm * r.st_seg, yb = std::min(ya + r.st_seg, o1);
+                if (ya < bp->push_y1[d] && yb > bp->push_y0[d]) ++segs;
+            }
+        bp->push_warps[d] = segs * r.st_nstrip;
+        bp->unit = r.st_nstrip;
+    }
+    return SR459_OK;
+}
+
+static int band_push(sr459_plan* p, int buf, int it, cudaStream_t st) {
     BandState* bs = p->bs;
     if (p->nranks == 1) return SR459_OK;
+    // development probe (tools/bench_bands.py --no-push): compute only, results are WRONG near the seams
+    { static const bool skip = getenv("SR459_BAND_NOPUSH") != nullptr; if (skip) return SR459_OK; }
     const int W = p->W, R = p->halo;
     const int rows = p->hr_hi - p->hr_lo;
     PushArgs a{};
     a.flags = bs->flags;
     a.n4 = (long long)R * W / 4;
     a.timeout_ns = 4000000000ull;
+    a.it = it;
     const int o0 = 2 * p->own_i0 - p->hr_lo, o1 = 2 * p->own_i1 - p->hr_lo;
     (void)rows;
     for (int d = 0; d < 2; ++d) {
@@ -464,29 +514,75 @@ int sr459_band_saa(sr459_plan* plan, const float* const* h_d_lr_ext, void* strea
     return band_saa(plan, h_d_lr_ext, (cudaStream_t)stream);
 }
 
+// Allocate (or grow) everything sr459_band_run(n_iter) needs.  Optional: band_run does it itself, but growing frees
+// device memory, which synchronises the whole device -- one process driving several bands of ONE GPU (tests) must not do
+// that while another band's loop is already waiting for this one.
+int sr459_band_reserve(sr459_plan* plan, const float* const* h_d_lr_ext, int n_iter, void* stream) {
+    SR_TRY(check_lr(plan, h_d_lr_ext));
+    if (!plan->band || n_iter < 0) { set_error("band_reserve: not a band plan or n_iter < 0"); return SR459_EINVAL; }
+    SR_DEVICE(plan->device);
+    SR_TRY(band_arena_alloc(plan));
+    if (n_iter == 0) return SR459_OK;
+    const float* lr_ibp[kMaxFrames];
+    for (int k = 0; k < plan->n; ++k) lr_ibp[k] = h_d_lr_ext[k] + (size_t)(plan->lr_lo - plan->bs->lr_ext_lo) * plan->w;
+    return band_prepare(plan, lr_ibp, n_iter, (cudaStream_t)stream);
+}
+
 // n_iter IBP iterations (run_sr.py:197-208) on the band's current buffer, the halo exchange after every iteration done
 // by k_band_push over peer memory.  Every rank of the image must make the same call.  Enqueues only; capturable.
-int sr459_band_run(sr459_plan* plan, const float* const* h_d_lr_ext, int n_iter, void* stream) {
+int sr459_band_run_range(sr459_plan* plan, const float* const* h_d_lr_ext, int it0, int it1, int n_iter, void* stream) {
     SR_TRY(check_lr(plan, h_d_lr_ext));
-    if (!plan->band || n_iter < 0) { set_error("band_run: not a band plan or n_iter < 0"); return SR459_EINVAL; }
+    if (!plan->band || n_iter < 0 || it0 < 0 || it1 < it0 || it1 > n_iter) { set_error("band_run: not a band plan or a bad iteration range"); return SR459_EINVAL; }
     SR_DEVICE(plan->device);
     cudaStream_t st = (cudaStream_t)stream;
     BandState* bs = plan->bs;
     SR_TRY(band_arena_alloc(plan));
-    if (n_iter == 0) return SR459_OK;
+    if (n_iter == 0 || it0 == it1) return SR459_OK;
     const float* lr_ibp[kMaxFrames];
     for (int k = 0; k < plan->n; ++k) lr_ibp[k] = h_d_lr_ext[k] + (size_t)(plan->lr_lo - bs->lr_ext_lo) * plan->w;
-    SR_TRY(band_prepare(plan, lr_ibp, n_iter, st));
-    for (int it = 0; it < n_iter; ++it) {
-        // iteration `it` reads buffer cur (owned rows + halos) and stores the owned rows of buffer cur^1; the push then
-        // fills the neighbours' halo rows of THEIR buffer cur^1 and returns once both neighbours have filled mine.
-        // Write-after-read: a neighbour last READ its cur^1 halos in iteration it-1, and it bumped my counter for
-        // iteration it-1 only after that kernel (stream order), which I waited for before starting iteration `it`.
-        SR_TRY(band_iterate(plan, lr_ibp, bs->hr[bs->cur], bs->hr[bs->cur ^ 1], it, st));
-        SR_TRY(band_push(plan, bs->cur ^ 1, st));
+    if (it0 == 0) SR_TRY(band_prepare(plan, lr_ibp, n_iter, st));
+    else if (!bs->recipe_valid || bs->iters != n_iter) { set_error("band_run: iterations must start at 0"); return SR459_EINVAL; }
+    FusedRecipe rec{};
+    if (!bs->child) rec = fused_recipe(plan, 2 * plan->own_i0, 2 * plan->own_i1);
+    // the streaming kernel (with its border segments) stores its boundary rows into the neighbours' buffers itself and
+    // its border warps wait for the neighbours' arrival counts; every other iteration kernel is followed by k_band_push
+    const bool probe_nopush = getenv("SR459_BAND_NOPUSH") != nullptr;
+    const bool in_kernel = !bs->child && rec.use_stream && rec.st_bnit > 0 && plan->nranks > 1 && !getenv("SR459_BAND_PUSH_KERNEL") && !probe_nopush;
+    for (int it = it0; it < it1; ++it) {
+        // iteration `it` reads buffer cur (owned rows + halos) and stores the owned rows of buffer cur^1; the boundary rows
+        // also go into the neighbours' halo rows of THEIR buffer cur^1, and iteration it+1 starts on the halo-reading part
+        // only once both neighbours' rows have arrived.  Write-after-read: a neighbour last READ its cur^1 halos in
+        // iteration it-1, and its arrivals for iteration it-1 were counted only after the warps that read them had
+        // finished; my halo-writing warps of iteration `it` waited for exactly that count before they started.
+        BandPeer bp;
+        if (in_kernel) { SR_TRY(band_fill_peer(plan, bs->cur ^ 1, it, rec, &bp)); plan->kpush = &bp; }
+        int rc = band_iterate(plan, lr_ibp, bs->hr[bs->cur], bs->hr[bs->cur ^ 1], it, st);
+        plan->kpush = nullptr;
+        SR_TRY(rc);
+        if (!in_kernel) SR_TRY(band_push(plan, bs->cur ^ 1, it, st));
         bs->cur ^= 1;
     }
     return SR459_OK;
+}
+
+// end of a run: wait for the neighbours' rows of the last iteration, advance the base of the arrival counts
+int sr459_band_run_close(sr459_plan* plan, void* stream) {
+    if (!plan || !plan->band || !plan->bs->recipe_valid) { set_error("band_run_close: no run is open"); return SR459_EINVAL; }
+    SR_DEVICE(plan->device);
+    BandState* bs = plan->bs;
+    if (plan->nranks == 1 || bs->iters == 0 || getenv("SR459_BAND_NOPUSH") || getenv("SR459_BAND_PROBE")) return SR459_OK;
+    FusedRecipe rec{};
+    if (!bs->child) rec = fused_recipe(plan, 2 * plan->own_i0, 2 * plan->own_i1);
+    const bool in_kernel = !bs->child && rec.use_stream && rec.st_bnit > 0 && !getenv("SR459_BAND_PUSH_KERNEL");
+    k_band_advance<<<1, 1, 0, (cudaStream_t)stream>>>(bs->flags, bs->iters, in_kernel ? rec.st_nstrip : 1, in_kernel ? BF_ARR_UP : BF_FROM_UP,
+                                                      plan->rank > 0, plan->rank < plan->nranks - 1, 4000000000ull);
+    SR_LAUNCH_CHECK("k_band_advance");
+    return SR459_OK;
+}
+
+int sr459_band_run(sr459_plan* plan, const float* const* h_d_lr_ext, int n_iter, void* stream) {
+    SR_TRY(sr459_band_run_range(plan, h_d_lr_ext, 0, n_iter, n_iter, stream));
+    return n_iter > 0 ? sr459_band_run_close(plan, stream) : SR459_OK;
 }
 
 // the old two-call form (caller-owned buffers, exchange done by the host layer) stays available

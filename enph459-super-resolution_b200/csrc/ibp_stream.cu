@@ -23,6 +23,7 @@
 #include "internal.h"
 #include "tma.h"
 
+#include <stdlib.h>
 #include <algorithm>
 
 namespace sr459 {
@@ -208,6 +209,21 @@ __device__ __forceinline__ void back_row(const LaneConst& k, float r1, float r2,
 
 __device__ __forceinline__ float clipf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
 
+// ---- row bands: system-scope flag accesses (the arrival counters are written by the neighbouring GPUs) ----------------------
+__device__ __forceinline__ unsigned ld_acquire_sys_u32(const unsigned* p) {
+    unsigned v;
+    asm volatile("ld.acquire.sys.global.u32 %0, [%1];" : "=r"(v) : "l"(p) : "memory");
+    return v;
+}
+__device__ __forceinline__ void st_release_sys_u32(unsigned* p, unsigned v) {
+    asm volatile("st.release.sys.global.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+    unsigned long long t;
+    asm volatile("mov.u64 %0, %globaltimer;" : "=l"(t));
+    return t;
+}
+
 // what a warp knows about itself (uniform across the warp)
 struct WarpCtx {
     int ya, yb;               // HR rows this warp updates (and whose sites it owns for the MSE)
@@ -215,6 +231,7 @@ struct WarpCtx {
     int h;                    // LR rows (site rows are 0..h-1)
     bool top;                 // ya == 0 and the lattice has row parity 1: the clamp terms of HR row 0 apply
     int x0;                   // first owned column
+    bool push[2];             // row bands: some of this warp's rows also go to the band above / below
 };
 
 // One lattice row.  T = step mod 4 fixes every register slot at compile time:
@@ -349,6 +366,15 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
         if (GEN) { st1 = st1 && (y1 >= c.ya) && (y1 < c.yb); st2 = st2 && (y1 + 1 >= c.ya) && (y1 + 1 < c.yb); }
         if (st1) *reinterpret_cast<float4*>(outp) = q1;
         if (st2) *reinterpret_cast<float4*>(outp + a.W) = q2;
+        if (GEN) {                                          // row bands: boundary rows go straight into the neighbours' halo rows
+            #pragma unroll
+            for (int d = 0; d < 2; ++d) {
+                if (!c.push[d] || (a.bp.probe & 2)) continue;
+                float* pp = a.bp.peer_out[d] + (outp - a.hr_out);
+                if (st1 && y1 >= a.bp.push_y0[d] && y1 < a.bp.push_y1[d]) *reinterpret_cast<float4*>(pp) = q1;
+                if (st2 && y1 + 1 >= a.bp.push_y0[d] && y1 + 1 < a.bp.push_y1[d]) *reinterpret_cast<float4*>(pp + a.W) = q2;
+            }
+        }
     }
     outp += 2 * a.W;
 }
@@ -393,22 +419,32 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     __shared__ __align__(8) uint64_t bars_all[SS_WARPS][SS_STAGES];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int gw = blockIdx.x * SS_WARPS + warp;
-    if (gw >= a.nseg * a.nstrip) return;                 // whole warps only; nothing below synchronises the CTA
-    const int strip = gw % a.nstrip, seg = gw / a.nstrip;
+    const int nbw = (a.b_top + a.b_bot) * a.nstrip;      // border warps come first (row bands)
+    if (gw >= nbw + a.nseg * a.nstrip) return;           // whole warps only; nothing below synchronises the CTA
     float* ring = sm + warp * (SS_STAGES * SS_STAGE_FLOATS);
     uint64_t* bars = bars_all[warp];
 
     WarpCtx c;
+    int strip, nit;
+    const int brows = 8 * a.b_nit - 6;
+    if (gw < nbw) {
+        strip = gw % a.nstrip; nit = a.b_nit;
+        const bool is_top = a.b_top && gw < a.nstrip;
+        c.ya = is_top ? a.y_base : a.y_end - brows;
+        c.yb = c.ya + brows;
+    } else {
+        const int g2 = gw - nbw;
+        strip = g2 % a.nstrip; nit = a.nit;
+        c.ya = a.y_base + a.b_top * brows + (g2 / a.nstrip) * a.seg_rows;   // segments partition the rows between the border zones
+        c.yb = min(c.ya + a.seg_rows, a.y_end - a.b_bot * brows);
+    }
     c.x0 = strip * SS_VALID;
-    c.ya = a.y_base + seg * a.seg_rows;                  // segments partition the rows this launch updates
-    c.yb = min(c.ya + a.seg_rows, a.y_end);
     c.h = a.h;
     c.top = (P == 1) && (c.ya == 0);
     const int ys0 = c.ya - 3 + (1 - P);                  // first site row the segment needs (parity P)
     c.a0 = (ys0 - P) >> 1;                               // exact: ys0 - P is even
     const int sb = ys0 + 2;                              // first NEW hr row of step 0
     const int xs0 = c.x0 - 8;
-    const int nit = a.nit;
 
     // programmatic dependent launch: the next iteration's grid may start (and run everything above and the
     // barrier set-up below) while this one drains; nothing written by the previous grid is touched before the wait
@@ -420,6 +456,29 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
         asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
     }
     asm volatile("griddepcontrol.wait;\n" ::: "memory");
+    // row bands: the warps whose windows reach into a halo wait until the neighbour's rows of the previous iteration have
+    // arrived (its counter reaches BASE + it); everybody else starts at once
+    c.push[0] = c.push[1] = false;
+    if (a.bp.flags != nullptr) {
+        c.push[0] = a.bp.has[0] && c.ya < a.bp.push_y1[0];
+        c.push[1] = a.bp.has[1] && c.yb > a.bp.push_y0[1];
+        const bool need_up = a.bp.has[0] && (c.ya - 8 < a.bp.push_y0[0]);
+        const bool need_dn = a.bp.has[1] && (c.yb + 8 > a.bp.push_y1[1]);
+        if ((need_up || need_dn) && lane == 0 && !(a.bp.probe & 1)) {
+            const unsigned want = (a.bp.flags[BF_BASE] + (unsigned)a.bp.it) * (unsigned)a.bp.unit;
+            const unsigned long long t0 = gtimer_ns();
+            #pragma unroll
+            for (int d = 0; d < 2; ++d) {
+                if (!(d == 0 ? need_up : need_dn)) continue;
+                const unsigned* f = a.bp.flags + (d == 0 ? BF_ARR_UP : BF_ARR_DOWN);
+                while ((int)(ld_acquire_sys_u32(f) - want) < 0) {
+                    if (gtimer_ns() - t0 > a.bp.timeout_ns) { a.bp.flags[BF_ERROR] = 1u; break; }
+                    __nanosleep(64);
+                }
+            }
+        }
+        __syncwarp();
+    }
     if (lane == 0) {
         #pragma unroll
         for (int st = 0; st < SS_STAGES; ++st) stream_issue(a, ring, bars, st, xs0, sb, c.a0);
@@ -495,7 +554,7 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
                 pat |= (m & 3) << (2 * t);
             }
             const int FAST = M_OWN | M_ST;
-            if (nf) kind = 3;
+            if (nf || c.push[0] || c.push[1]) kind = 3;     // pushing warps take the general form (it has the peer stores)
             else if (pat == (FAST | FAST << 2 | FAST << 4 | FAST << 6)) kind = 0;
             else if (pat == (0 | 0 << 2 | M_OWN << 4 | FAST << 6)) kind = 1;
             else if (pat == (FAST | FAST << 2 | FAST << 4 | M_ST << 6)) kind = 2;
@@ -522,6 +581,17 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     #pragma unroll
     for (int off = 16; off > 0; off >>= 1) e2 += __shfl_xor_sync(0xffffffffu, e2, off);
     if (lane == 0) a.partial[gw] = (double)e2;
+
+    // row bands: once my peer stores are visible system-wide, count my arrival in the neighbour's arena (one remote
+    // atomic per pushing warp; the neighbour waits for `unit` of them per iteration)
+    if ((c.push[0] || c.push[1]) && !(a.bp.probe & 4)) {
+        __threadfence_system();
+        __syncwarp();
+        if (lane == 0) {
+            if (c.push[0]) atomicAdd_system(a.bp.peer_flag[0], 1u);
+            if (c.push[1]) atomicAdd_system(a.bp.peer_flag[1], 1u);
+        }
+    }
 }
 
 void stream_geometry(int H, int W, int n_sm, int* nit_out, int* seg_rows, int* nseg_out, int* nstrip_out) {
@@ -556,7 +626,7 @@ int launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const i
 }
 
 int launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st) {
-    const int warps = a.nseg * a.nstrip;
+    const int warps = (a.nseg + a.b_top + a.b_bot) * a.nstrip;
     if (warps <= 0) return SR459_OK;
     const size_t smem = sizeof(float) * (size_t)SS_WARPS * SS_STAGES * SS_STAGE_FLOATS;
     static PerDeviceOnce configured;
@@ -572,7 +642,7 @@ int launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st) {
     cudaLaunchAttribute attr[1];
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
-    cfg.attrs = attr; cfg.numAttrs = 1;
+    { static const bool no_pdl = getenv("SR459_NO_PDL") != nullptr; cfg.attrs = attr; cfg.numAttrs = no_pdl ? 0 : 1; }
     cudaError_t le;
     switch (P * 2 + Q) {
         case 0: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 0>, a); break;

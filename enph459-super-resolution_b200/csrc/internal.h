@@ -290,6 +290,22 @@ int    ws_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int 
 int    sep_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
 int    sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
 
+// ---- row bands: flag words at the head of a band arena, and what an iteration kernel needs to exchange halos itself (bands.cu)
+constexpr int BF_FROM_UP = 0, BF_FROM_DOWN = 1, BF_ERROR = 2, BF_BASE = 3, BF_TICKET = 4, BF_ARR_UP = 5, BF_ARR_DOWN = 6;
+struct BandPeer {
+    unsigned* flags;                    // my flag words (null: no in-kernel exchange)
+    unsigned* peer_flag[2];             // the arrival counter (BF_ARR_*) of the band above / below: one remote add per pushing warp
+    float* peer_out[2];                 // the neighbour's copy of the buffer this launch writes, biased so that
+                                        // [local row * W + x] is the same global pixel as in my buffer
+    int push_y0[2], push_y1[2];         // local rows that are ALSO stored to the band above / below
+    int push_warps[2];                  // warps with a share in those rows
+    int unit;                           // arrivals per iteration and direction (= strips): wait for unit * (BASE + it)
+    int has[2];
+    int it;                             // iteration within the run: wait for BASE + it, publish BASE + it + 1
+    unsigned long long timeout_ns;
+    int probe;                          // development timing probes (SR459_BAND_PROBE): 1 no waits, 2 no peer stores, 4 no fence / publish
+};
+
 // ---- register-streaming fused iteration (ibp_stream.cu): one lattice, rank-1 PSF, whole image ---------
 struct alignas(64) StreamArgs {
     CUtensorMap tm_hr;                  // hr_in as a {W, H} tensor, box 128 x 8
@@ -299,7 +315,9 @@ struct alignas(64) StreamArgs {
     int y_base, y_end;                  // rows this launch updates, partitioned into segments (whole image: 0, H)
     int nit;                            // loop iterations (4 lattice rows each) per warp
     int seg_rows;                       // HR rows a warp updates = 8 nit - 6
-    int nseg, nstrip;                   // warps = nseg * nstrip
+    int nseg, nstrip;                   // interior warps = nseg * nstrip
+    int b_nit, b_top, b_bot;            // row bands: short border segments (8 b_nit - 6 rows) at the band's top / bottom edge, mapped to
+                                        // the FIRST warps of the grid so that their rows reach the neighbours while the interior still runs
     float alpha, lo, hi;
     float acol[7], brow[7];
     float mtab[4];                      // frames with a sample at a site: [2*(last site row) + (last site col)]
@@ -309,6 +327,7 @@ struct alignas(64) StreamArgs {
     float mr[2], mt[2];                 // frames with sy = -1 / +1 valid at a site col: [last site col]
     float m_dupc, m_msec;               // frames (-1,-1) / (+1,+1)
     double* partial;                    // one slot per warp
+    BandPeer bp;                        // row bands: halo rows stored straight into the neighbours' buffers
 };
 struct EdgeSumArgs;
 int  launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st);
@@ -316,6 +335,7 @@ bool ibp_stream_supported(int kh, int kw, int smax, bool separable, int W, int n
 int  stream_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
 int  stream_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
 void stream_geometry(int H, int W, int n_sm, int* nit, int* seg_rows, int* nseg, int* nstrip);
+constexpr int kStreamBorderNit = 2;     // border segments of row bands: 10 rows (>= the 8 rows a neighbour needs)
 // edge vectors + their variances (added to *vsum); buf holds 2h + 2w + 4 floats: colS1, leftS1, rowS1, topS1, scal
 int  launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const int* sy, const int* sx, int P, int Q,
                              float* buf, double* vsum, int own_a0, int own_a1, int top_owned, cudaStream_t st);

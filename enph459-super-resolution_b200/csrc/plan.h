@@ -106,6 +106,7 @@ struct sr459_plan {
     // -1 = everything)
     int store_y0 = -1, store_y1 = -1, mse_i0 = -1, mse_i1 = -1;
     BandState* bs = nullptr;              // row-band plans (bands.cu)
+    const BandPeer* kpush = nullptr;      // set by band_run around one iteration: the kernel exchanges the halo rows itself
 };
 
 template <typename T>
@@ -126,6 +127,7 @@ struct FusedRecipe {
     bool use_stream;
     bool use_lat;
     int st_nit, st_seg, st_nseg, st_nstrip;
+    int st_bnit, st_btop, st_bbot;        // row bands: border segments of the streaming kernel (internal.h StreamArgs)
     int fast_tx, fast_ty;
     DensePass all;
     int n_fast, n_all, per_iter;

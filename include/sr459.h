@@ -209,9 +209,16 @@ int sr459_band_attach(sr459_plan* plan, const unsigned char* up_handle64, void* 
                       const unsigned char* down_handle64, void* down_arena, int down_device);
 /* shift_and_add restricted to this band (halo rows included) from LR rows only -> the current buffer             */
 int sr459_band_saa(sr459_plan* plan, const float* const* h_d_lr_ext, void* stream);
+/* optional: allocate / grow what sr459_band_run(n_iter) needs now (growing frees device memory = a device-wide sync) */
+int sr459_band_reserve(sr459_plan* plan, const float* const* h_d_lr_ext, int n_iter, void* stream);
 /* n_iter iterations on the current buffer; after each one a kernel stores the band's boundary rows into the
  * neighbours' halo rows and waits for theirs.  Every rank must make the same calls.  Enqueues only (capturable).   */
 int sr459_band_run(sr459_plan* plan, const float* const* h_d_lr_ext, int n_iter, void* stream);
+/* the iterations [it0, it1) of a run of n_iter (it0 == 0 prepares; sr459_band_run_close ends it): one process driving
+ * several bands of ONE GPU interleaves the bands iteration by iteration, so that no kernel ever waits for one that is
+ * enqueued behind it (streams of one device may share a hardware queue)                                            */
+int sr459_band_run_range(sr459_plan* plan, const float* const* h_d_lr_ext, int it0, int it1, int n_iter, void* stream);
+int sr459_band_run_close(sr459_plan* plan, void* stream);
 /* two-call form with caller-owned buffers (LR rows [lr_lo, lr_hi)) and the exchange left to the host layer:
  * once per ibp() call ...                                                                                          */
 int sr459_band_begin(sr459_plan* plan, const float* const* h_d_lr_local, int n_iter, void* stream);

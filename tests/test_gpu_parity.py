@@ -613,42 +613,42 @@ def test_row_bands_peer_memory_path_vs_oracle(sr, world, case):
     _errs_close(errs, e_o)
 
 
-def test_row_bands_peer_memory_graph_replay_and_reuse(sr):
-    """One band per rank is the same code with world 1; here two bands, the loop captured in a CUDA graph per band and
-    replayed twice (the second job re-uses plans, graphs and arenas), odd iteration counts refused for a second replay."""
+def test_row_bands_peer_memory_graph_replay_two_gpus(sr):
+    """One band per GPU inside one process (peer access instead of cudaIpc): each band's whole loop captured in a CUDA
+    graph and replayed for a second job that re-uses plans, graphs and arenas.  Needs two GPUs: on ONE device a band's
+    captured loop would wait for kernels of the other band that the device may only run afterwards (streams of one
+    device can share a hardware queue); the single-GPU emulation interleaves iteration by iteration instead
+    (run_emulated_peer), and bench.py --gpus N replays the graphs with one process per GPU."""
+    import threading
     import torch
     from sr459.bands import BandPlan
+    if torch.cuda.device_count() < 2:
+        pytest.skip("needs two GPUs")
     rng = np.random.default_rng(33)
     h, w, K = 128, 96, 6
     psf = O.make_gaussian_psf()
-    plans = [BandPlan(4, h, w, NOMINAL, psf, r, 2) for r in range(2)]
+    plans = [BandPlan(4, h, w, NOMINAL, psf, r, 2, device=r) for r in range(2)]
     plans[0].attach_local(None, plans[1]); plans[1].attach_local(plans[0], None)
-    streams = [torch.cuda.Stream() for _ in plans]
+    exts = None
     for job in range(2):
         lrs = [rng.uniform(0, 255, (h, w)) for _ in NOMINAL]
         saa_o = O.shift_and_add_integer(lrs, NOMINAL)
         hr_o, e_o = O.ibp_integer_shifts(lrs, NOMINAL, psf, saa_o, n_iter=K)
-        if job == 0:
-            exts = [[torch.from_numpy(l[p.layout.lr_ext_lo:p.layout.lr_ext_hi].astype(np.float32)).cuda() for l in lrs] for p in plans]
+        if exts is None:
+            exts = [[torch.from_numpy(l[p.layout.lr_ext_lo:p.layout.lr_ext_hi].astype(np.float32)).to(f"cuda:{p.device}") for l in lrs] for p in plans]
         else:
             for p, ext in zip(plans, exts):
                 for t, l in zip(ext, lrs):
                     t.copy_(torch.from_numpy(l[p.layout.lr_ext_lo:p.layout.lr_ext_hi].astype(np.float32)))
-        torch.cuda.synchronize()
-        sums = []
-        for p, st, ext in zip(plans, streams, exts):
-            with torch.cuda.stream(st):
-                p.saa(ext)
-        torch.cuda.synchronize()
-        import threading
         out = [None, None]
 
         def go(i):
-            with torch.cuda.stream(streams[i]):
-                out[i] = plans[i].run_peer(exts[i], K, graph=(job == 1), reduce=False) if job == 1 else plans[i].run_peer(exts[i], K, reduce=False)
+            with torch.cuda.device(plans[i].device):
+                plans[i].saa(exts[i])
+                out[i] = plans[i].run_peer(exts[i], K, graph=(job == 1), reduce=False)
+                torch.cuda.synchronize()
         ths = [threading.Thread(target=go, args=(i,)) for i in range(2)]
         [t.start() for t in ths]; [t.join() for t in ths]
-        torch.cuda.synchronize()
         hr = np.zeros((2 * h, 2 * w), dtype=np.float32)
         for p in plans:
             lay = p.layout

@@ -2,13 +2,13 @@
 """Row-band IBP of ONE 3072x4096 HR image across N GPUs (BASELINE config 4), launched by torchrun:
 
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 --master-port P \
-        tools/bench_bands.py [--psf gaussian7|measured31] [--iters 200] [--h 1536 --w 2048] [--check]
+        tools/bench_bands.py [--psf gaussian7|measured31|measured7] [--iters 200] [--h 1536 --w 2048] [--fractional]
 
-Every rank owns a band of HR rows, runs the fused iteration kernel on it and exchanges halo rows with
-its neighbours through NCCL send/recv after each iteration (sr459.bands).  Timing: CUDA events around
-the K-iteration loop, barrier on both sides, max over ranks.  --check also runs the whole image on
-rank 0 alone and compares (bands must reproduce the single-GPU result to float32 round-off).
-Prints one JSON line on rank 0.
+Every rank owns a band of HR rows, builds its initial image from its own LR rows (banded SAA) and runs the iteration
+kernels on it; the halo rows travel as peer-memory stores from k_band_push (csrc/bands.cu).  The loop is one CUDA graph.
+Timing: CUDA events around the replay, barrier on both sides, per-rank values and the max.  SR459_BAND_NOPUSH=1 in the
+environment skips the exchange (compute-only probe; the seams are then wrong).  The measured PSFs are the committed
+reference-generated ones (tests/golden/g_psf.npz).  Prints one JSON line on rank 0.
 """
 import argparse
 import json
@@ -20,24 +20,17 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 sys.path.insert(0, ROOT)
 NOMINAL = [(+0.5, -0.5), (+0.5, +0.5), (-0.5, -0.5), (-0.5, +0.5)]
-
-
-def synthetic_psf31():
-    """A non-separable 31x31 stand-in for the measured pinhole PSF (the pinhole PNGs do not travel)."""
-    y, x = np.mgrid[-15:16, -15:16].astype(np.float64)
-    k = np.exp(-(x * x / 18.0 + y * y / 8.0 + 0.05 * x * y)) + 0.15 * np.exp(-((x - 4) ** 2 + (y + 3) ** 2) / 6.0)
-    k[np.abs(k) < 1e-4 * k.max()] = 0.0
-    return k / k.sum()
+CALIBRATED = [(0.47225, -0.43385), (0.4897, 0.4641), (-0.4798, -0.4553), (-0.4856, 0.4369)]
 
 
 def main():
     ap = argparse.ArgumentParser()
-    ap.add_argument("--psf", choices=["gaussian7", "measured31"], default="measured31")
+    ap.add_argument("--psf", choices=["gaussian7", "measured31", "measured7"], default="measured31")
     ap.add_argument("--iters", type=int, default=200)
     ap.add_argument("--h", type=int, default=1536)
     ap.add_argument("--w", type=int, default=2048)
-    ap.add_argument("--check", action="store_true")
-    ap.add_argument("--graph", action="store_true", help="capture the K-iteration loop (kernels + NCCL send/recv) into one CUDA graph")
+    ap.add_argument("--fractional", action="store_true")
+    ap.add_argument("--reps", type=int, default=3)
     args = ap.parse_args()
 
     import torch
@@ -47,71 +40,58 @@ def main():
 
     world = int(os.environ.get("WORLD_SIZE", "1")); rank = int(os.environ.get("RANK", "0")); local = int(os.environ.get("LOCAL_RANK", "0"))
     torch.cuda.set_device(local)
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
     if world > 1:
-        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    g = np.load(os.path.join(ROOT, "tests", "golden", "g_psf.npz"))
+    psf = {"gaussian7": sr459.make_gaussian_psf(), "measured31": g["k31"], "measured7": g["k7"]}[args.psf]
+    shifts = CALIBRATED if args.fractional else NOMINAL
     h, w, K = args.h, args.w, args.iters
-    psf = sr459.make_gaussian_psf() if args.psf == "gaussian7" else synthetic_psf31()
     rng = np.random.default_rng(459)                       # identical on every rank
-    lrs = [rng.uniform(0, 255, (h, w)).astype(np.float32) for _ in NOMINAL]
-    full_plan = sr459.Plan(4, h, w, NOMINAL, psf)
-    d_lrs = [torch.from_numpy(f).cuda() for f in lrs]
-    saa = full_plan.saa(d_lrs)                              # every rank builds the same initial image
+    lrs = [torch.from_numpy(rng.uniform(0, 255, (h, w)).astype(np.float32)).cuda() for _ in shifts]
 
-    bp = BandPlan(4, h, w, NOMINAL, psf, rank, world)
-    lay = bp.layout
-    lr_local = [f[lay.lr_lo:lay.lr_hi].contiguous() for f in d_lrs]
-
-    def barrier():
+    def sync():
+        torch.cuda.synchronize()
         if world > 1:
             dist.barrier()
         torch.cuda.synchronize()
 
-    def once(k_iter):
-        hr_local = saa[lay.hr_lo:lay.hr_hi].clone()
-        barrier()
-        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        e0.record()
-        res, errs = bp.run(lr_local, hr_local, k_iter, graph=args.graph)
-        e1.record()
-        barrier()
-        return res, errs, (bp.last_loop_ms if args.graph else e0.elapsed_time(e1))
-
-    once(min(K, 5))                                         # warm-up (NCCL channels, plan scratch)
-    res, errs, ms = once(K)
-    t = torch.tensor([ms], dtype=torch.float64, device="cuda")
+    bp = BandPlan(4, h, w, shifts, psf, rank, world)
     if world > 1:
-        dist.all_reduce(t, op=dist.ReduceOp.MAX)
-    ms = float(t.item())
+        bp.attach()
+    lay = bp.layout
+    ext = [f[lay.lr_ext_lo:lay.lr_ext_hi].contiguous() for f in lrs]
+    bp.saa(ext)
+    bp.run_peer(ext, K, reduce=False)                        # eager warm-up: lazy scratch sized by K
+    sync()
+    runs, errs = [], None
+    for rep in range(args.reps + 1):
+        bp.saa(ext)
+        sync()
+        errs = bp.run_peer(ext, K, graph=True, reduce=False)
+        sync()
+        if rep:
+            runs.append(bp.last_loop_ms)
+    t = torch.tensor([min(runs)], dtype=torch.float64, device="cuda")
+    allt = [torch.zeros_like(t) for _ in range(world)]
+    if world > 1:
+        dist.all_gather(allt, t)
+    else:
+        allt = [t]
+    per_rank = [float(x.item()) for x in allt]
     line = {
-        "workload": f"config4: one {2*h}x{2*w} HR image, 4 frames, {args.psf} PSF, {K} IBP iterations, {world} row band(s), "
-                    f"halo {lay.halo} rows exchanged by NCCL send/recv every iteration",
-        "n_gpus": world, "iters": K, "cuda_graph": bool(args.graph), "ms_total": ms, "ms_per_iteration": ms / K,
-        "hr_mpix_per_s": (4.0 * h * w / 1e6) / (ms / 1e3), "final_mse": errs[-1] if errs else None,
+        "workload": f"config4: one {2*h}x{2*w} HR image, 4 frames, {args.psf} PSF, {'fractional' if args.fractional else 'integer'} shifts, "
+                    f"{K} IBP iterations, {world} row band(s), halo {lay.halo} rows; {bp.exchange_kind}",
+        "n_gpus": world, "iters": K, "no_push_probe": bool(os.environ.get("SR459_BAND_NOPUSH")),
+        "us_per_iteration": 1e3 * max(per_rank) / K, "per_rank_us_per_iteration": [1e3 * x / K for x in per_rank],
+        "hr_mpix_per_s": (4.0 * h * w / 1e6) / (max(per_rank) / 1e3),
         "halo_bytes_per_iteration_per_neighbour": lay.halo * lay.W * 4,
     }
-    if args.check:
-        owned = res[lay.owned].contiguous()
-        hr_full = saa.clone()
-        ref_errs = full_plan.ibp_(d_lrs, hr_full, K)
-        d = float((owned - hr_full[lay.own_y0:lay.own_y1]).abs().max().item())
-        dt = torch.tensor([d], dtype=torch.float64, device="cuda")
-        if world > 1:
-            dist.all_reduce(dt, op=dist.ReduceOp.MAX)
-        line["max_abs_vs_single_gpu"] = float(dt.item())
-        line["mse_rel_vs_single_gpu"] = float(np.max(np.abs(np.array(errs) / np.array(ref_errs) - 1.0)))
     if rank == 0:
         print(json.dumps(line), flush=True)
-    if args.graph:
-        # a process group whose NCCL communicator has work captured in a CUDA graph does not tear down cleanly
-        # (destroy_process_group blocks); everything is measured and printed, so leave without the teardown
-        torch.cuda.synchronize()
-        if world > 1:
-            dist.barrier()
-        sys.stdout.flush(); sys.stderr.flush()
-        os._exit(0)
-    bp.close(); full_plan.close()
+    bp.close()
     if world > 1:
+        dist.barrier()
         dist.destroy_process_group()
 
 
