@@ -86,6 +86,12 @@ _SIGNATURES = {
     "sr459_band_begin": (_I, [_P, _PP, _I, _P]),
     "sr459_band_iterate": (_I, [_P, _PP, _P, _P, _I, _P]),
     "sr459_band_errors": (_I, [_P, _I, _PD, _P]),
+    "sr459_find_peaks": (_I, [_P, _I, _I, _I, _I, _D, _PI, _P, _P]),
+    "sr459_pinhole_fit": (_I, [_P, _I, _I, _I, _I, _PI, _I, _D, _I, _PD, _PD, _PI, _P]),
+    "sr459_psf_mtf": (_I, [_PD, _I, _I, _I, _PD, _PD, _P]),
+    "sr459_edge_mtf": (_I, [_P, _I, _I, _I, _I, _I, _I, _I, _D, _PD, _PD, _PD, _PD, _PD, _PD, _P]),
+    "sr459_edge_mtf_capacity": (_I, []),
+    "sr459_local_contrast": (_I, [_PD, _I, _I, _PD, _P]),
 }
 
 

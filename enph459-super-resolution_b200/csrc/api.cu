@@ -24,7 +24,7 @@ void set_error(const char* fmt, ...) {
 
 // numpy's pairwise summation (np.sum / np.mean on a contiguous 1-d float64 run), so that PSF
 // normalisation reproduces the reference's rounding.
-static double np_pairwise_sum(const double* a, size_t n) {
+double np_pairwise_sum(const double* a, size_t n) {
     if (n < 8) {
         double r = 0.0;
         for (size_t i = 0; i < n; ++i) r += a[i];

@@ -14,6 +14,9 @@ void set_error(const char* fmt, ...);
 extern std::atomic<uint64_t> g_launches;
 inline void count_launch(int n = 1) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
 
+// numpy's pairwise summation of a contiguous float64 run (api.cu)
+double np_pairwise_sum(const double* a, size_t n);
+
 // every device allocation of the library goes through these (alloc.cu: optional guard bands)
 cudaError_t gmalloc(void** p, size_t bytes);
 void gfree(void* p);

@@ -229,6 +229,44 @@ int sr459_band_iterate(sr459_plan* plan, const float* const* h_d_lr_local, const
  * and divides by n*h*w as run_sr.py:202,206 do).  Synchronises the stream; SR459_ECUDA if an exchange timed out.   */
 int sr459_band_errors(sr459_plan* plan, int n_iter, double* h_sums, void* stream);
 
+/* ---- shift calibration / PSF characterisation ------------------------------------------------- */
+/* find_peak(img, smooth_sigma=2.0)                data_collection/psf_mtf_utils.py:48-51, batched: for each of the
+ * n_img images (uint8 or float32, H x W, contiguous one after the other) the flat index row*W+col of the FIRST maximum
+ * of scipy's gaussian_filter(img, sigma) (float64, boundary 'reflect', truncate 4).  sigma <= 3.  d_smooth_out (may be
+ * NULL): n_img*H*W doubles receiving the smoothed images.  Synchronises the stream.                                 */
+int sr459_find_peaks(const void* d_imgs, int is_f32, int n_img, int H, int W, double sigma, int* h_peaks,
+                     double* d_smooth_out, void* stream);
+/* find_pinhole_center(img)        calibration_beam_shift/calibrate_shift_grid.py:66-96, batched, from the peaks on:
+ * extract_psf (psf_mtf_utils.py:54-71: ROI of +-radius around the peak, clipped at the image, minus the bg_percentile
+ * of the ring >= 0.6*radius from the ROI centre, clamped at 0), fit_gaussian_psf (:115-131: 7-parameter rotated Gaussian,
+ * same start point and bounds; projected Levenberg-Marquardt, at most max_iter accepted steps), and the centre-of-mass
+ * fall-back (:88-96).  h_out: 12 doubles per image = cx, cy (image coordinates), amp, x0, y0, sigma_x, sigma_y, theta,
+ * offset (ROI coordinates; NaN without a fit), status (0 fit, 1 centre of mass, 2 peak), peak row, peak col.
+ * h_roi (may be NULL): 31*31 doubles per image, the background-subtracted ROI with row pitch = its width;
+ * h_roi_dims (may be NULL): rows, cols, first row, first col per image.  radius <= 15.  is_f32 == 2: float64 images;
+ * bg_percentile < 0: no background removal (fit_gaussian_psf on a ready-made ROI).  Synchronises the stream.           */
+int sr459_pinhole_fit(const void* d_imgs, int is_f32, int n_img, int H, int W, const int* h_peaks, int radius,
+                      double bg_percentile, int max_iter, double* h_out, double* h_roi, int* h_roi_dims, void* stream);
+/* compute_mtf(psf)                                 psf_mtf_utils.py:134-170: the PSF (host, float64, ph x pw) centred in
+ * a pad x pad zero array (pad even), normalised to unit sum, |DFT2| with the origin at the centre, normalised to its
+ * maximum; h_radial: pad/2 ring means about (pad/2, pad/2); h_mtf2d (may be NULL): pad*pad.  Synchronises.          */
+int sr459_psf_mtf(const double* h_psf, int ph, int pw, int pad, double* h_mtf2d, double* h_radial, void* stream);
+
+/* ---- quality analytics on HR outputs ------------------------------------------------------------ */
+/* slanted_edge_esf(roi, side) + esf_to_mtf + mtf_at_fraction   mono_cal_target/analysis.ipynb cells 7 and 10, for the
+ * ROI [ry0, ry0+rh) x [rx0, rx0+rw) of a device image (uint8 or float32, row pitch in elements).  right_side: 0 = 'left'.
+ * Outputs (host, each may be NULL, capacity sr459_edge_mtf_capacity() doubles): esf_x, esf_y, lsf (n_esf values), freq
+ * and mtf (n_esf / 2 values, cycles per pixel).  h_scal (8 doubles): status, n_esf, edge angle in degrees, MTF50 and
+ * MTF10 in cycles/mm at pixel pitch pitch_mm (NaN where the notebook's function returns nan), number of edge pixels,
+ * number on the chosen side, gradient threshold.  The notebook's RuntimeErrors come back as SR459_EINVAL with the same
+ * text in sr459_last_error().  Synchronises the stream.                                                               */
+int sr459_edge_mtf(const void* d_img, int is_f32, int pitch, int ry0, int rx0, int rh, int rw, int right_side,
+                   double pitch_mm, double* h_esf_x, double* h_esf_y, double* h_lsf, double* h_freq, double* h_mtf,
+                   double* h_scal, void* stream);
+int sr459_edge_mtf_capacity(void);
+/* local_contrast(profile, window=20)               analysis.ipynb cell 4 (host arrays in and out)                    */
+int sr459_local_contrast(const double* h_profile, int n, int window, double* h_out, void* stream);
+
 #if defined(__GNUC__)
 #pragma GCC visibility pop
 #endif

@@ -1,4 +1,4 @@
-"""sr459.analysis against the reference notebook's own functions.
+"""oracle/analysis_oracle.py (the numpy checker of sr459.analysis) against the reference notebook's own functions.
 
 Golden vectors: tests/golden/g_analysis.npz, produced by tests/golden/make_golden_analysis.py, which exec's the
 function cells of /root/reference/mono_cal_target/analysis.ipynb unmodified.  Bars: ESF / LSF / MTF arrays to
@@ -15,7 +15,7 @@ from conftest import golden
 
 from importlib import import_module
 
-A = import_module("enph459-super-resolution_b200.analysis")
+A = import_module("oracle.analysis_oracle")
 
 
 def _rel(a, b):

@@ -1,4 +1,4 @@
-"""sr459.calibration against the reference's data_collection/psf_mtf_utils.py.
+"""oracle/calibration_oracle.py (the numpy checker of sr459.calibration) against the reference's data_collection/psf_mtf_utils.py.
 
 Golden vectors: tests/golden/g_calibration.npz from tests/golden/make_golden_calibration.py (the reference module
 imported unmodified).  Bars: integer decisions (peak pixel, ROI shape, crop) exact; deterministic float64 steps
@@ -14,7 +14,7 @@ import pytest
 
 from conftest import golden
 
-Cal = import_module("enph459-super-resolution_b200.calibration")
+Cal = import_module("oracle.calibration_oracle")
 
 
 def _rel(a, b):
