@@ -153,7 +153,8 @@ void plan_free(sr459_plan* p) {
     DeviceGuard guard(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
-                    p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters};
+                    p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters,
+                    p->d_edge_ml[0], p->d_edge_ml[1], p->d_edge_ml[2], p->d_edge_ml[3]};
     for (void* q : ptrs) if (q) gfree(q);
     free_taps(p->taps_f);
     free_taps(p->taps_b);
@@ -429,6 +430,13 @@ FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
         }
         stream_geometry(uy1 - uy0 - (r.st_btop + r.st_bbot) * brows, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
         r.n_fast = (r.st_nseg + r.st_btop + r.st_bbot) * r.st_nstrip;
+    } else if (sep_ok && (p->path == 0 || p->path == 7) && !p->band && uy0 == 0 && uy1 == p->H && (big || p->path == 7) &&
+               ibp_stream_ml_supported(p->kh, p->kw, p->smax, p->separable, W, p->nslot)) {
+        r.use_stream_ml = true;
+        int n_sm = p->n_sm;
+        if (!n_sm) { cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, p->device); }
+        stream_ml_geometry(p->H, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
+        r.n_fast = r.st_nseg * r.st_nstrip;
     } else if (sep_ok && p->path != 7 && (big || p->path >= 4)) {
         r.use_ws = (p->path == 0 || p->path == 4);
         if (r.use_ws) ibp_ws_tile(&fth, &ftw); else ibp_sep_tile(&fth, &ftw);
@@ -455,7 +463,7 @@ FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
 }
 
 // S1 planes + sum of V for the frames of this call (ibp_sep.cu restructuring (2))
-int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaStream_t st) {
+int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaStream_t st, bool stream_ml) {
     const int rows = p->lr_hi - p->lr_lo;
     const int pitch = (p->w + 3) & ~3;
     if (p->s1_rows != rows || p->s1_pitch != pitch) {
@@ -494,6 +502,16 @@ int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaS
         const int h_loc = (p->hr_hi - p->hr_lo) / 2;     // the local image of a row band (whole image: h)
         SR_TRY(launch_stream_edge_sums(lr, p->n, h_loc, p->w, p->isy, p->isx, p->slot_pq[0] >> 1, p->slot_pq[0] & 1,
                                        p->d_edge, p->d_vsum, p->own_i0 - p->lr_lo, p->own_i1 - p->lr_lo, p->own_i0 == 0, st));
+    }
+    if (stream_ml) {                                  // per lattice: map + edge vectors of ITS frames (+ their variances)
+        for (int s = 0; s < p->nslot; ++s) {
+            SR_TRY(stream_make_s1_map(&p->tm_s1ml[s], p->d_s1[s], p->w, rows, pitch));
+            SR_TRY(plan_alloc(p, &p->d_edge_ml[s], (size_t)2 * p->h + 2 * p->w + 4));
+            const float* sub[kMaxFrames]; int sy[kMaxFrames], sx[kMaxFrames];
+            for (int f = 0; f < p->slot_n[s]; ++f) { const int k = p->slot_k[s][f]; sub[f] = lr[k]; sy[f] = p->isy[k]; sx[f] = p->isx[k]; }
+            SR_TRY(launch_stream_edge_sums(sub, p->slot_n[s], p->h, p->w, sy, sx, p->slot_pq[s] >> 1, p->slot_pq[s] & 1,
+                                           p->d_edge_ml[s], p->d_vsum, 0, p->h, 1, st));
+        }
     }
     return SR459_OK;
 }
@@ -542,6 +560,36 @@ int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, c
         f.partial = partial;
         if (p->kpush) f.bp = *p->kpush;                   // row bands: the kernel exchanges the halo rows itself
         return launch_ibp_stream(f, P, Q, st);
+    }
+    if (r.use_stream_ml) {
+        StreamMLArgs f{};
+        SR_TRY(stream_ml_make_hr_map(&f.tm_hr, cur, p->W, p->H));
+        f.hr_out = nxt;
+        f.H = p->H; f.W = p->W; f.h = p->h; f.w = p->w;
+        f.nit = r.st_nit; f.seg_rows = r.st_seg; f.nseg = r.st_nseg; f.nstrip = r.st_nstrip;
+        f.alpha = g.alpha; f.lo = g.lo; f.hi = g.hi;
+        memcpy(f.acol, p->acol, sizeof(f.acol));
+        memcpy(f.brow, p->brow, sizeof(f.brow));
+        int mask = 0;
+        for (int s = 0; s < p->nslot; ++s) {
+            const int P = p->slot_pq[s] >> 1, Q = p->slot_pq[s] & 1;
+            mask |= 1 << p->slot_pq[s];
+            f.tm_s1[s] = p->tm_s1ml[s];
+            memcpy(f.mtab[s], p->mtab[s], sizeof(f.mtab[s]));
+            f.edge[s] = p->d_edge_ml[s];
+            for (int i = 0; i < p->slot_n[s]; ++i) {
+                const int k = p->slot_k[s][i];
+                const int oy = (P + p->isy[k]) >> 1, ox = (Q + p->isx[k]) >> 1;
+                if (p->isx[k] == -1) { f.mc[s][0] += 1.f; if (oy == 0) f.mc[s][1] += 1.f; }
+                if (p->isx[k] == +1) { f.ml[s][0] += 1.f; if (oy == 0) f.ml[s][1] += 1.f; }
+                if (p->isy[k] == -1) { f.mr[s][0] += 1.f; if (ox == 0) f.mr[s][1] += 1.f; }
+                if (p->isy[k] == +1) { f.mt[s][0] += 1.f; if (ox == 0) f.mt[s][1] += 1.f; }
+                if (p->isy[k] == -1 && p->isx[k] == -1) f.m_dupc[s] += 1.f;
+                if (p->isy[k] == +1 && p->isx[k] == +1) f.m_msec[s] += 1.f;
+            }
+        }
+        f.partial = partial;
+        return launch_ibp_stream_ml(f, mask, st);
     }
     if (r.use_lat) {
         LatCall c{};
@@ -610,7 +658,7 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
-        if (r.use_sep || r.use_stream) { SR_TRY(sep_prepare(p, lr, r.use_stream, st)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
+        if (r.use_sep || r.use_stream || r.use_stream_ml) { SR_TRY(sep_prepare(p, lr, r.use_stream, st, r.use_stream_ml)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
         for (int it = 0; it < n_iter; ++it) {
             SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st, it));
             std::swap(cur, nxt);
@@ -885,8 +933,9 @@ int sr459_plan_set_path(sr459_plan* plan, int path) {
         set_error("separable TMA kernel not available for this plan (needs integer |shift| <= 1, a rank-1 PSF up to 7x7, W % 4 == 0)");
         return SR459_EUNSUPPORTED;
     }
-    if (path == 7 && (plan->band || !ibp_stream_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W, plan->nslot))) {
-        set_error("streaming kernel not available for this plan (needs a single parity lattice and a whole-image plan)");
+    if (path == 7 && (plan->band || !(ibp_stream_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W, plan->nslot) ||
+                                      ibp_stream_ml_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W, plan->nslot)))) {
+        set_error("streaming kernel not available for this plan (needs a whole-image plan)");
         return SR459_EUNSUPPORTED;
     }
     if ((path == 2 || path == 3) && !fused_supported(plan)) { set_error("fused integer path not available for this plan"); return SR459_EUNSUPPORTED; }

@@ -241,7 +241,7 @@ struct WarpCtx {
 // otherwise the site row is a valid interior one and MODE says whether the warp owns it for the MSE
 // (M_OWN) and whether this step's two HR rows are stored (M_ST).
 constexpr int M_OWN = 1, M_ST = 2, M_GEN = 4;
-template <int T, int P, int Q, int MODE, bool LEFT>
+template <int T, int P, int Q, int MODE, bool LEFT, bool BAND>
 __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const WarpCtx& c, const StreamArgs& a,
                                             const int aj, const float* __restrict__ s1row, const float* __restrict__ pf,
                                             float*& outp, const float cS, const float lS, const int lane) {
@@ -366,7 +366,7 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
         if (GEN) { st1 = st1 && (y1 >= c.ya) && (y1 < c.yb); st2 = st2 && (y1 + 1 >= c.ya) && (y1 + 1 < c.yb); }
         if (st1) *reinterpret_cast<float4*>(outp) = q1;
         if (st2) *reinterpret_cast<float4*>(outp + a.W) = q2;
-        if (GEN) {                                          // row bands: boundary rows go straight into the neighbours' halo rows
+        if (GEN && BAND) {                                  // row bands: boundary rows go straight into the neighbours' halo rows
             #pragma unroll
             for (int d = 0; d < 2; ++d) {
                 if (!c.push[d] || (a.bp.probe & 2)) continue;
@@ -380,7 +380,7 @@ __device__ __forceinline__ void stream_step(State& s, const LaneConst& k, const 
 }
 
 // Four steps; M0..M3 are the steps' MODEs (see stream_step)
-template <int P, int Q, int M0, int M1, int M2, int M3, bool LEFT>
+template <int P, int Q, int M0, int M1, int M2, int M3, bool LEFT, bool BAND>
 __device__ __forceinline__ void stream_iteration(State& s, const LaneConst& k, const WarpCtx& c, const StreamArgs& a,
                                                  const int it, const float* __restrict__ ring, uint64_t* bars,
                                                  float*& outp, float& curC, float& curL, const int lane) {
@@ -396,11 +396,11 @@ __device__ __forceinline__ void stream_iteration(State& s, const LaneConst& k, c
     }
     const unsigned FULL = 0xffffffffu;
     #define EDGE(t) (LEFT ? __shfl_sync(FULL, curC, t) : 0.0f), (LEFT ? __shfl_sync(FULL, curL, t) : 0.0f)
-    stream_step<0, P, Q, M0, LEFT>(s, k, c, a, aj + 0, s1s + 0 * 64, hrs + 2 * SS_COLS, outp, EDGE(0), lane);
-    stream_step<1, P, Q, M1, LEFT>(s, k, c, a, aj + 1, s1s + 1 * 64, hrs + 4 * SS_COLS, outp, EDGE(1), lane);
-    stream_step<2, P, Q, M2, LEFT>(s, k, c, a, aj + 2, s1s + 2 * 64, hrs + 6 * SS_COLS, outp, EDGE(2), lane);
+    stream_step<0, P, Q, M0, LEFT, BAND>(s, k, c, a, aj + 0, s1s + 0 * 64, hrs + 2 * SS_COLS, outp, EDGE(0), lane);
+    stream_step<1, P, Q, M1, LEFT, BAND>(s, k, c, a, aj + 1, s1s + 1 * 64, hrs + 4 * SS_COLS, outp, EDGE(1), lane);
+    stream_step<2, P, Q, M2, LEFT, BAND>(s, k, c, a, aj + 2, s1s + 2 * 64, hrs + 6 * SS_COLS, outp, EDGE(2), lane);
     mbar_wait(&bars[nslot], (uint32_t)(((it + 2) / SS_STAGES) & 1));          // the next stage: its first two rows are prefetched now
-    stream_step<3, P, Q, M3, LEFT>(s, k, c, a, aj + 3, s1s + 3 * 64, nxt, outp, EDGE(3), lane);
+    stream_step<3, P, Q, M3, LEFT, BAND>(s, k, c, a, aj + 3, s1s + 3 * 64, nxt, outp, EDGE(3), lane);
     #undef EDGE
     curC = nC; curL = nL;
 }
@@ -413,13 +413,14 @@ __device__ __forceinline__ void stream_issue(const StreamArgs& a, float* ring, u
     tma_load_2d(dst + SS_HR_FLOATS, &a.tm_s1, xs0 >> 1, a0 + SS_SROWS * (stage - 1), &bars[slot]);
 }
 
-template <int P, int Q>
+// BAND: the launch works on a row band whose halo rows it exchanges itself; the whole-image instantiation carries none of that code
+template <int P, int Q, bool BAND>
 __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid_constant__ StreamArgs a) {
     extern __shared__ __align__(128) float sm[];
     __shared__ __align__(8) uint64_t bars_all[SS_WARPS][SS_STAGES];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int gw = blockIdx.x * SS_WARPS + warp;
-    const int nbw = (a.b_top + a.b_bot) * a.nstrip;      // border warps come first (row bands)
+    const int nbw = BAND ? (a.b_top + a.b_bot) * a.nstrip : 0;      // border warps come first (row bands)
     if (gw >= nbw + a.nseg * a.nstrip) return;           // whole warps only; nothing below synchronises the CTA
     float* ring = sm + warp * (SS_STAGES * SS_STAGE_FLOATS);
     uint64_t* bars = bars_all[warp];
@@ -427,7 +428,7 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     WarpCtx c;
     int strip, nit;
     const int brows = 8 * a.b_nit - 6;
-    if (gw < nbw) {
+    if (BAND && gw < nbw) {
         strip = gw % a.nstrip; nit = a.b_nit;
         const bool is_top = a.b_top && gw < a.nstrip;
         c.ya = is_top ? a.y_base : a.y_end - brows;
@@ -435,8 +436,8 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     } else {
         const int g2 = gw - nbw;
         strip = g2 % a.nstrip; nit = a.nit;
-        c.ya = a.y_base + a.b_top * brows + (g2 / a.nstrip) * a.seg_rows;   // segments partition the rows between the border zones
-        c.yb = min(c.ya + a.seg_rows, a.y_end - a.b_bot * brows);
+        c.ya = a.y_base + (BAND ? a.b_top * brows : 0) + (g2 / a.nstrip) * a.seg_rows;   // segments partition the rows between the border zones
+        c.yb = min(c.ya + a.seg_rows, a.y_end - (BAND ? a.b_bot * brows : 0));
     }
     c.x0 = strip * SS_VALID;
     c.h = a.h;
@@ -459,7 +460,7 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
     // row bands: the warps whose windows reach into a halo wait until the neighbour's rows of the previous iteration have
     // arrived (its counter reaches BASE + it); everybody else starts at once
     c.push[0] = c.push[1] = false;
-    if (a.bp.flags != nullptr) {
+    if (BAND && a.bp.flags != nullptr) {
         c.push[0] = a.bp.has[0] && c.ya < a.bp.push_y1[0];
         c.push[1] = a.bp.has[1] && c.yb > a.bp.push_y0[1];
         const bool need_up = a.bp.has[0] && (c.ya - 8 < a.bp.push_y0[0]);
@@ -554,7 +555,7 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
                 pat |= (m & 3) << (2 * t);
             }
             const int FAST = M_OWN | M_ST;
-            if (nf || c.push[0] || c.push[1]) kind = 3;     // pushing warps take the general form (it has the peer stores)
+            if (nf || (BAND && (c.push[0] || c.push[1]))) kind = 3;     // pushing warps take the general form (it has the peer stores)
             else if (pat == (FAST | FAST << 2 | FAST << 4 | FAST << 6)) kind = 0;
             else if (pat == (0 | 0 << 2 | M_OWN << 4 | FAST << 6)) kind = 1;
             else if (pat == (FAST | FAST << 2 | FAST << 4 | M_ST << 6)) kind = 2;
@@ -562,15 +563,15 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
         }
         constexpr int F = M_OWN | M_ST;
         if (left) {
-            if (kind == 0)      stream_iteration<P, Q, F, F, F, F, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else if (kind == 1) stream_iteration<P, Q, 0, 0, M_OWN, F, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else if (kind == 2) stream_iteration<P, Q, F, F, F, M_ST, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else                stream_iteration<P, Q, M_GEN, M_GEN, M_GEN, M_GEN, true>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            if (kind == 0)      stream_iteration<P, Q, F, F, F, F, true, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 1) stream_iteration<P, Q, 0, 0, M_OWN, F, true, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 2) stream_iteration<P, Q, F, F, F, M_ST, true, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else                stream_iteration<P, Q, M_GEN, M_GEN, M_GEN, M_GEN, true, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
         } else {
-            if (kind == 0)      stream_iteration<P, Q, F, F, F, F, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else if (kind == 1) stream_iteration<P, Q, 0, 0, M_OWN, F, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else if (kind == 2) stream_iteration<P, Q, F, F, F, M_ST, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
-            else                stream_iteration<P, Q, M_GEN, M_GEN, M_GEN, M_GEN, false>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            if (kind == 0)      stream_iteration<P, Q, F, F, F, F, false, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 1) stream_iteration<P, Q, 0, 0, M_OWN, F, false, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else if (kind == 2) stream_iteration<P, Q, F, F, F, M_ST, false, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
+            else                stream_iteration<P, Q, M_GEN, M_GEN, M_GEN, M_GEN, false, BAND>(s, k, c, a, it, ring, bars, outp, curC, curL, lane);
         }
         // stage it+1 is consumed: refill its slot with stage it+4
         __syncwarp();
@@ -584,7 +585,7 @@ __global__ void __launch_bounds__(SS_THREADS, SS_CTAS) k_ibp_stream(const __grid
 
     // row bands: once my peer stores are visible system-wide, count my arrival in the neighbour's arena (one remote
     // atomic per pushing warp; the neighbour waits for `unit` of them per iteration)
-    if ((c.push[0] || c.push[1]) && !(a.bp.probe & 4)) {
+    if (BAND && (c.push[0] || c.push[1]) && !(a.bp.probe & 4)) {
         __threadfence_system();
         __syncwarp();
         if (lane == 0) {
@@ -631,10 +632,14 @@ int launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st) {
     const size_t smem = sizeof(float) * (size_t)SS_WARPS * SS_STAGES * SS_STAGE_FLOATS;
     static PerDeviceOnce configured;
     if (configured.need()) {
-        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 0, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 1, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<0, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 0, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_stream<1, 1, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
     const int grid = (warps + SS_WARPS - 1) / SS_WARPS;
     cudaLaunchConfig_t cfg{};
@@ -643,12 +648,17 @@ int launch_ibp_stream(const StreamArgs& a, int P, int Q, cudaStream_t st) {
     attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[0].val.programmaticStreamSerializationAllowed = 1;
     { static const bool no_pdl = getenv("SR459_NO_PDL") != nullptr; cfg.attrs = attr; cfg.numAttrs = no_pdl ? 0 : 1; }
+    const bool band = a.bp.flags != nullptr || a.b_top || a.b_bot;
     cudaError_t le;
-    switch (P * 2 + Q) {
-        case 0: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 0>, a); break;
-        case 1: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 1>, a); break;
-        case 2: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 0>, a); break;
-        default: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 1>, a); break;
+    switch (P * 2 + Q + (band ? 4 : 0)) {
+        case 0: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 0, false>, a); break;
+        case 1: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 1, false>, a); break;
+        case 2: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 0, false>, a); break;
+        case 3: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 1, false>, a); break;
+        case 4: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 0, true>, a); break;
+        case 5: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<0, 1, true>, a); break;
+        case 6: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 0, true>, a); break;
+        default: le = cudaLaunchKernelEx(&cfg, k_ibp_stream<1, 1, true>, a); break;
     }
     if (le != cudaSuccess) { set_error("launch of k_ibp_stream failed: %s", cudaGetErrorString(le)); return SR459_ECUDA; }
     SR_LAUNCH_CHECK("k_ibp_stream");

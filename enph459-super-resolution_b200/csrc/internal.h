@@ -343,6 +343,29 @@ constexpr int kStreamBorderNit = 2;     // border segments of row bands: 10 rows
 int  launch_stream_edge_sums(const float* const* lr, int n, int h, int w, const int* sy, const int* sx, int P, int Q,
                              float* buf, double* vsum, int own_a0, int own_a1, int top_owned, cudaStream_t st);
 
+// ---- register-streaming fused iteration for 2..4 lattices (ibp_stream_ml.cu): rank-1 PSF, whole image -----------
+struct alignas(64) StreamMLArgs {
+    CUtensorMap tm_hr;                  // hr_in as a {W, H} tensor, box 128 x 8
+    CUtensorMap tm_s1[kMaxSlots];       // S1 planes {w, h} in slot order (ascending P*2+Q), box 64 x 4
+    float* hr_out;
+    int H, W, h, w;
+    int nit;                            // loop iterations (4 pairs of HR rows each) per warp
+    int seg_rows;                       // HR rows a warp updates = 8 nit - 8
+    int nseg, nstrip;
+    float alpha, lo, hi;
+    float acol[7], brow[7];
+    float mtab[kMaxSlots][4];           // frames with a sample at a site: [2*(last site row) + (last site col)]
+    const float* edge[kMaxSlots];       // per lattice: colS1[h], leftS1[h], rowS1[w], topS1[w], scal[4] (k_edge_sums)
+    float mc[kMaxSlots][2], ml[kMaxSlots][2];   // frames with sx = -1 / +1 valid at a site row: [last site row]
+    float mr[kMaxSlots][2], mt[kMaxSlots][2];   // frames with sy = -1 / +1 valid at a site col: [last site col]
+    float m_dupc[kMaxSlots], m_msec[kMaxSlots]; // frames (-1,-1) / (+1,+1)
+    double* partial;                    // one slot per warp
+};
+int  launch_ibp_stream_ml(const StreamMLArgs& a, int mask, cudaStream_t st);
+bool ibp_stream_ml_supported(int kh, int kw, int smax, bool separable, int W, int nslot);
+int  stream_ml_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
+void stream_ml_geometry(int H, int W, int n_sm, int* nit, int* seg_rows, int* nseg, int* nstrip);
+
 // ---- lattice form for large / non-separable PSFs (ibp_lat.cu): reach <= 15, |integer HR shift| <= 1 ---------
 struct LatPlan;                         // tables + site planes, owned by the plan
 struct LatCall {

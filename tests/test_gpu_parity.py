@@ -392,12 +392,52 @@ def test_streaming_kernel_small_psfs_anisotropic_and_unit_range(sr):
     _check_against(g, *res, peak=1.0, scale=1.0 / 255.0, what="g_unit path7")
 
 
-def test_streaming_kernel_refuses_two_lattices(sr):
-    plan = sr.Plan(5, 32, 32, [(0.0, 0.0)] + NOMINAL, O.make_gaussian_psf())
-    with pytest.raises(sr.Sr459Error) as ei:
-        plan.set_path(7)
-    assert ei.value.code == -4
-    plan.close()
+_LAT_SHIFT = {0: [(0.0, 0.0)], 1: [(0.0, 0.5), (0.0, -0.5)], 2: [(0.5, 0.0), (-0.5, 0.0)], 3: [(0.5, 0.5), (-0.5, -0.5), (0.5, -0.5)]}
+MULTI_LATTICE_SETS = [sum((_LAT_SHIFT[pq] for pq in range(4) if mask >> pq & 1), []) for mask in (3, 5, 6, 7, 9, 10, 11, 12, 13, 14, 15)]
+MULTI_LATTICE_SETS += [
+    [(0.0, 0.0)] + NOMINAL,                                   # mono_cal_target's own five frames (run_sr.py:60-66)
+    [(0.0, 0.0), (-0.5, 0.0), (0.0, -0.5), (-0.5, -0.5)],     # all four lattices, row-0 / column-0 duplicates only
+    [(0.0, 0.0), (0.5, 0.0), (0.0, 0.5), (0.5, 0.5)],         # all four lattices, MSE-only terms only
+    [(0.0, 0.0)] * 2 + [(0.5, 0.5)] * 3 + [(-0.5, -0.5)] * 3,
+]
+
+
+@pytest.mark.parametrize("shifts", MULTI_LATTICE_SETS)
+@pytest.mark.parametrize("hw", [(160, 320), (100, 150), (33, 48), (7, 60), (2, 2), (231, 58)])
+def test_multi_lattice_streaming_kernel_vs_oracle(sr, shifts, hw):
+    """k_ibp_stream_ml (path 7 with two to four parity lattices): every lattice mask, interior and general iterations,
+    top segment, left strip, last site row / column, partial last segment and strip, images smaller than one strip."""
+    if len(shifts) > 8:
+        pytest.skip("more than 8 frames")
+    rng = np.random.default_rng(26)
+    h, w = hw
+    lrs = [rng.uniform(0, 255, (h, w)) for _ in shifts]
+    psf = O.make_gaussian_psf()
+    saa_o = O.shift_and_add_integer(lrs, shifts)
+    hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, saa_o, n_iter=4)
+    native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 4, 7)
+    _close(hr, hr_o, what=f"ibp path7 multi-lattice {shifts} {hw}")
+    _close(hr[:8], hr_o[:8], what="top rows"); _close(hr[-8:], hr_o[-8:], what="bottom rows")
+    _close(hr[:, :8], hr_o[:, :8], what="left cols"); _close(hr[:, -8:], hr_o[:, -8:], what="right cols")
+    _errs_close(errs, e_o)
+
+
+def test_multi_lattice_streaming_kernel_is_the_default_and_handles_small_psfs(sr):
+    rng = np.random.default_rng(27)
+    shifts = [(0.0, 0.0)] + NOMINAL
+    lrs = [rng.uniform(0, 255, (96, 160)) for _ in shifts]
+    saa_o = O.shift_and_add_integer(lrs, shifts)
+    gy = np.exp(-0.5 * (np.arange(-3, 4) / 0.7) ** 2); gx = np.exp(-0.5 * (np.arange(-3, 4) / 1.4) ** 2)
+    aniso = np.outer(gy / gy.sum(), gx / gx.sum())
+    for psf in (O.make_gaussian_psf(3, 0.6), O.make_gaussian_psf(5, 0.9), np.array([[1.0]]), aniso, O.make_gaussian_psf()):
+        hr_o, e_o = O.ibp_integer_shifts(lrs, shifts, psf, saa_o, n_iter=5)
+        for path in (0, 7):
+            native, saa, hr, errs = _run_pipeline(sr, lrs, shifts, psf, 5, path)
+            _close(hr, hr_o, what=f"path{path} multi-lattice psf {psf.shape}")
+            _errs_close(errs, e_o)
+    a = _run_pipeline(sr, lrs, shifts, O.make_gaussian_psf(), 5, 0)      # auto == path 7 bit for bit: the plan picks this kernel
+    b = _run_pipeline(sr, lrs, shifts, O.make_gaussian_psf(), 5, 7)
+    assert np.array_equal(a[2], b[2]) and np.array_equal(np.asarray(a[3]), np.asarray(b[3]))
 
 
 def test_non_separable_psf_refuses_path4(sr):
