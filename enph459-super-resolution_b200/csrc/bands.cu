@@ -29,7 +29,7 @@ namespace {
 constexpr int kLrMargin   = 32;          // extra LR rows beyond hr_lo/2 and hr_hi/2 the caller provides (SAA)
 constexpr int kFlagWords  = 64;          // 256 B at the head of the arena
 constexpr int F_FROM_UP = BF_FROM_UP, F_FROM_DOWN = BF_FROM_DOWN, F_ERROR = BF_ERROR, F_BASE = BF_BASE, F_TICKET = BF_TICKET;
-constexpr int kPushCtas   = 16;          // CTAs per direction
+constexpr int kPushCtas   = 64;          // CTAs per direction (512 KB per direction for a 31x31 PSF: 2 float4 per thread)
 }
 
 struct BandState {

@@ -26,6 +26,7 @@
 #include "internal.h"
 #include <algorithm>
 #include <string.h>
+#include <stdlib.h>
 
 namespace sr459 {
 
@@ -44,8 +45,9 @@ __device__ __forceinline__ float lat_sum2(u64 v) {
 
 constexpr int LT_ROWS = 32;             // site rows per tile: lane <-> row
 constexpr int LT_WARPS = 4;
-constexpr int LT_NB = 16;               // outputs per lane (consecutive site columns)
-constexpr int LT_COLS = LT_WARPS * LT_NB;   // 64
+// NB = outputs per lane (consecutive site columns), a template parameter: 16 for whole images (tile = 32 x 64 sites; the best
+// FFMA2 : LDS ratio), 8 for thin row bands (32 x 32 sites: twice the CTAs, so that a band of 1/8 of the image still gives every
+// SM scheduler three warps -- one warp alone runs at about a third of the FFMA2 issue rate)
 
 // Weight tables of one direction.  Tap sets per axis: parity 0 = the NT even taps, parity 1 = the NT-1 odd
 // taps (+ one zero).  e[][][tu][m] = (w[2m], w[2m+1]); o[][][tu][m] = (w[2m-1], w[2m]) with w[-1] = w[NT] = 0:
@@ -64,29 +66,29 @@ struct LatGeom {
     int slot_pq[kMaxSlots];             // P*2+Q
 };
 
-template <int NT>
-__device__ __forceinline__ void lat_load_window(const float* p, u64 (&xp)[(LT_NB + NT) / 2]) {
+template <int NT, int NB>
+__device__ __forceinline__ void lat_load_window(const float* p, u64 (&xp)[(NB + NT) / 2]) {
     const ulonglong2* q = reinterpret_cast<const ulonglong2*>(p);
     #pragma unroll
-    for (int i = 0; i < (LT_NB + NT) / 4; ++i) { const ulonglong2 t = q[i]; xp[2 * i] = t.x; xp[2 * i + 1] = t.y; }
+    for (int i = 0; i < (NB + NT) / 4; ++i) { const ulonglong2 t = q[i]; xp[2 * i] = t.x; xp[2 * i + 1] = t.y; }
 }
 
 // out[b] += sum_t w[t] * x[b + DELTA + t], b = 0..15; x = 32 floats as 16 aligned pairs; acc = (lo, hi) halves.
 // Split by the parity of b + DELTA so that one weight packing is in use while the other one is being fetched.
-template <int NT, int DELTA>
-__device__ __forceinline__ void lat_conv_even(const u64 (&xp)[(LT_NB + NT) / 2], const u64 (&we)[NT / 2], u64 (&acc)[LT_NB]) {
+template <int NT, int NB, int DELTA>
+__device__ __forceinline__ void lat_conv_even(const u64 (&xp)[(NB + NT) / 2], const u64 (&we)[NT / 2], u64 (&acc)[NB]) {
     #pragma unroll
     for (int m = 0; m < NT / 2; ++m) {
         #pragma unroll
-        for (int b = DELTA; b < LT_NB; b += 2) acc[b] = lat_fma2(xp[(b + DELTA) / 2 + m], we[m], acc[b]);
+        for (int b = DELTA; b < NB; b += 2) acc[b] = lat_fma2(xp[(b + DELTA) / 2 + m], we[m], acc[b]);
     }
 }
-template <int NT, int DELTA>
-__device__ __forceinline__ void lat_conv_odd(const u64 (&xp)[(LT_NB + NT) / 2], const u64 (&wo)[NT / 2 + 2], u64 (&acc)[LT_NB]) {
+template <int NT, int NB, int DELTA>
+__device__ __forceinline__ void lat_conv_odd(const u64 (&xp)[(NB + NT) / 2], const u64 (&wo)[NT / 2 + 2], u64 (&acc)[NB]) {
     #pragma unroll
     for (int m = 0; m <= NT / 2; ++m) {
         #pragma unroll
-        for (int b = 1 - DELTA; b < LT_NB; b += 2) acc[b] = lat_fma2(xp[(b + DELTA - 1) / 2 + m], wo[m], acc[b]);
+        for (int b = 1 - DELTA; b < NB; b += 2) acc[b] = lat_fma2(xp[(b + DELTA - 1) / 2 + m], wo[m], acc[b]);
     }
 }
 template <int NT>
@@ -104,25 +106,25 @@ __device__ __forceinline__ void lat_load_wo(const u64* row, u64 (&wo)[NT / 2 + 2
 
 // one parity phase of a 2-D correlation: acc[b] += sum_{tu < ntu} sum_tv w[tu][tv] * x[row tu][b + DELTA + tv];
 // software-pipelined: next window and next weight packing are fetched under the FFMA2 of the current ones
-template <int NT, int DELTA>
-__device__ __forceinline__ void lat_conv_phase(const float* base, int pitch, const u64 (*wt)[NT + 2], int ntu, u64 (&acc)[LT_NB]) {
-    u64 xa[(LT_NB + NT) / 2], xb[(LT_NB + NT) / 2], we[NT / 2], wo[NT / 2 + 2];
-    lat_load_window<NT>(base, xa);
+template <int NT, int NB, int DELTA>
+__device__ __forceinline__ void lat_conv_phase(const float* base, int pitch, const u64 (*wt)[NT + 2], int ntu, u64 (&acc)[NB]) {
+    u64 xa[(NB + NT) / 2], xb[(NB + NT) / 2], we[NT / 2], wo[NT / 2 + 2];
+    lat_load_window<NT, NB>(base, xa);
     lat_load_we<NT>(wt[0], we);
     #pragma unroll 1
     for (int tu = 0; tu < ntu; tu += 2) {                    // two tap rows per trip: windows alternate xa / xb
         const int t1 = min(tu + 1, ntu - 1), t2 = min(tu + 2, ntu - 1);
         lat_load_wo<NT>(wt[tu], wo);
-        lat_load_window<NT>(base + t1 * pitch, xb);
-        lat_conv_even<NT, DELTA>(xa, we, acc);
+        lat_load_window<NT, NB>(base + t1 * pitch, xb);
+        lat_conv_even<NT, NB, DELTA>(xa, we, acc);
         lat_load_we<NT>(wt[t1], we);
-        lat_conv_odd<NT, DELTA>(xa, wo, acc);
+        lat_conv_odd<NT, NB, DELTA>(xa, wo, acc);
         if (tu + 1 < ntu) {                                  // warp-uniform
             lat_load_wo<NT>(wt[t1], wo);
-            lat_load_window<NT>(base + t2 * pitch, xa);
-            lat_conv_even<NT, DELTA>(xb, we, acc);
+            lat_load_window<NT, NB>(base + t2 * pitch, xa);
+            lat_conv_even<NT, NB, DELTA>(xb, we, acc);
             lat_load_we<NT>(wt[t2], we);
-            lat_conv_odd<NT, DELTA>(xb, wo, acc);
+            lat_conv_odd<NT, NB, DELTA>(xb, wo, acc);
         } else {
             lat_load_we<NT>(wt[t2], we);
         }
@@ -130,11 +132,12 @@ __device__ __forceinline__ void lat_conv_phase(const float* base, int pitch, con
 }
 
 
-template <int NT> struct LatDims {
+template <int NT, int NB> struct LatDims {
     static constexpr int RT = NT - 1;               // padded PSF reach (odd)
     static constexpr int HB = (RT + 1) / 2;         // largest window offset magnitude
     static constexpr int SR = LT_ROWS + NT;         // staged rows per plane
-    static constexpr int SC = LT_COLS + NT;         // staged columns per plane
+    static constexpr int COLS = LT_WARPS * NB;      // site columns per tile
+    static constexpr int SC = COLS + NT;            // staged columns per plane
     static constexpr int SP = (((SC + 4) / 4) & 1) ? SC + 4 : SC + 8;   // pitch: multiple of 4 floats, odd in float4 units
 };
 
@@ -149,9 +152,9 @@ struct alignas(16) LatFwdArgs {
     float* bl[kMaxSlots];
 };
 
-template <int NT>
+template <int NT, int NB>
 __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_constant__ LatFwdArgs<NT> a) {
-    typedef LatDims<NT> D;
+    typedef LatDims<NT, NB> D;
     extern __shared__ __align__(16) float sm[];             // [4 phases][SR][SP] + weight table
     const LatGeom& g = a.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -159,7 +162,7 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_const
     u64 (*wsm)[2][NT][NT + 2] = reinterpret_cast<u64 (*)[2][NT][NT + 2]>(sm + 4 * D::SR * D::SP);
     for (int i = tid; i < 2 * NT * (NT + 2); i += LT_WARPS * 32) reinterpret_cast<ulonglong2*>(wsm)[i] = __ldg(a.tab + i);
     const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
-    const int A0 = g.sa_lo + blockIdx.y * LT_ROWS, B0 = blockIdx.x * LT_COLS;
+    const int A0 = g.sa_lo + blockIdx.y * LT_ROWS, B0 = blockIdx.x * D::COLS;
     int du0[2], dv0[2];
     #pragma unroll
     for (int p = 0; p < 2; ++p) { du0[p] = -((D::RT + p - P) >> 1); dv0[p] = -((D::RT + p - Q) >> 1); }
@@ -202,22 +205,22 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 3) k_lat_fwd(const __grid_const
     }
     __syncthreads();
 
-    u64 acc[LT_NB];
+    u64 acc[NB];
     #pragma unroll
-    for (int b = 0; b < LT_NB; ++b) acc[b] = 0ull;
+    for (int b = 0; b < NB; ++b) acc[b] = 0ull;
     #pragma unroll 1
     for (int ph = 0; ph < 4; ++ph) {
         const int pr = ph >> 1, pc = ph & 1;
         const int us = (P + D::RT - pr) & 1, vs = (Q + D::RT - pc) & 1;
-        const float* base = sm + (ph * D::SR + lane) * D::SP + LT_NB * warp;
+        const float* base = sm + (ph * D::SR + lane) * D::SP + NB * warp;
         const int ntu = NT - us;                             // the odd tap set has NT-1 rows
-        lat_conv_phase<NT, 0>(base, D::SP, wsm[us][vs], ntu, acc);
+        lat_conv_phase<NT, NB, 0>(base, D::SP, wsm[us][vs], ntu, acc);
     }
-    const int ar = A0 + lane, bc = B0 + LT_NB * warp;
+    const int ar = A0 + lane, bc = B0 + NB * warp;
     if (ar < g.sa_hi && bc < g.w) {
         float* d = a.bl[s] + (size_t)(ar - g.sa_lo) * g.pitch + bc;
         #pragma unroll
-        for (int q = 0; q < LT_NB / 4; ++q) {
+        for (int q = 0; q < NB / 4; ++q) {
             if (bc + 4 * q < g.pitch)                        // pitch is a multiple of 4 >= w: whole float4s
                 *reinterpret_cast<float4*>(d + 4 * q) = make_float4(lat_sum2(acc[4 * q]), lat_sum2(acc[4 * q + 1]),
                                                                     lat_sum2(acc[4 * q + 2]), lat_sum2(acc[4 * q + 3]));
@@ -439,15 +442,15 @@ __device__ __noinline__ float lat_edge_terms(LatEdgeRefs e, int Y, int X) {
     return v;
 }
 
-template <int NT>
+template <int NT, int NB>
 __global__ void __launch_bounds__(LT_WARPS * 32, 4) k_lat_bwd(const __grid_constant__ LatBwdArgs<NT> a) {
-    typedef LatDims<NT> D;
+    typedef LatDims<NT, NB> D;
     extern __shared__ __align__(16) float sm[];             // [nslot][SR][SP] + weight table
     const LatGeom& g = a.g;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     u64 (*wsm)[2][NT][NT + 2] = reinterpret_cast<u64 (*)[2][NT][NT + 2]>(sm + g.nslot * D::SR * D::SP);
     for (int i = tid; i < 2 * NT * (NT + 2); i += LT_WARPS * 32) reinterpret_cast<ulonglong2*>(wsm)[i] = __ldg(a.tab + i);
-    const int M0 = a.m_lo + blockIdx.y * LT_ROWS, N0 = blockIdx.x * LT_COLS;
+    const int M0 = a.m_lo + blockIdx.y * LT_ROWS, N0 = blockIdx.x * D::COLS;
 
     // ---- stage the residual planes around the tile: rows [M0-HB, M0-HB+SR), cols [N0-HB, N0-HB+SC) -------
     for (int s = 0; s < g.nslot; ++s) {
@@ -477,28 +480,28 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 4) k_lat_bwd(const __grid_const
     __syncthreads();
 
     const int m = M0 + lane;
-    const int n0 = N0 + LT_NB * warp;
+    const int n0 = N0 + NB * warp;
     #pragma unroll 1
     for (int py = 0; py < 2; ++py) {
-        float v0[LT_NB];
+        float v0[NB];
         #pragma unroll 1
         for (int px = 0; px < 2; ++px) {
-            u64 acc[LT_NB];
+            u64 acc[NB];
             #pragma unroll
-            for (int b = 0; b < LT_NB; ++b) acc[b] = 0ull;
+            for (int b = 0; b < NB; ++b) acc[b] = 0ull;
             for (int s = 0; s < g.nslot; ++s) {
                 const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
                 const int qy = D::RT + P - py, qx = D::RT + Q - px;
                 const int us = qy & 1, vs = qx & 1;
                 const int ro = D::HB - (qy >> 1), delta = D::HB - (qx >> 1);     // 0 or 1
-                const float* base = sm + (s * D::SR + lane + ro) * D::SP + LT_NB * warp;
+                const float* base = sm + (s * D::SR + lane + ro) * D::SP + NB * warp;
                 const int ntu = NT - us;
-                if (delta == 0) lat_conv_phase<NT, 0>(base, D::SP, wsm[us][vs], ntu, acc);
-                else            lat_conv_phase<NT, 1>(base, D::SP, wsm[us][vs], ntu, acc);
+                if (delta == 0) lat_conv_phase<NT, NB, 0>(base, D::SP, wsm[us][vs], ntu, acc);
+                else            lat_conv_phase<NT, NB, 1>(base, D::SP, wsm[us][vs], ntu, acc);
             }
             if (px == 0) {
                 #pragma unroll
-                for (int b = 0; b < LT_NB; ++b) v0[b] = lat_sum2(acc[b]);
+                for (int b = 0; b < NB; ++b) v0[b] = lat_sum2(acc[b]);
             } else if (m < a.m_hi && n0 < g.w) {
                 // ---- epilogue of HR row Y = 2m + py: 32 consecutive pixels per lane ---------------------------
                 const int Y = 2 * m + py, X0 = 2 * n0;
@@ -506,7 +509,7 @@ __global__ void __launch_bounds__(LT_WARPS * 32, 4) k_lat_bwd(const __grid_const
                 float* hout = a.hr_out + (size_t)(Y - g.hr_lo) * g.W + X0;
                 const bool edge = (a.has_row0 && Y <= D::RT) || (a.has_col0 && X0 <= D::RT);
                 #pragma unroll
-                for (int q = 0; q < LT_NB / 2; ++q) {
+                for (int q = 0; q < NB / 2; ++q) {
                     if (X0 + 4 * q >= g.W) break;
                     const float4 hv = __ldg(reinterpret_cast<const float4*>(hin) + q);
                     float c0 = v0[2 * q], c1 = lat_sum2(acc[2 * q]), c2 = v0[2 * q + 1], c3 = lat_sum2(acc[2 * q + 1]);
@@ -568,7 +571,7 @@ struct LatPlan {
     float* d_A[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
     float *d_btop = nullptr, *d_bleft = nullptr, *d_arow = nullptr, *d_acol = nullptr;
     int64_t bytes = 0;
-    bool attr_done = false;
+    bool attr_done[2] = {false, false};   // per tile width (NB = 8 / 16)
 };
 
 bool lat_supported(int kh, int kw, int smax, int W) {
@@ -679,23 +682,23 @@ static int lat_ensure_planes(LatPlan* L, const LatGeom& g) {
     return SR459_OK;
 }
 
-template <int NT>
+template <int NT, int NB>
 static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const LatTab<NT>& ft, const LatTab<NT>& bt, cudaStream_t st) {
-    typedef LatDims<NT> D;
+    typedef LatDims<NT, NB> D;
     const LatGeom& g = S.g;
     const size_t smem_f = sizeof(float) * 4 * D::SR * D::SP + sizeof(LatTab<NT>), smem_b = sizeof(float) * g.nslot * D::SR * D::SP + sizeof(LatTab<NT>);
-    if (!L->attr_done) {
-        SR_CUDA(cudaFuncSetAttribute(k_lat_fwd<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
-        SR_CUDA(cudaFuncSetAttribute(k_lat_bwd<NT>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * kMaxSlots * D::SR * D::SP + sizeof(LatTab<NT>))));
-        L->attr_done = true;
+    if (!L->attr_done[NB == 16]) {
+        SR_CUDA(cudaFuncSetAttribute(k_lat_fwd<NT, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem_f));
+        SR_CUDA(cudaFuncSetAttribute(k_lat_bwd<NT, NB>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)(sizeof(float) * kMaxSlots * D::SR * D::SP + sizeof(LatTab<NT>))));
+        L->attr_done[NB == 16] = true;
     }
-    const int tiles_x = (g.w + LT_COLS - 1) / LT_COLS;
+    const int tiles_x = (g.w + D::COLS - 1) / D::COLS;
     {   // forward
         LatFwdArgs<NT> a;
         a.tab = reinterpret_cast<const ulonglong2*>(L->d_tabf); a.g = g; a.hr = c.hr_in;
         for (int s = 0; s < kMaxSlots; ++s) a.bl[s] = L->d_bl[s];
         dim3 grid(tiles_x, (g.sa_hi - g.sa_lo + LT_ROWS - 1) / LT_ROWS, g.nslot);
-        k_lat_fwd<NT><<<grid, LT_WARPS * 32, smem_f, st>>>(a);
+        k_lat_fwd<NT, NB><<<grid, LT_WARPS * 32, smem_f, st>>>(a);
         SR_LAUNCH_CHECK("k_lat_fwd");
     }
     {   // B on row 0 / column 0
@@ -726,7 +729,7 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
         a.arow = L->d_arow; a.acol = L->d_acol; a.psf = L->d_psf;
         a.has_row0 = S.has_row0; a.has_col0 = S.has_col0;
         dim3 grid(tiles_x, (a.m_hi - a.m_lo + LT_ROWS - 1) / LT_ROWS);
-        k_lat_bwd<NT><<<grid, LT_WARPS * 32, smem_b, st>>>(a);
+        k_lat_bwd<NT, NB><<<grid, LT_WARPS * 32, smem_b, st>>>(a);
         SR_LAUNCH_CHECK("k_lat_bwd");
     }
     return SR459_OK;
@@ -735,8 +738,13 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
 int lat_iterate(LatPlan* L, const LatCall& c, cudaStream_t st) {
     LatSetup S; lat_setup(L, c, S);
     SR_TRY(lat_ensure_planes(L, S.g));
-    if (L->NT == 16) return lat_iterate_t<16>(L, c, S, L->f16, L->b16, st);
-    return lat_iterate_t<8>(L, c, S, L->f8, L->b8, st);
+    // thin updates (row bands): the narrow tile doubles the CTA count as long as the wide one cannot fill the machine
+    int n_sm = 148; { int dev = 0; if (cudaGetDevice(&dev) == cudaSuccess) cudaDeviceGetAttribute(&n_sm, cudaDevAttrMultiProcessorCount, dev); }
+    const long long wide_tiles = (long long)((S.g.w + 4 * 16 - 1) / (4 * 16)) * (((c.upd_y1 - c.upd_y0) / 2 + LT_ROWS - 1) / LT_ROWS);
+    static const int force_nb = getenv("SR459_LAT_NB") ? atoi(getenv("SR459_LAT_NB")) : 0;
+    const bool narrow = force_nb ? force_nb == 8 : wide_tiles < 3LL * n_sm;
+    if (L->NT == 16) return narrow ? lat_iterate_t<16, 8>(L, c, S, L->f16, L->b16, st) : lat_iterate_t<16, 16>(L, c, S, L->f16, L->b16, st);
+    return narrow ? lat_iterate_t<8, 8>(L, c, S, L->f8, L->b8, st) : lat_iterate_t<8, 16>(L, c, S, L->f8, L->b8, st);
 }
 
 }  // namespace sr459
