@@ -312,7 +312,7 @@ int iterate_generic(sr459_plan* p, const float* const* lr, const float* cur, flo
     for (int k = 0; k < p->n; ++k) { e.lr[k] = lr[k]; e.out[k] = p->d_err + k * lpx; }
     e.partial = p->d_partial + (size_t)it * p->per_iter;
     e.mse_i0 = p->mse_i0 < 0 ? 0 : p->mse_i0; e.mse_i1 = p->mse_i1 < 0 ? p->h : p->mse_i1;
-    SR_TRY(launch_resample_err(e, st, nullptr));
+    SR_TRY(launch_resample_err_tile(e, st));
     // backward: zero-insert + pad + prefilter per frame, evaluate at -s, sum, transposed blur + update
     if (p->fir_ok && p->path == 0) {                        // the same linear map as ONE table-driven FIR kernel (fir.cu)
         FirBpArgs fb{};
@@ -352,7 +352,7 @@ int iterate_generic(sr459_plan* p, const float* const* lr, const float* cur, flo
     return launch_corr2d(u, st);
 }
 
-int generic_per_iter(const sr459_plan* p) { return p->n * ((p->h + 7) / 8) * ((p->w + 31) / 32); }
+int generic_per_iter(const sr459_plan* p) { return ((p->h + kRsTileH - 1) / kRsTileH) * ((p->w + kRsTileW - 1) / kRsTileW); }   // k_resample_err_tile: one slot per CTA
 
 // ---- fused integer path ------------------------------------------------------------------------------
 bool fused_supported(const sr459_plan* p) {

@@ -111,6 +111,9 @@ struct ResampleErrArgs {
     int mse_i0, mse_i1;     // LR rows whose squared residuals are counted (row bands: the owned ones)
 };
 int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_out);
+// one CTA per kRsTileH x kRsTileW LR tile and all frames, coefficient region staged in shared memory; ONE partial per CTA
+constexpr int kRsTileH = 16, kRsTileW = 64;
+int launch_resample_err_tile(const ResampleErrArgs& a, cudaStream_t st);
 
 // ---- FIR form of the fractional-shift back-projection (fir.cu) ---------------------
 constexpr int kFirTaps = 20;            // LR taps per axis: (2*16 + 4) HR samples / factor 2, rounded up

@@ -503,4 +503,140 @@ int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_
     return SR459_OK;
 }
 
+// ---- the same, one CTA per 16 x 64 LR tile and ALL frames: the coefficient region the tile's taps touch (about 38 x 134 samples:
+// the frames' sub-pixel shifts move it by a pixel or two) is staged ONCE in shared memory, de-interleaved by column parity so that
+// the stride-2 reads of neighbouring lanes fall into consecutive banks; the row tables sit in shared memory, the column table of
+// the thread's column in registers.  16 shared-memory loads per output instead of 16 cached global gathers + two 32-byte table
+// loads (k_resample_err: 38 us at config 2; this one: see DESIGN.md).  Tables are used as they are (every boundary rule stays
+// inside them); a tile whose taps span more than the staged region (never for |shift| < 4) falls back to global gathers.
+constexpr int RE_SR = 2 * kRsTileH + 8, RE_SC = 2 * kRsTileW + 8, RE_HP = RE_SC / 2 + 1;
+
+__global__ void __launch_bounds__(256, 3) k_resample_err_tile(const __grid_constant__ ResampleErrArgs a) {
+    __shared__ float coef[RE_SR][2][RE_HP];
+    __shared__ AxisTap sty[kMaxFrames][kRsTileH];
+    __shared__ double red[8];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int y0 = blockIdx.y * kRsTileH, x0 = blockIdx.x * kRsTileW;
+    const int th = min(kRsTileH, a.h - y0), tw = min(kRsTileW, a.w - x0);
+    // bounds of the coefficient region: the tables are monotone in the output index (coordinates grow with it, clamps keep the
+    // order), so the first and last entries of every frame bound it -- uniform loads, all in flight at once
+    int rlo = 0x7fffffff, rhi = -1, clo = 0x7fffffff, chi = -1;
+    for (int k = 0; k < a.n; ++k) {
+        const int4 r0 = __ldg(reinterpret_cast<const int4*>(a.ty + (size_t)k * a.h + y0));
+        const int4 r1 = __ldg(reinterpret_cast<const int4*>(a.ty + (size_t)k * a.h + y0 + th - 1));
+        const int4 c0 = __ldg(reinterpret_cast<const int4*>(a.tx + (size_t)k * a.w + x0));
+        const int4 c1 = __ldg(reinterpret_cast<const int4*>(a.tx + (size_t)k * a.w + x0 + tw - 1));
+        rlo = min(rlo, min(min(min(r0.x, r0.y), min(r0.z, r0.w)), min(min(r1.x, r1.y), min(r1.z, r1.w))));
+        rhi = max(rhi, max(max(max(r0.x, r0.y), max(r0.z, r0.w)), max(max(r1.x, r1.y), max(r1.z, r1.w))));
+        clo = min(clo, min(min(min(c0.x, c0.y), min(c0.z, c0.w)), min(min(c1.x, c1.y), min(c1.z, c1.w))));
+        chi = max(chi, max(max(max(c0.x, c0.y), max(c0.z, c0.w)), max(max(c1.x, c1.y), max(c1.z, c1.w))));
+    }
+    const int nr = rhi - rlo + 1, nc = chi - clo + 1;
+    const bool staged = nr <= RE_SR && nc <= RE_SC;
+    const int cx = tid & 63, rg = tid >> 6;             // column of the tile, group of four rows
+    const int x = x0 + cx;
+    // every global load the thread needs next is issued here, before the first dependent use: its share of the coefficient
+    // region, its share of the row tables, the column taps of its column for the first frames
+    constexpr int PER = (RE_SR * RE_SC + 255) / 256, NPF = 4;
+    AxisTap tyv;
+    if (tid < a.n * th) { const int k = tid / th, r = tid - k * th; tyv = load_tap(a.ty + (size_t)k * a.h + y0 + r); }
+    if (staged) {
+        float cv[PER];
+        #pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            const int e = tid + 256 * i, r = e / RE_SC, c = e - r * RE_SC;
+            cv[i] = (r < nr && c < nc) ? __ldg(a.coef + (size_t)(rlo + r) * a.cpitch + clo + c) : 0.0f;
+        }
+        #pragma unroll
+        for (int i = 0; i < PER; ++i) {
+            const int e = tid + 256 * i, r = e / RE_SC, c = e - r * RE_SC;
+            if (r < RE_SR) coef[r][c & 1][c >> 1] = cv[i];
+        }
+    }
+    if (tid < a.n * th) { const int k = tid / th, r = tid - k * th; sty[k][r] = tyv; }
+    // the column taps and the LR samples of the first NPF frames travel while the CTA meets at the barrier
+    AxisTap txv[NPF];
+    float lrv[NPF][4];
+    const bool col_ok = cx < tw;
+    #pragma unroll
+    for (int k = 0; k < NPF; ++k) {
+        if (k < a.n && col_ok) {
+            txv[k] = load_tap(a.tx + (size_t)k * a.w + x);
+            #pragma unroll
+            for (int r4 = 0; r4 < 4; ++r4) {
+                const int r = rg * 4 + r4;
+                lrv[k][r4] = (r < th && a.lr[k]) ? __ldg(a.lr[k] + (size_t)(y0 + r) * a.w + x) : 0.0f;
+            }
+        }
+    }
+    __syncthreads();
+    float e2 = 0.0f;
+    auto one_frame = [&](const int k, const AxisTap& tx, const float (&lrk)[4]) {
+        int co[4];
+        #pragma unroll
+        for (int j = 0; j < 4; ++j) { const int c = tx.idx[j] - clo; co[j] = (c & 1) * RE_HP + (c >> 1); }
+        #pragma unroll
+        for (int r4 = 0; r4 < 4; ++r4) {
+            const int r = rg * 4 + r4, y = y0 + r;
+            if (r >= th) break;
+            const AxisTap& ty = sty[k][r];
+            float sim = 0.0f;
+            if (staged) {
+                #pragma unroll
+                for (int i = 0; i < 4; ++i) {
+                    const float* row = &coef[ty.idx[i] - rlo][0][0];
+                    float v = 0.0f;
+                    #pragma unroll
+                    for (int j = 0; j < 4; ++j) v = fmaf(tx.w[j], row[co[j]], v);
+                    sim = fmaf(ty.w[i], v, sim);
+                }
+            } else {
+                sim = gather16(a.coef, a.cpitch, ty, tx);
+            }
+            const size_t o = (size_t)y * a.w + x;
+            if (a.lr[k]) {
+                const float e = lrk[r4] - sim;
+                a.out[k][o] = e;
+                if (y >= a.mse_i0 && y < a.mse_i1) e2 = fmaf(e, e, e2);
+            } else {
+                a.out[k][o] = sim;
+            }
+        }
+    };
+    if (col_ok) {
+        #pragma unroll
+        for (int k = 0; k < NPF; ++k) if (k < a.n) one_frame(k, txv[k], lrv[k]);
+        for (int k = NPF; k < a.n; ++k) {                  // more than NPF frames: loaded in place
+            const AxisTap tx = load_tap(a.tx + (size_t)k * a.w + x);
+            float lrk[4];
+            #pragma unroll
+            for (int r4 = 0; r4 < 4; ++r4) {
+                const int r = rg * 4 + r4;
+                lrk[r4] = (r < th && a.lr[k]) ? __ldg(a.lr[k] + (size_t)(y0 + r) * a.w + x) : 0.0f;
+            }
+            one_frame(k, tx, lrk);
+        }
+    }
+    if (a.partial) {
+        double d = (double)e2;
+        #pragma unroll
+        for (int o = 16; o > 0; o >>= 1) d += __shfl_xor_sync(0xffffffffu, d, o);
+        if (lane == 0) red[warp] = d;
+        __syncthreads();
+        if (tid == 0) {
+            double t = 0.0;
+            #pragma unroll
+            for (int i = 0; i < 8; ++i) t += red[i];
+            a.partial[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = t;
+        }
+    }
+}
+
+int launch_resample_err_tile(const ResampleErrArgs& a, cudaStream_t st) {
+    dim3 grid((a.w + kRsTileW - 1) / kRsTileW, (a.h + kRsTileH - 1) / kRsTileH);
+    k_resample_err_tile<<<grid, 256, 0, st>>>(a);
+    SR_LAUNCH_CHECK("k_resample_err_tile");
+    return SR459_OK;
+}
+
 }  // namespace sr459
