@@ -153,7 +153,7 @@ void plan_free(sr459_plan* p) {
     DeviceGuard guard(p->device);
     void* ptrs[] = {p->d_zoom_y, p->d_zoom_x, p->d_saa_ty, p->d_saa_tx, p->d_fwd_ty, p->d_fwd_tx, p->d_bwd_ty,
                     p->d_bwd_tx, p->d_coef_lr, p->d_zoomed, p->d_coef_pad, p->d_B, p->d_acc, p->d_err, p->d_hr2,
-                    p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum, p->d_counters,
+                    p->d_partial, p->d_errors, p->d_edge, p->d_fir_iy0, p->d_fir_ix0, p->d_fir_wy, p->d_fir_wx, p->d_s1[0], p->d_s1[1], p->d_s1[2], p->d_s1[3], p->d_vsum,
                     p->d_edge_ml[0], p->d_edge_ml[1], p->d_edge_ml[2], p->d_edge_ml[3]};
     for (void* q : ptrs) if (q) gfree(q);
     free_taps(p->taps_f);
@@ -411,7 +411,7 @@ FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
     int fth, ftw;
     ibp_fast_tile(&fth, &ftw);
     bool fast_ok = ibp_fast_supported(p->kh, p->kw, p->smax) && (W % 4 == 0) && p->path != 2 && p->path != 1 && p->path != 8;
-    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || (p->path >= 4 && p->path <= 7));
+    bool sep_ok = ibp_sep_supported(p->kh, p->kw, p->smax, p->separable, W) && (p->path == 0 || p->path == 4 || p->path == 7);
     bool big = (long long)(uy1 - uy0) * W >= 64 * 64;
     const bool lat_ok = p->lat != nullptr && (p->path == 0 || p->path == 8);
     // the streaming kernel treats the local buffer (a row band with its halo) as an image of its own: what the
@@ -438,8 +438,8 @@ FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1) {
         stream_ml_geometry(p->H, W, n_sm, &r.st_nit, &r.st_seg, &r.st_nseg, &r.st_nstrip);
         r.n_fast = r.st_nseg * r.st_nstrip;
     } else if (sep_ok && p->path != 7 && (big || p->path >= 4)) {
-        r.use_ws = (p->path == 0 || p->path == 4);
-        if (r.use_ws) ibp_ws_tile(&fth, &ftw); else ibp_sep_tile(&fth, &ftw);
+        r.use_ws = true;
+        ibp_ws_tile(&fth, &ftw);
         r.use_sep = true;
         r.fast_tx = (W + ftw - 1) / ftw;
         r.fast_ty = (uy1 - uy0 + fth - 1) / fth;
@@ -478,7 +478,6 @@ int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaS
     for (int s = 0; s < p->nslot; ++s) {
         if (!p->d_s1[s]) {
             SR_TRY(plan_alloc(p, &p->d_s1[s], (size_t)rows * pitch));
-            SR_TRY(sep_make_s1_map(&p->tm_s1[s], p->d_s1[s], p->w, rows, pitch));
             SR_TRY(ws_make_s1_map(&p->tm_s1w[s], p->d_s1[s], p->w, rows, pitch));
         }
         a.s1[s] = p->d_s1[s];
@@ -513,16 +512,6 @@ int sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaS
                                            p->d_edge_ml[s], p->d_vsum, 0, p->h, 1, st));
         }
     }
-    return SR459_OK;
-}
-
-int sep_counters(sr459_plan* p, int n_iter, cudaStream_t st) {
-    if (n_iter > p->counters_cap) {
-        if (p->d_counters) { gfree(p->d_counters); p->d_counters = nullptr; p->scratch -= (int64_t)p->counters_cap * 4; }
-        SR_TRY(plan_alloc(p, &p->d_counters, (size_t)n_iter));
-        p->counters_cap = n_iter;
-    }
-    SR_CUDA(cudaMemsetAsync(p->d_counters, 0, sizeof(int) * (size_t)n_iter, st));
     return SR459_OK;
 }
 
@@ -600,8 +589,7 @@ int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, c
     }
     if (r.use_sep) {
         SepArgs f{};
-        if (r.use_ws) SR_TRY(ws_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
-        else          SR_TRY(sep_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
+        SR_TRY(ws_make_hr_map(&f.tm_hr, cur, p->W, p->hr_hi - p->hr_lo));
         f.g = g;
         for (int k = 0; k < p->n; ++k) f.lr[k] = lr[k];
         f.hr_out = nxt;
@@ -610,17 +598,16 @@ int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, c
         memcpy(f.brow, p->brow, sizeof(f.brow));
         f.nph = p->nslot;
         for (int s = 0; s < p->nslot; ++s) {
-            f.tm_s1[s] = r.use_ws ? p->tm_s1w[s] : p->tm_s1[s];
+            f.tm_s1[s] = p->tm_s1w[s];
             f.ph_pq[s] = p->slot_pq[s];
             memcpy(f.mtab[s], p->mtab[s], sizeof(f.mtab[s]));
         }
         f.s1_row0 = p->lr_lo;
         f.tiles_x = r.fast_tx; f.tiles_y = r.fast_ty; f.ty_origin = uy0;
         f.partial = partial;
-        f.tile_counter = (it >= 0 && p->d_counters && p->path == 6) ? p->d_counters + it : nullptr;
         f.n_sm = p->n_sm;
         { static const int dbg = getenv("SR459_DBG") ? atoi(getenv("SR459_DBG")) : 0; f.dbg = dbg; }
-        return r.use_ws ? launch_ibp_ws(f, st) : launch_ibp_sep(f, st);
+        return launch_ibp_ws(f, st);
     }
     if (r.use_fast) {
         FastArgs f{};
@@ -658,7 +645,7 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
-        if (r.use_sep || r.use_stream || r.use_stream_ml) { SR_TRY(sep_prepare(p, lr, r.use_stream, st, r.use_stream_ml)); SR_TRY(sep_counters(p, n_iter, st)); d_add = p->d_vsum; }
+        if (r.use_sep || r.use_stream || r.use_stream_ml) { SR_TRY(sep_prepare(p, lr, r.use_stream, st, r.use_stream_ml)); d_add = p->d_vsum; }
         for (int it = 0; it < n_iter; ++it) {
             SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st, it));
             std::swap(cur, nxt);
@@ -929,6 +916,7 @@ int sr459_plan_is_integer(const sr459_plan* plan) { return plan && plan->is_int 
 int sr459_plan_set_path(sr459_plan* plan, int path) {
     if (!plan || path < 0 || path > 8) { set_error("plan_set_path: bad arguments"); return SR459_EINVAL; }
     if (path == 8 && !plan->lat) { set_error("lattice kernel not available for this plan (needs integer |shift| <= 1, factor 2, PSF reach <= 15, W % 4 == 0)"); return SR459_EUNSUPPORTED; }
+    if (path == 5 || path == 6) { set_error("paths 5 and 6 (the four-phase and the persistent separable kernels) were removed; use 4 (k_ibp_ws) or 7 (streaming)"); return SR459_EUNSUPPORTED; }
     if (path >= 4 && path <= 7 && !(fused_supported(plan) && ibp_sep_supported(plan->kh, plan->kw, plan->smax, plan->separable, plan->W))) {
         set_error("separable TMA kernel not available for this plan (needs integer |shift| <= 1, a rank-1 PSF up to 7x7, W % 4 == 0)");
         return SR459_EUNSUPPORTED;

@@ -247,7 +247,7 @@ int  launch_ibp_fast(const FastArgs& a, cudaStream_t st);
 bool ibp_fast_supported(int kh, int kw, int smax);
 void ibp_fast_tile(int* th, int* tw);
 
-// ---- separable-PSF fused iteration (ibp_sep.cu): TMA-staged tiles, pre-summed co-sited frames -------
+// ---- separable-PSF fused iteration (lattice.cu, ibp_ws.cu): TMA-staged tiles, pre-summed co-sited frames -------
 constexpr int kMaxSlots = 4;            // active parity lattices
 
 struct LatticeArgs {                    // k_lattice_sums: S1 planes + sum of V, once per ibp() call
@@ -281,20 +281,15 @@ struct alignas(64) SepArgs {
     int tiles_x, tiles_y;
     int ty_origin;                      // global HR row of tile row 0 (even)
     double* partial;                    // one slot per tile
-    int* tile_counter;                  // pipelined kernel: zeroed counter of this iteration (null: one CTA per tile)
     int n_sm;                           // SMs of the device (grid of the pipelined kernel)
     int dbg;                            // development probes (SR459_DBG): 1 = no arithmetic, 2 = no TMA loads
 };
-int    launch_ibp_sep(const SepArgs& a, cudaStream_t st);
 bool   ibp_sep_supported(int kh, int kw, int smax, bool separable, int W);
-void   ibp_sep_tile(int* th, int* tw);
 // warp-synchronous form of the same iteration (ibp_ws.cu): tile 64 x 112, own TMA box shapes
 int    launch_ibp_ws(const SepArgs& a, cudaStream_t st);
 void   ibp_ws_tile(int* th, int* tw);
 int    ws_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
 int    ws_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
-int    sep_make_hr_map(CUtensorMap* out, const float* base, int W, int rows);
-int    sep_make_s1_map(CUtensorMap* out, const float* base, int w, int rows, int pitch);
 
 // ---- row bands: flag words at the head of a band arena, and what an iteration kernel needs to exchange halos itself (bands.cu)
 constexpr int BF_FROM_UP = 0, BF_FROM_DOWN = 1, BF_ERROR = 2, BF_BASE = 3, BF_TICKET = 4, BF_ARR_UP = 5, BF_ARR_DOWN = 6;

@@ -84,14 +84,12 @@ struct sr459_plan {
     float mtab[kMaxSlots][4] = {{0}};
     float* d_s1[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
     int   s1_rows = 0, s1_pitch = 0;
-    CUtensorMap tm_s1[kMaxSlots];     // box of ibp_sep.cu
     CUtensorMap tm_s1w[kMaxSlots];    // box of ibp_ws.cu
     double* d_vsum = nullptr;
     float* d_edge = nullptr;          // ibp_stream.cu edge vectors: colS1[h], leftS1[h], rowS1[w], topS1[w], scal[4]
     CUtensorMap tm_s1s;               // box of ibp_stream.cu (single lattice)
     CUtensorMap tm_s1ml[sr459::kMaxSlots];   // same box, one per lattice (ibp_stream_ml.cu)
     float* d_edge_ml[sr459::kMaxSlots] = {};  // per-lattice edge vectors of ibp_stream_ml.cu
-    int*  d_counters = nullptr; int counters_cap = 0;   // per-iteration tile counters of the pipelined kernel
     LatPlan* lat = nullptr;           // ibp_lat.cu: large / non-separable PSFs
     int   n_sm = 0;
 
@@ -145,7 +143,6 @@ bool fused_supported(const sr459_plan* p);
 bool use_fused(const sr459_plan* p);
 FusedRecipe fused_recipe(const sr459_plan* p, int uy0, int uy1);
 int  sep_prepare(sr459_plan* p, const float* const* lr, bool stream_kernel, cudaStream_t st, bool stream_ml = false);
-int  sep_counters(sr459_plan* p, int n_iter, cudaStream_t st);
 int  iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, const float* cur, float* nxt,
                    double* partial, int uy0, int uy1, cudaStream_t st, int it = -1);
 int  iterate_generic(sr459_plan* p, const float* const* lr, const float* cur, float* nxt, int it, cudaStream_t st);

@@ -146,11 +146,11 @@ void sr459_plan_destroy(sr459_plan* plan);
 int sr459_plan_is_integer(const sr459_plan* plan);
 /* Force a code path, for tests: 0 = automatic, 1 = generic stage-by-stage path,
  * 2 = dense fused integer kernel, 3 = polyphase fused kernel (any 7x7 PSF),
- * 4 = TMA-staged separable-PSF fused kernel, warp-synchronous form (the default
- * for rank-1 PSFs), 5 = its four-phase shared-memory form, 6 = the persistent
- * pipelined variant of 5 (single parity lattice only), 7 = the register-streaming
- * kernel (one warp per strip, TMA row ring; rank-1 PSF and a single parity lattice;
- * the default when it applies).
+ * 4 = TMA-staged separable-PSF fused kernel, warp-synchronous form (row bands
+ * of several lattices), 7 = the register-streaming kernels (one warp per strip,
+ * TMA row ring; rank-1 PSF; one lattice: k_ibp_stream, two to four lattices:
+ * k_ibp_stream_ml; the default when they apply), 8 = the lattice kernels for PSFs
+ * up to 31 x 31.  (5 and 6, two superseded separable kernels, were removed.)
  * SR459_EUNSUPPORTED if the plan's geometry cannot run the requested path.    */
 int sr459_plan_set_path(sr459_plan* plan, int path);
 /* Bytes of device scratch the plan holds.                                     */
