@@ -358,6 +358,10 @@ def bands_record(sr459, torch, dist, world, rank, peak, k31):
     def sync():
         torch.cuda.synchronize(); dist.barrier(); torch.cuda.synchronize()
 
+    how = {"gaussian7": "the iteration kernel (k_ibp_stream) stores its boundary rows straight into the neighbours' halo rows over NVLink peer "
+                        "memory -- border segments run first, one remote arrival count per warp, the next iteration's border warps wait on the counts",
+           "measured31": "after the lattice kernels (narrow 32 x 32-site tiles on thin bands) k_band_push stores the boundary rows into the neighbours' "
+                         "halo rows over NVLink peer memory and waits for theirs"}
     for tag, psf in (("measured31", k31), ("gaussian7", sr459.make_gaussian_psf())):
         full = sr459.Plan(4, h, w, NOMINAL, psf)
         saa = full.saa(lrs)
@@ -391,12 +395,15 @@ def bands_record(sr459, torch, dist, world, rank, peak, k31):
         ms, dmax, single, saa_band = [float(x) for x in t.tolist()]
         out[tag] = {
             "workload": f"config4: one {2*h}x{2*w} HR image, 4 frames, {tag} PSF, {K} IBP iterations, {world} row bands, "
-                        f"halo {lay.halo} rows; {bp.exchange_kind}; every band's initial image from its own LR rows",
+                        f"halo {lay.halo} rows; {how[tag]}; no collective on the data path, the whole loop is one CUDA graph; "
+                        f"every band's initial image from its own LR rows (banded SAA)",
             "us_per_iteration": 1e3 * ms / K, "single_gpu_us_per_iteration": 1e3 * single / K,
             "speedup_vs_single_gpu": single / ms, "efficiency": single / ms / world,
             "banded_saa_us": 1e3 * saa_band,
             "max_abs_vs_single_gpu": dmax, "mse_rel_vs_single_gpu": float(np.max(np.abs(np.array(errs) / np.array(ref_errs) - 1.0))),
-            "halo_bytes_per_iteration_per_neighbour": lay.halo * lay.W * 4, "hr_mpix_per_s": 4.0 * h * w / 1e6 / (ms / 1e3),
+            "halo_bytes_per_iteration_per_neighbour": lay.halo * lay.W * 4,
+            "nvlink_bytes_per_iteration_per_neighbour": lay.halo * lay.W * 4 + 4 * ((lay.W + 111) // 112 if tag == "gaussian7" else 1),
+            "hr_mpix_per_s": 4.0 * h * w / 1e6 / (ms / 1e3),
             "timing": "CUDA events around one graph replay of the whole loop, best of 2, max over ranks",
         }
         bp.close(); full.close()
@@ -416,6 +423,8 @@ def run_b200_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device; there is no CPU fallback (use --impl reference for the CPU port)")
     torch.cuda.set_device(local)
+    from sr459.driver import pin_rank_to_cores
+    cpu_aff = pin_rank_to_cores(local, world)          # every rank on its own share of the host cores (no-op at N = 1)
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
@@ -493,12 +502,14 @@ def run_b200_arm(args):
     sets8 = [torch.from_numpy(rng.integers(0, 256, (n, h, w), dtype=np.uint8)).pin_memory() for _ in range(ring)]
     pipe8.run([sets8[i % ring] for i in range(max(args.warmup, 3))])
     e2e_runs = []
-    for rep in range(3):                              # median of three timed runs of `steps` jobs each
+    e2e_jobs = max(args.steps, 40)                    # jobs per timed run: the pipeline's fill + drain (one H2D and one D2H copy that
+                                                      # cannot overlap compute, about 0.5 ms) must not dominate a short run
+    for rep in range(3):                              # median of three timed runs of `e2e_jobs` jobs each
         barrier()
         t0 = time.perf_counter()
-        pipe8.run([sets8[i % ring] for i in range(args.steps)])
+        pipe8.run([sets8[i % ring] for i in range(e2e_jobs)])
         torch.cuda.synchronize()
-        e2e_runs.append(time.perf_counter() - t0)
+        e2e_runs.append((time.perf_counter() - t0) * args.steps / e2e_jobs)      # scaled to `steps` jobs
     e2e8_s = statistics.median(e2e_runs)
     lat8 = pipe8.run_latency([sets8[i % ring] for i in range(min(5, args.steps))])
     barrier()
@@ -544,10 +555,10 @@ def run_b200_arm(args):
                              "in the 126 MB L2: ncu counts `traffic` DRAM bytes per launch (cold L2), dram_achieved = traffic / launch time"},
         "e2e": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
                 "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat8),
-                "runs": 3, "worst_run_value": world * args.steps * hr_mpix / (e2e8_worst_ms / 1e3),
+                "runs": 3, "jobs_per_run": e2e_jobs, "cpu_affinity": cpu_aff, "worst_run_value": world * args.steps * hr_mpix / (e2e8_worst_ms / 1e3),
                 "api": "sr459.driver.FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): run_sr.py's own I/O formats -- pinned uint8 frames in "
                        "(load_gray, :73-75), uint8 HR image out (clip + truncation, :303), conversions on the device; 3 jobs in flight, "
-                       "one CUDA-graph replay per job; median of 3 runs of `steps` jobs (max over ranks of each rank's median)"},
+                       "one CUDA-graph replay per job; median of 3 runs of `jobs_per_run` jobs each, reported per `steps` jobs (max over ranks of each rank's median)"},
         "gpu_launches": int(launches),
         "final_mse": errs[-1],
         "mse_monotone": all(b < a for a, b in zip(errs, errs[1:])),

@@ -157,7 +157,8 @@ class BandPlan:
                                                     sh.ctypes.data_as(C.POINTER(C.c_double)), kp, kh, kw,
                                                     float(step), float(clip_lo), float(clip_hi), int(rank), int(world)))
         self._h = handle
-        self.exchange_kind = "boundary rows stored into the neighbours' halo rows over NVLink peer memory by a kernel after every iteration (no collective; one CUDA graph)"
+        self.exchange_kind = ("boundary rows stored into the neighbours' halo rows over NVLink peer memory (by the streaming iteration kernel itself, "
+                              "else by k_band_push after the iteration's kernels); no collective; one CUDA graph")
         out = (C.c_int * 8)()
         _lib.check(self._lib.sr459_band_layout(self._h, out))
         ext = (C.c_int * 4)()
