@@ -55,7 +55,8 @@ struct TileCtx {
 // ---- stage 2: B on lattice (P,Q), residuals, accumulation ------------------------------------------
 // M > 0: exactly M (<= 4) frames live on this lattice and the tile needs no bounds checks: everything is
 //        compile-time unrolled.  M == 0: general instantiation (edge tiles, more than 4 frames per lattice).
-template <int P, int Q, int M>
+// RR: the PSF is zero outside |tap offset| <= RR (the measured 7 x 7 PSF of the reference has an empty outer ring: RR = 2)
+template <int P, int Q, int M, int RR>
 __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __restrict__ hs,
                                               float* __restrict__ plane, const TileCtx& c, float& e2,
                                               bool wait_stage1) {
@@ -124,6 +125,7 @@ __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __
         const float* base = hs + (2 * a0 + P + 1) * FH_COLS + 2 * b + (Q ? 2 : 0);
         #pragma unroll
         for (int rr = 0; rr < 13; ++rr) {
+            if (rr < 3 - RR || rr > 9 + RR) continue;       // no site of the four needs this staged row
             float v[8];
             #pragma unroll
             for (int q = 0; q < 4; ++q) {
@@ -133,9 +135,9 @@ __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __
             #pragma unroll
             for (int s = 0; s < 4; ++s) {
                 const int dy = rr - 3 - 2 * s;           // staged row - site centre row
-                if (dy >= -3 && dy <= 3) {
+                if (dy >= -RR && dy <= RR) {
                     #pragma unroll
-                    for (int dx = -3; dx <= 3; ++dx)
+                    for (int dx = -RR; dx <= RR; ++dx)
                         B[s] = fmaf(a.psf[(3 - dy) * 7 + (3 - dx)], v[dx + (Q ? 3 : 4)], B[s]);
                 }
             }
@@ -189,21 +191,21 @@ __device__ __forceinline__ void stage_forward(const FastArgs& a, const float* __
     }
 }
 
-template <int P, int Q>
+template <int P, int Q, int RR>
 __device__ __forceinline__ void forward_dispatch(const FastArgs& a, const float* __restrict__ hs, float* __restrict__ plane,
                                                  const TileCtx& c, float& e2, bool wait_stage1, bool edge) {
     const int m = a.ph_n[P * 2 + Q];
-    if (edge || m > F_PRE) { stage_forward<P, Q, 0>(a, hs, plane, c, e2, wait_stage1); return; }
+    if (edge || m > F_PRE) { stage_forward<P, Q, 0, RR>(a, hs, plane, c, e2, wait_stage1); return; }
     switch (m) {
-        case 1: stage_forward<P, Q, 1>(a, hs, plane, c, e2, wait_stage1); break;
-        case 2: stage_forward<P, Q, 2>(a, hs, plane, c, e2, wait_stage1); break;
-        case 3: stage_forward<P, Q, 3>(a, hs, plane, c, e2, wait_stage1); break;
-        default: stage_forward<P, Q, 4>(a, hs, plane, c, e2, wait_stage1); break;
+        case 1: stage_forward<P, Q, 1, RR>(a, hs, plane, c, e2, wait_stage1); break;
+        case 2: stage_forward<P, Q, 2, RR>(a, hs, plane, c, e2, wait_stage1); break;
+        case 3: stage_forward<P, Q, 3, RR>(a, hs, plane, c, e2, wait_stage1); break;
+        default: stage_forward<P, Q, 4, RR>(a, hs, plane, c, e2, wait_stage1); break;
     }
 }
 
 // ---- stage 3: transposed-blur contribution of lattice (P,Q) to a 4-cell column strip --------------
-template <int P, int Q>
+template <int P, int Q, int RR>
 __device__ __forceinline__ void stage_backward(const FastArgs& a, const float* __restrict__ plane,
                                                int i0, int j, float (&o)[4][2][2]) {
     #pragma unroll
@@ -216,14 +218,14 @@ __device__ __forceinline__ void stage_backward(const FastArgs& a, const float* _
             #pragma unroll
             for (int oy = 0; oy < 2; ++oy) {
                 #pragma unroll
-                for (int ta = 0; ta < 7; ++ta) {
+                for (int ta = 3 - RR; ta <= 3 + RR; ++ta) {
                     if (((ta + P + 3 + oy) & 1) != 0) continue;
                     const int da = (oy + ta + 1 - P) / 2;      // exact: numerator is even
                     if (cell + da != ar) continue;
                     #pragma unroll
                     for (int ox = 0; ox < 2; ++ox) {
                         #pragma unroll
-                        for (int tb = 0; tb < 7; ++tb) {
+                        for (int tb = 3 - RR; tb <= 3 + RR; ++tb) {
                             if (((tb + Q + 3 + ox) & 1) != 0) continue;
                             const int db = (ox + tb + 1 - Q) / 2;
                             o[cell][oy][ox] = fmaf(a.psf[ta * 7 + tb], v[db], o[cell][oy][ox]);
@@ -246,7 +248,7 @@ __device__ __noinline__ float b_direct(const FastArgs& a, const float* __restric
 
 __device__ __forceinline__ int clampi2(int v, int lo, int hi) { return min(max(v, lo), hi); }
 
-template <int DUMMY>
+template <int RR>
 __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant__ FastArgs a) {
     extern __shared__ __align__(16) float sm[];
     __shared__ float R0[FT_W + 8];       // duplicates deposited on HR row 0, x = x0-4 .. x0+131
@@ -301,10 +303,10 @@ __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant
     float e2 = 0.0f;
     {
         int slot = 0;
-        if (a.ph_n[0]) { forward_dispatch<0, 0>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
-        if (a.ph_n[1]) { forward_dispatch<0, 1>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
-        if (a.ph_n[2]) { forward_dispatch<1, 0>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
-        if (a.ph_n[3]) { forward_dispatch<1, 1>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[0]) { forward_dispatch<0, 0, RR>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[1]) { forward_dispatch<0, 1, RR>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[2]) { forward_dispatch<1, 0, RR>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
+        if (a.ph_n[3]) { forward_dispatch<1, 1, RR>(a, hs, planes + slot * FA_R * FA_C, c, e2, slot == 0, edge); ++slot; }
         if (slot == 0) {                 // no frames at all: still finish stage 1
             asm volatile("cp.async.wait_all;\n" ::: "memory");
             __syncthreads();
@@ -385,10 +387,10 @@ __global__ void __launch_bounds__(F_THREADS, 3) k_ibp_fast(const __grid_constant
         #pragma unroll
         for (int cc = 0; cc < 4; ++cc) { o[cc][0][0] = o[cc][0][1] = o[cc][1][0] = o[cc][1][1] = 0.f; }
         int slot = 0;
-        if (a.ph_n[0]) { stage_backward<0, 0>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
-        if (a.ph_n[1]) { stage_backward<0, 1>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
-        if (a.ph_n[2]) { stage_backward<1, 0>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
-        if (a.ph_n[3]) { stage_backward<1, 1>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[0]) { stage_backward<0, 0, RR>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[1]) { stage_backward<0, 1, RR>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[2]) { stage_backward<1, 0, RR>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
+        if (a.ph_n[3]) { stage_backward<1, 1, RR>(a, planes + slot * FA_R * FA_C, i0, j, o); ++slot; }
 
         const int gx = c.x0 + 2 * j;
         #pragma unroll
@@ -444,10 +446,15 @@ int launch_ibp_fast(const FastArgs& a, cudaStream_t st) {
     size_t smem = sizeof(float) * (FH_ROWS * FH_COLS + (size_t)nph * FA_R * FA_C);
     static PerDeviceMax configured;
     if (configured.raise(smem)) {
-        SR_CUDA(cudaFuncSetAttribute(k_ibp_fast<0>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_fast<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+        SR_CUDA(cudaFuncSetAttribute(k_ibp_fast<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     }
+    // effective reach of the PSF: an empty outer ring halves the multiply-adds (25 instead of 49 taps)
+    bool ring_empty = true;
+    for (int i = 0; i < 7; ++i) ring_empty = ring_empty && a.psf[i] == 0.f && a.psf[42 + i] == 0.f && a.psf[7 * i] == 0.f && a.psf[7 * i + 6] == 0.f;
     dim3 grid(a.tiles_x, a.tiles_y);
-    k_ibp_fast<0><<<grid, F_THREADS, smem, st>>>(a);
+    if (ring_empty) k_ibp_fast<2><<<grid, F_THREADS, smem, st>>>(a);
+    else            k_ibp_fast<3><<<grid, F_THREADS, smem, st>>>(a);
     SR_LAUNCH_CHECK("k_ibp_fast");
     return SR459_OK;
 }

@@ -112,7 +112,7 @@ struct ResampleErrArgs {
 };
 int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_out);
 // one CTA per kRsTileH x kRsTileW LR tile and all frames, coefficient region staged in shared memory; ONE partial per CTA
-constexpr int kRsTileH = 16, kRsTileW = 64;
+constexpr int kRsTileH = 16, kRsTileW = 32;
 int launch_resample_err_tile(const ResampleErrArgs& a, cudaStream_t st);
 
 // ---- FIR form of the fractional-shift back-projection (fir.cu) ---------------------

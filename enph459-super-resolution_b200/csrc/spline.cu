@@ -509,12 +509,12 @@ int launch_resample_err(const ResampleErrArgs& a, cudaStream_t st, int* nblocks_
 // the thread's column in registers.  16 shared-memory loads per output instead of 16 cached global gathers + two 32-byte table
 // loads (k_resample_err: 38 us at config 2; this one: see DESIGN.md).  Tables are used as they are (every boundary rule stays
 // inside them); a tile whose taps span more than the staged region (never for |shift| < 4) falls back to global gathers.
-constexpr int RE_SR = 2 * kRsTileH + 8, RE_SC = 2 * kRsTileW + 8, RE_HP = RE_SC / 2 + 1;
+constexpr int RE_SR = 2 * kRsTileH + 8, RE_SC = 2 * kRsTileW + 8, RE_HP = RE_SC / 2 + 1, RE_THREADS = 4 * kRsTileW;
 
-__global__ void __launch_bounds__(256, 3) k_resample_err_tile(const __grid_constant__ ResampleErrArgs a) {
+__global__ void __launch_bounds__(RE_THREADS, 768 / RE_THREADS) k_resample_err_tile(const __grid_constant__ ResampleErrArgs a) {
     __shared__ float coef[RE_SR][2][RE_HP];
     __shared__ AxisTap sty[kMaxFrames][kRsTileH];
-    __shared__ double red[8];
+    __shared__ double red[RE_THREADS / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int y0 = blockIdx.y * kRsTileH, x0 = blockIdx.x * kRsTileW;
     const int th = min(kRsTileH, a.h - y0), tw = min(kRsTileW, a.w - x0);
@@ -533,23 +533,23 @@ __global__ void __launch_bounds__(256, 3) k_resample_err_tile(const __grid_const
     }
     const int nr = rhi - rlo + 1, nc = chi - clo + 1;
     const bool staged = nr <= RE_SR && nc <= RE_SC;
-    const int cx = tid & 63, rg = tid >> 6;             // column of the tile, group of four rows
+    const int cx = tid % kRsTileW, rg = tid / kRsTileW;             // column of the tile, group of four rows
     const int x = x0 + cx;
     // every global load the thread needs next is issued here, before the first dependent use: its share of the coefficient
     // region, its share of the row tables, the column taps of its column for the first frames
-    constexpr int PER = (RE_SR * RE_SC + 255) / 256, NPF = 4;
+    constexpr int PER = (RE_SR * RE_SC + RE_THREADS - 1) / RE_THREADS, NPF = 4;
     AxisTap tyv;
     if (tid < a.n * th) { const int k = tid / th, r = tid - k * th; tyv = load_tap(a.ty + (size_t)k * a.h + y0 + r); }
     if (staged) {
         float cv[PER];
         #pragma unroll
         for (int i = 0; i < PER; ++i) {
-            const int e = tid + 256 * i, r = e / RE_SC, c = e - r * RE_SC;
+            const int e = tid + RE_THREADS * i, r = e / RE_SC, c = e - r * RE_SC;
             cv[i] = (r < nr && c < nc) ? __ldg(a.coef + (size_t)(rlo + r) * a.cpitch + clo + c) : 0.0f;
         }
         #pragma unroll
         for (int i = 0; i < PER; ++i) {
-            const int e = tid + 256 * i, r = e / RE_SC, c = e - r * RE_SC;
+            const int e = tid + RE_THREADS * i, r = e / RE_SC, c = e - r * RE_SC;
             if (r < RE_SR) coef[r][c & 1][c >> 1] = cv[i];
         }
     }
@@ -626,7 +626,7 @@ __global__ void __launch_bounds__(256, 3) k_resample_err_tile(const __grid_const
         if (tid == 0) {
             double t = 0.0;
             #pragma unroll
-            for (int i = 0; i < 8; ++i) t += red[i];
+            for (int i = 0; i < RE_THREADS / 32; ++i) t += red[i];
             a.partial[(size_t)blockIdx.y * gridDim.x + blockIdx.x] = t;
         }
     }
@@ -634,7 +634,7 @@ __global__ void __launch_bounds__(256, 3) k_resample_err_tile(const __grid_const
 
 int launch_resample_err_tile(const ResampleErrArgs& a, cudaStream_t st) {
     dim3 grid((a.w + kRsTileW - 1) / kRsTileW, (a.h + kRsTileH - 1) / kRsTileH);
-    k_resample_err_tile<<<grid, 256, 0, st>>>(a);
+    k_resample_err_tile<<<grid, RE_THREADS, 0, st>>>(a);
     SR_LAUNCH_CHECK("k_resample_err_tile");
     return SR459_OK;
 }
