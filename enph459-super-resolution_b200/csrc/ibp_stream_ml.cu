@@ -127,13 +127,13 @@ template <int MASK, int PQ, bool GEN, bool LEFT>
 __device__ __forceinline__ void lattice_part(State& s, const LaneConst& k, const WarpCtx& c, const StreamMLArgs& a, const int aj,
                                              const float* __restrict__ s1stage, const float Cx, const float Cy, const float Cz, const float Cw,
                                              const float C0x, const float C0y, const float C0z, const float C0w, const bool top_step,
-                                             float& Wx, float& Wy, float& Wz, float& Ww, const int lane) {
+                                             const bool own_fast, float& Wx, float& Wy, float& Wz, float& Ww, const int lane) {
     constexpr int P = PQ >> 1, Q = PQ & 1, S = slot_of(MASK, PQ);
     float B1, B2;
     row_pass<Q>(k.b, Cx, Cy, Cz, Cw, B1, B2);
     const float2 s1 = *reinterpret_cast<const float2*>(s1stage + S * ML_S1_FLOATS);
-    float m1 = k.mI1[S], m2 = k.mI2[S], w1 = k.wI1[S], w2 = k.wI2[S];
-    bool valid = true, last = false, own = true;
+    float m1 = k.mI1[S], m2 = k.mI2[S], w1 = own_fast ? k.wI1[S] : 0.0f, w2 = own_fast ? k.wI2[S] : 0.0f;
+    bool valid = true, last = false, own = own_fast;
     if (GEN) {
         valid = (aj >= 0) && (aj < c.h);
         last = (aj == c.h - 1);
@@ -200,6 +200,9 @@ __device__ __forceinline__ void ml_step(State& s, const LaneConst& k, const Warp
     constexpr bool ROW0 = (MASK & 3) != 0, ROW1 = (MASK & 12) != 0;
     #define WIN(u) s.v[(2 * T + (u)) & 7]
     const bool top_step = GEN && ROW1 && c.top && (aj == 0);
+    // fast form (interior site rows away from the image's top rows): ownership and stores still depend on where the pair sits in the
+    // warp's segment (warm-up and tail iterations) -- warp-uniform flags instead of a second code path
+    const bool ownE = (2 * aj >= c.ya) && (2 * aj < c.yb), ownO = (2 * aj + 1 >= c.ya) && (2 * aj + 1 < c.yb);
     // ---- column passes: even row 2a over window rows u = 0..6 (weight acol[6-u]), odd row 2a+1 over u = 1..7 (acol[7-u])
     u64 Elo = 0, Ehi = 0, Olo = 0, Ohi = 0;
     if (ROW0 || top_step) {                             // (for a = 0 the even row's column pass IS the one of HR row 0)
@@ -235,14 +238,14 @@ __device__ __forceinline__ void ml_step(State& s, const LaneConst& k, const Warp
     // ---- lattices of the even row ---------------------------------------------------------------------------------------------
     if (ROW0) {
         float Wx = 0.f, Wy = 0.f, Wz = 0.f, Ww = 0.f;
-        if (MASK & 1) lattice_part<MASK, 0, GEN, LEFT>(s, k, c, a, aj, s1row, Ex, Ey, Ez, Ew, 0.f, 0.f, 0.f, 0.f, false, Wx, Wy, Wz, Ww, lane);
-        if (MASK & 2) lattice_part<MASK, 1, GEN, LEFT>(s, k, c, a, aj, s1row, Ex, Ey, Ez, Ew, 0.f, 0.f, 0.f, 0.f, false, Wx, Wy, Wz, Ww, lane);
+        if (MASK & 1) lattice_part<MASK, 0, GEN, LEFT>(s, k, c, a, aj, s1row, Ex, Ey, Ez, Ew, 0.f, 0.f, 0.f, 0.f, false, ownE, Wx, Wy, Wz, Ww, lane);
+        if (MASK & 2) lattice_part<MASK, 1, GEN, LEFT>(s, k, c, a, aj, s1row, Ex, Ey, Ez, Ew, 0.f, 0.f, 0.f, 0.f, false, ownE, Wx, Wy, Wz, Ww, lane);
         s.wr[(2 * T) & 7].lo = pk(Wx, Wy); s.wr[(2 * T) & 7].hi = pk(Wz, Ww);
     }
     if (ROW1) {
         float Wx = 0.f, Wy = 0.f, Wz = 0.f, Ww = 0.f;
-        if (MASK & 4) lattice_part<MASK, 2, GEN, LEFT>(s, k, c, a, aj, s1row, Ox, Oy, Oz, Ow, Ex, Ey, Ez, Ew, top_step, Wx, Wy, Wz, Ww, lane);
-        if (MASK & 8) lattice_part<MASK, 3, GEN, LEFT>(s, k, c, a, aj, s1row, Ox, Oy, Oz, Ow, Ex, Ey, Ez, Ew, top_step, Wx, Wy, Wz, Ww, lane);
+        if (MASK & 4) lattice_part<MASK, 2, GEN, LEFT>(s, k, c, a, aj, s1row, Ox, Oy, Oz, Ow, Ex, Ey, Ez, Ew, top_step, ownO, Wx, Wy, Wz, Ww, lane);
+        if (MASK & 8) lattice_part<MASK, 3, GEN, LEFT>(s, k, c, a, aj, s1row, Ox, Oy, Oz, Ow, Ex, Ey, Ez, Ew, top_step, ownO, Wx, Wy, Wz, Ww, lane);
         s.wr[(2 * T + 1) & 7].lo = pk(Wx, Wy); s.wr[(2 * T + 1) & 7].hi = pk(Wz, Ww);
     }
 
@@ -273,8 +276,7 @@ __device__ __forceinline__ void ml_step(State& s, const LaneConst& k, const Warp
     upk(fma2(k.alpha2, o2lo, h2.lo), q2.x, q2.y); upk(fma2(k.alpha2, o2hi, h2.hi), q2.z, q2.w);
     q1.x = clipf(q1.x, k.lo, k.hi); q1.y = clipf(q1.y, k.lo, k.hi); q1.z = clipf(q1.z, k.lo, k.hi); q1.w = clipf(q1.w, k.lo, k.hi);
     q2.x = clipf(q2.x, k.lo, k.hi); q2.y = clipf(q2.y, k.lo, k.hi); q2.z = clipf(q2.z, k.lo, k.hi); q2.w = clipf(q2.w, k.lo, k.hi);
-    bool st1 = k.st_ok, st2 = k.st_ok;
-    if (GEN) { st1 = st1 && (y1 >= c.ya) && (y1 < c.yb); st2 = st2 && (y1 + 1 >= c.ya) && (y1 + 1 < c.yb); }
+    const bool st1 = k.st_ok && (y1 >= c.ya) && (y1 < c.yb), st2 = k.st_ok && (y1 + 1 >= c.ya) && (y1 + 1 < c.yb);
     if (st1) *reinterpret_cast<float4*>(outp) = q1;
     if (st2) *reinterpret_cast<float4*>(outp + a.W) = q2;
     outp += 2 * a.W;
@@ -393,9 +395,9 @@ __global__ void __launch_bounds__(ML_THREADS, ML_CTAS) k_ibp_stream_ml(const __g
     if (lane == 0 && ML_STAGES <= nit + 1) ml_issue<MASK>(a, ring, bars, ML_STAGES, xs0, sb, c.a0);
 
     for (int it = 0; it < nit; ++it) {
-        // fast form: the four pairs are interior site rows, owned, both HR rows stored, away from the top clamp rows
+        // fast form: the four pairs are interior site rows (all frames present) and none of the rows written sees the top clamp terms
         const int aj0 = c.a0 + 4 * it, aj3 = aj0 + 3;
-        const bool fast = (aj0 >= 0) && (aj3 < c.h - 1) && (2 * aj0 - 3 >= max(c.ya, c.top ? 4 : 0)) && (2 * aj3 + 1 < c.yb);
+        const bool fast = (aj0 >= 0) && (aj3 < c.h - 1) && !(c.top && 2 * aj0 - 3 < 4);
         if (left) {
             if (fast) ml_iteration<MASK, false, true>(s, k, c, a, it, ring, bars, outp, lane);
             else      ml_iteration<MASK, true, true>(s, k, c, a, it, ring, bars, outp, lane);
