@@ -122,7 +122,14 @@ int plan_common_init(sr459_plan* p, int device, int n_frames, int h, int w, int 
             }
         }
     }
-    if (fused_supported(p) && lat_supported(kh, kw, p->smax, p->W)) SR_TRY(lat_create(&p->lat, psf, kh, kw));
+    if (fused_supported(p) && lat_supported(kh, kw, p->smax, p->W)) {
+        SR_TRY(lat_create(&p->lat, psf, kh, kw));
+        if (!p->side) {                                    // k_lat_edge_b runs beside k_lat_fwd
+            SR_CUDA(cudaStreamCreateWithFlags(&p->side, cudaStreamNonBlocking));
+            SR_CUDA(cudaEventCreateWithFlags(&p->ev_fork, cudaEventDisableTiming));
+            SR_CUDA(cudaEventCreateWithFlags(&p->ev_join, cudaEventDisableTiming));
+        }
+    }
     // parity lattices of the integer HR shifts (only meaningful for |shift| <= 1)
     if (p->is_int && p->smax <= 1 && factor == 2) {
         for (int ph = 0; ph < 4; ++ph) {
@@ -585,6 +592,11 @@ int iterate_fused(sr459_plan* p, const FusedRecipe& r, const float* const* lr, c
         fill_lat_call(p, c, uy0, uy1);
         for (int k = 0; k < p->n; ++k) c.lr[k] = lr[k];
         c.hr_in = cur; c.hr_out = nxt; c.partial = partial;
+        if (p->lat_s1) {                                   // S1 planes of this call (sep_prepare): elementwise residual pass
+            c.s1_n = p->nslot; c.s1_row0 = p->lr_lo; c.s1_rows = p->s1_rows;
+            for (int s = 0; s < p->nslot; ++s) { c.s1_pq[s] = p->slot_pq[s]; c.s1[s] = p->d_s1[s]; }
+        }
+        c.side = p->side; c.ev_fork = p->ev_fork; c.ev_join = p->ev_join;
         return lat_iterate(p->lat, c, st);
     }
     if (r.use_sep) {
@@ -645,7 +657,10 @@ static int run_ibp(sr459_plan* p, const float* const* lr, float* d_hr, int n_ite
         FusedRecipe r = fused_recipe(p, 0, p->H);
         p->per_iter = r.per_iter;
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
-        if (r.use_sep || r.use_stream || r.use_stream_ml) { SR_TRY(sep_prepare(p, lr, r.use_stream, st, r.use_stream_ml)); d_add = p->d_vsum; }
+        p->lat_s1 = false;
+        if (r.use_sep || r.use_stream || r.use_stream_ml || (r.use_lat && p->nslot > 0 && !getenv("SR459_LAT_NO_S1"))) {
+            SR_TRY(sep_prepare(p, lr, r.use_stream, st, r.use_stream_ml)); d_add = p->d_vsum; p->lat_s1 = r.use_lat;
+        }
         for (int it = 0; it < n_iter; ++it) {
             SR_TRY(iterate_fused(p, r, lr, cur, nxt, p->d_partial + (size_t)it * r.per_iter, 0, p->H, st, it));
             std::swap(cur, nxt);

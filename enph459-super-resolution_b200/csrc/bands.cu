@@ -488,7 +488,10 @@ static int band_prepare(sr459_plan* p, const float* const* lr_ibp, int n_iter, c
         SR_TRY(plan_ensure_errors(p, n_iter));
         SR_TRY(plan_ensure_partial(p, (size_t)n_iter * r.per_iter));
         p->band_uses_vsum = false;
-        if (r.use_sep || r.use_stream) { SR_TRY(sep_prepare(p, lr_ibp, r.use_stream, st)); p->band_uses_vsum = true; }
+        p->lat_s1 = false;
+        if (r.use_sep || r.use_stream || (r.use_lat && p->nslot > 0 && !getenv("SR459_LAT_NO_S1"))) {
+            SR_TRY(sep_prepare(p, lr_ibp, r.use_stream, st)); p->band_uses_vsum = true; p->lat_s1 = r.use_lat;
+        }
     }
     bs->recipe_valid = true; bs->iters = n_iter;
     p->band_recipe_valid = true; p->band_iters = n_iter;

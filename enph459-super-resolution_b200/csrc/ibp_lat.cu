@@ -280,6 +280,7 @@ struct LatResidArgs {
     float* acol;                        // [H] clamp duplicates on HR column 0 ((0,0): only frames with sy != -1)
     int rows_per_cta, nsite_cta;        // part A: CTAs per slot = ceil(rows / rows_per_cta)
     int nrow_cta, ncol_cta;             // parts B/C: CTAs of 256 columns along row 0 / 256 rows along column 0
+    int first_cta;                      // blockIdx offset: nA when part A ran in k_lat_resid_s1 (only parts B/C are launched)
     double* partial;                    // one slot per CTA
 };
 
@@ -298,9 +299,10 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
     const int tid = threadIdx.x;
     double e2 = 0.0;
     const int nA = a.nsite_cta * g.nslot;
-    if ((int)blockIdx.x < nA) {
+    const int bid = (int)blockIdx.x + a.first_cta;
+    if (bid < nA) {
         // ---- part A: regular sites ------------------------------------------------------------------
-        const int s = blockIdx.x / a.nsite_cta, cb = blockIdx.x - s * a.nsite_cta;
+        const int s = bid / a.nsite_cta, cb = bid - s * a.nsite_cta;
         const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
         const int r0 = g.sa_lo + cb * a.rows_per_cta, r1 = min(r0 + a.rows_per_cta, g.sa_hi);
         for (int ar = r0; ar < r1; ++ar) {
@@ -337,8 +339,8 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
                 e2 += (double)q;
             }
         }
-    } else if ((int)blockIdx.x < nA + a.nrow_cta) {
-        const int c0 = ((int)blockIdx.x - nA) * 256;                       // this CTA's 256 columns
+    } else if (bid < nA + a.nrow_cta) {
+        const int c0 = (bid - nA) * 256;                       // this CTA's 256 columns
         // ---- parts B/C along HR row 0 / LR row 0 (only where the local rows include them) -----------------
         if (g.hr_lo == 0) {
             for (int x = c0 + tid; x < min(g.W, c0 + 256); x += 256) {
@@ -365,7 +367,7 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
         }
     } else {
         // ---- parts B/C along HR column 0 / LR column 0 ----------------------------------------------------------
-        const int r0 = ((int)blockIdx.x - nA - a.nrow_cta) * 256;           // this CTA's 256 rows
+        const int r0 = (bid - nA - a.nrow_cta) * 256;           // this CTA's 256 rows
         for (int y = g.hr_lo + r0 + tid; y < min(g.hr_hi, g.hr_lo + r0 + 256); y += 256) {
             float acc = 0.f;
             for (int k = 0; k < a.n; ++k) {
@@ -390,6 +392,71 @@ __global__ void __launch_bounds__(256) k_lat_resid(const LatResidArgs a) {
                 e2 += (double)(e * e);
             }
         }
+    }
+    __shared__ double red[8];
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) e2 += __shfl_xor_sync(0xffffffffu, e2, o);
+    if ((tid & 31) == 0) red[tid >> 5] = e2;
+    __syncthreads();
+    if (tid == 0) {
+        double t = 0.0;
+        #pragma unroll
+        for (int i = 0; i < 8; ++i) t += red[i];
+        a.partial[bid] = t;
+    }
+}
+
+// part A from pre-summed planes: A_s = S1_s - m B_s, squared error (S1 - m B)^2 / m over the site rows this launch owns (the
+// within-site variance V of the frames is constant over the iterations: k_lattice_sums, added once by the caller).
+// One CTA per site row and slot, as part A of k_lat_resid (same partial-sum slots).
+struct LatResidS1Args {
+    LatGeom g;
+    int n;
+    int sy[kMaxFrames], sx[kMaxFrames], slot_of[kMaxFrames];
+    int lr_lo, lr_hi, own_i0, own_i1;
+    const float* bl[kMaxSlots];
+    float* A[kMaxSlots];
+    const float* s1[kMaxSlots];         // by lattice slot
+    int s1_row0, s1_rows;
+    int nsite_cta;
+    double* partial;
+};
+
+__global__ void __launch_bounds__(256) k_lat_resid_s1(const __grid_constant__ LatResidS1Args a) {
+    const LatGeom& g = a.g;
+    const int tid = threadIdx.x;
+    const int s = blockIdx.x / a.nsite_cta, ar = g.sa_lo + (blockIdx.x - s * a.nsite_cta);
+    const int P = g.slot_pq[s] >> 1, Q = g.slot_pq[s] & 1;
+    int m_all = 0, m_last = 0;                          // frames with a sample at a site of this row: columns < w-1 / column w-1
+    #pragma unroll
+    for (int k = 0; k < kMaxFrames; ++k) {
+        if (k < a.n && a.slot_of[k] == s) {
+            const int i = ar + ((P + a.sy[k]) >> 1), ox = (Q + a.sx[k]) >> 1;
+            if (i < g.h && i >= a.lr_lo && i < a.lr_hi) { ++m_all; if (ox == 0) ++m_last; }
+        }
+    }
+    const bool own = ar >= a.own_i0 && ar < a.own_i1;
+    const bool have = ar >= a.s1_row0 && ar < a.s1_row0 + a.s1_rows;
+    const float* blrow = a.bl[s] + (size_t)(ar - g.sa_lo) * g.pitch;
+    const float* srow = a.s1[s] + (size_t)(have ? ar - a.s1_row0 : 0) * g.pitch;
+    float* out = a.A[s] + (size_t)(ar - g.sa_lo) * g.pitch;
+    const float mf = have ? (float)m_all : 0.0f, ml = have ? (float)m_last : 0.0f;
+    const float wf = (own && mf > 0.0f) ? 1.0f / mf : 0.0f, wl = (own && ml > 0.0f) ? 1.0f / ml : 0.0f;
+    double e2 = 0.0;
+    for (int b4 = tid; 4 * b4 < g.w; b4 += 256) {                          // pitch is a multiple of 4: whole float4s
+        const float4 bl = __ldg(reinterpret_cast<const float4*>(blrow) + b4);
+        const float4 sv = have ? __ldg(reinterpret_cast<const float4*>(srow) + b4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        const int b = 4 * b4;
+        float4 r; float q = 0.0f;
+        {
+            const bool l0 = b == g.w - 1, l1 = b + 1 == g.w - 1, l2 = b + 2 == g.w - 1, l3 = b + 3 == g.w - 1;
+            r.x = fmaf(-(l0 ? ml : mf), bl.x, sv.x); q = fmaf(r.x * (l0 ? wl : wf), r.x, q);
+            r.y = (b + 1 < g.w) ? fmaf(-(l1 ? ml : mf), bl.y, sv.y) : 0.0f; q = fmaf(r.y * (l1 ? wl : wf), r.y, q);
+            r.z = (b + 2 < g.w) ? fmaf(-(l2 ? ml : mf), bl.z, sv.z) : 0.0f; q = fmaf(r.z * (l2 ? wl : wf), r.z, q);
+            r.w = (b + 3 < g.w) ? fmaf(-(l3 ? ml : mf), bl.w, sv.w) : 0.0f; q = fmaf(r.w * (l3 ? wl : wf), r.w, q);
+        }
+        *(reinterpret_cast<float4*>(out) + b4) = r;
+        e2 += (double)q;
     }
     __shared__ double red[8];
     #pragma unroll
@@ -693,6 +760,9 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
         L->attr_done[NB == 16] = true;
     }
     const int tiles_x = (g.w + D::COLS - 1) / D::COLS;
+    if (c.side != nullptr && c.ev_fork != nullptr && c.ev_join != nullptr) {
+        SR_CUDA(cudaEventRecord(c.ev_fork, st)); SR_CUDA(cudaStreamWaitEvent(c.side, c.ev_fork, 0));
+    }
     {   // forward
         LatFwdArgs<NT> a;
         a.tab = reinterpret_cast<const ulonglong2*>(L->d_tabf); a.g = g; a.hr = c.hr_in;
@@ -701,12 +771,14 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
         k_lat_fwd<NT, NB><<<grid, LT_WARPS * 32, smem_f, st>>>(a);
         SR_LAUNCH_CHECK("k_lat_fwd");
     }
-    {   // B on row 0 / column 0
+    const bool forked = c.side != nullptr && c.ev_fork != nullptr && c.ev_join != nullptr;
+    {   // B on row 0 / column 0: independent of k_lat_fwd (both only read hr) -> on the side stream beside it when there is one
         LatEdgeBArgs a{g, c.hr_in, L->d_psf, L->RT, L->d_btop, L->d_bleft};
         const int npts = (g.hr_lo == 0 ? g.W : 0) + (g.hr_hi - g.hr_lo);
-        k_lat_edge_b<<<(npts + 7) / 8, 256, 0, st>>>(a);
+        k_lat_edge_b<<<(npts + 7) / 8, 256, 0, forked ? c.side : st>>>(a);
         SR_LAUNCH_CHECK("k_lat_edge_b");
     }
+    bool joined = !forked;
     {   // residuals
         LatResidArgs a{};
         a.g = g; a.n = c.n;
@@ -716,8 +788,37 @@ static int lat_iterate_t(LatPlan* L, const LatCall& c, const LatSetup& S, const 
         a.btop = L->d_btop; a.bleft = L->d_bleft; a.arow = L->d_arow; a.acol = L->d_acol;
         a.rows_per_cta = S.rows_per_cta; a.nsite_cta = S.nsite_cta; a.nrow_cta = S.nrow_cta; a.ncol_cta = S.ncol_cta;
         a.partial = c.partial;
-        k_lat_resid<<<S.nsite_cta * g.nslot + S.nrow_cta + S.ncol_cta, 256, 0, st>>>(a);
-        SR_LAUNCH_CHECK("k_lat_resid");
+        const int nA = S.nsite_cta * g.nslot;
+        // pre-summed planes for every lattice of this call: part A is one elementwise pass (k_lat_resid_s1)
+        const float* s1_of[kMaxSlots] = {nullptr, nullptr, nullptr, nullptr};
+        bool have_s1 = c.s1_n > 0 && S.rows_per_cta == 1;
+        for (int t = 0; t < g.nslot && have_s1; ++t) {
+            for (int q = 0; q < c.s1_n; ++q) if (c.s1_pq[q] == g.slot_pq[t]) s1_of[t] = c.s1[q];
+            if (!s1_of[t]) have_s1 = false;
+        }
+        if (have_s1) {
+            LatResidS1Args r{};
+            r.g = g; r.n = c.n;
+            for (int k = 0; k < c.n; ++k) { r.sy[k] = c.sy[k]; r.sx[k] = c.sx[k]; r.slot_of[k] = S.slot_of[k]; }
+            r.lr_lo = c.lr_lo; r.lr_hi = c.lr_hi; r.own_i0 = c.own_i0; r.own_i1 = c.own_i1;
+            for (int s = 0; s < kMaxSlots; ++s) { r.bl[s] = L->d_bl[s]; r.A[s] = L->d_A[s]; r.s1[s] = s1_of[s]; }
+            r.s1_row0 = c.s1_row0; r.s1_rows = c.s1_rows; r.nsite_cta = S.nsite_cta; r.partial = c.partial;
+            // the clamp / MSE-only terms of row 0 and column 0 (parts B / C) need k_lat_fwd's planes and k_lat_edge_b's vectors: on the
+            // side stream, behind k_lat_edge_b and a second fork after k_lat_fwd, beside the elementwise pass
+            cudaStream_t sbc = st;
+            if (forked) { SR_CUDA(cudaEventRecord(c.ev_fork, st)); SR_CUDA(cudaStreamWaitEvent(c.side, c.ev_fork, 0)); sbc = c.side; }
+            k_lat_resid_s1<<<nA, 256, 0, st>>>(r);
+            SR_LAUNCH_CHECK("k_lat_resid_s1");
+            a.first_cta = nA;
+            k_lat_resid<<<S.nrow_cta + S.ncol_cta, 256, 0, sbc>>>(a);
+            SR_LAUNCH_CHECK("k_lat_resid");
+            if (forked) { SR_CUDA(cudaEventRecord(c.ev_join, c.side)); SR_CUDA(cudaStreamWaitEvent(st, c.ev_join, 0)); joined = true; }
+        } else {
+            if (!joined) { SR_CUDA(cudaEventRecord(c.ev_join, c.side)); SR_CUDA(cudaStreamWaitEvent(st, c.ev_join, 0)); joined = true; }
+            a.first_cta = 0;
+            k_lat_resid<<<nA + S.nrow_cta + S.ncol_cta, 256, 0, st>>>(a);
+            SR_LAUNCH_CHECK("k_lat_resid");
+        }
     }
     {   // backward + update
         LatBwdArgs<NT> a;

@@ -374,6 +374,13 @@ struct LatCall {
     const float* lr[kMaxFrames];
     const float* hr_in; float* hr_out;
     double* partial;                    // lat_per_iter() slots
+    // optional pre-summed S1 planes (k_lattice_sums, once per ibp() call): the site residuals become A = S1 - m B, one elementwise
+    // pass instead of a pass over the n frames; the caller then adds the planes' sum of V to the squared-error sums
+    int s1_n;                           // 0: not available
+    int s1_pq[kMaxSlots];               // P*2+Q of plane t
+    const float* s1[kMaxSlots];         // rows x pitch floats, pitch = (w + 3) & ~3; plane row r = site row s1_row0 + r
+    int s1_row0, s1_rows;
+    cudaStream_t side; cudaEvent_t ev_fork, ev_join;   // optional: k_lat_edge_b runs beside k_lat_fwd (null: in line)
 };
 bool    lat_supported(int kh, int kw, int smax, int W);
 int     lat_create(LatPlan** out, const double* psf, int kh, int kw);

@@ -86,6 +86,7 @@ struct sr459_plan {
     int   s1_rows = 0, s1_pitch = 0;
     CUtensorMap tm_s1w[kMaxSlots];    // box of ibp_ws.cu
     double* d_vsum = nullptr;
+    bool lat_s1 = false;              // the lattice kernels of the current call use the S1 planes (elementwise residual pass)
     float* d_edge = nullptr;          // ibp_stream.cu edge vectors: colS1[h], leftS1[h], rowS1[w], topS1[w], scal[4]
     CUtensorMap tm_s1s;               // box of ibp_stream.cu (single lattice)
     CUtensorMap tm_s1ml[sr459::kMaxSlots];   // same box, one per lattice (ibp_stream_ml.cu)
