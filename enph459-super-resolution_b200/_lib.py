@@ -58,6 +58,7 @@ _SIGNATURES = {
     "sr459_f32_to_u8": (_I, [_P, _L, _P, _P]),
     "sr459_blur": (_I, [_P, _I, _I, _PD, _I, _I, _P, _P]),
     "sr459_zoom": (_I, [_P, _I, _I, _I, _P, _P]),
+    "sr459_zoom_to": (_I, [_P, _I, _I, _I, _I, _I, _P, _P]),
     "sr459_shift": (_I, [_P, _I, _I, _D, _D, _P, _P]),
     "sr459_forward_model": (_I, [_P, _I, _I, _PD, _I, _I, _D, _D, _I, _P, _P]),
     "sr459_back_project": (_I, [_P, _I, _I, _PD, _I, _I, _D, _D, _I, _I, _I, _P, _P]),

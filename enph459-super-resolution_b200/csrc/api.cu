@@ -820,29 +820,34 @@ int sr459_blur(const float* d_img, int H, int W, const double* h_psf, int kh, in
     return rc;
 }
 
-int sr459_zoom(const float* d_in, int h, int w, int factor, float* d_out, void* stream) {
-    if (!d_in || !d_out || h < 1 || w < 1 || factor < 1) { set_error("zoom: bad arguments"); return SR459_EINVAL; }
+int sr459_zoom_to(const float* d_in, int h, int w, int H, int W, int order, float* d_out, void* stream) {
+    if (!d_in || !d_out || h < 1 || w < 1 || H < 1 || W < 1) { set_error("zoom: bad arguments"); return SR459_EINVAL; }
+    if (order != 0 && order != 1 && order != 3) { set_error("zoom: spline order %d is not implemented (0, 1 and 3 are)", order); return SR459_EUNSUPPORTED; }
     cudaStream_t st = (cudaStream_t)stream;
-    const int H = h * factor, W = w * factor;
     std::vector<AxisTap> ty, tx;
-    build_zoom_axis(h, H, ty);
-    build_zoom_axis(w, W, tx);
+    build_zoom_axis(h, H, ty, order);
+    build_zoom_axis(w, W, tx, order);
     AxisTap *dty = nullptr, *dtx = nullptr; float* coef = nullptr;
     int rc = upload_taps_tbl(ty, &dty);
     if (rc == SR459_OK) rc = upload_taps_tbl(tx, &dtx);
-    if (rc == SR459_OK) rc = dev_alloc(&coef, (size_t)h * w);
-    if (rc == SR459_OK) {
+    if (rc == SR459_OK && order == 3) rc = dev_alloc(&coef, (size_t)h * w);
+    if (rc == SR459_OK && order == 3) {
         PrefilterJob j{d_in, coef, h, w, h, w, h, w, SRC_PLAIN, 1};
         rc = launch_prefilter2d(&j, 1, st);
     }
     if (rc == SR459_OK) {
         ResampleSumArgs a{};
-        a.coef[0] = coef; a.cpitch[0] = w; a.n = 1; a.ty = dty; a.tx = dtx; a.Hout = H; a.Wout = W; a.scale = 1.0f; a.out = d_out;
+        a.coef[0] = order == 3 ? coef : d_in; a.cpitch[0] = w; a.n = 1; a.ty = dty; a.tx = dtx; a.Hout = H; a.Wout = W; a.scale = 1.0f; a.out = d_out;
         rc = launch_resample_sum(a, st);
     }
     cudaStreamSynchronize(st);
     if (dty) gfree(dty); if (dtx) gfree(dtx); if (coef) gfree(coef);
     return rc;
+}
+
+int sr459_zoom(const float* d_in, int h, int w, int factor, float* d_out, void* stream) {
+    if (factor < 1) { set_error("zoom: bad arguments"); return SR459_EINVAL; }
+    return sr459_zoom_to(d_in, h, w, h * factor, w * factor, 3, d_out, stream);
 }
 
 // shared body of shift / forward_model / back_project: out = spline(pad(src virtual)) evaluated with tables

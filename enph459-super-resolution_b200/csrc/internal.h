@@ -78,7 +78,7 @@ struct PrefilterJob {
 int launch_prefilter2d(const PrefilterJob* h_jobs, int njobs, cudaStream_t st);
 
 // host-side table builders (double precision, converted to float weights)
-void build_zoom_axis(int n_in, int n_out, std::vector<AxisTap>& out);
+void build_zoom_axis(int n_in, int n_out, std::vector<AxisTap>& out, int order = 3);   // order 0, 1 or 3
 // shift tables: output o = 0..n_out-1 at stride `stride` (decimation), coordinate o*stride - s + 12
 void build_shift_axis(int n, double s, int n_out, int stride, std::vector<AxisTap>& out);
 

@@ -43,12 +43,24 @@ static inline int mirror_idx(long long i, int n) {
     return (int)(m >= n ? p - m : m);
 }
 
-void build_zoom_axis(int n_in, int n_out, std::vector<AxisTap>& out) {
+void build_zoom_axis(int n_in, int n_out, std::vector<AxisTap>& out, int order) {
     out.resize(n_out);
     double ratio = (n_out > 1) ? (double)(n_in - 1) / (double)(n_out - 1) : 1.0;
     for (int o = 0; o < n_out; ++o) {
         double x = (double)o * ratio;
         bool valid = (x >= 0.0) && (x <= (double)(n_in - 1));   // mode='constant', cval=0
+        if (order < 2) {                                        // nearest / linear: no prefilter, 1 or 2 taps, samples outside are 0
+            const double fl = order == 0 ? floor(x + 0.5) : floor(x), t = x - fl;
+            const long long i0 = (long long)fl;
+            const double wv[2] = {order == 0 ? 1.0 : 1.0 - t, order == 0 ? 0.0 : t};
+            for (int j = 0; j < 4; ++j) {
+                const long long i = i0 + (j < 2 ? j : 0);
+                const bool in = i >= 0 && i < n_in;
+                out[o].idx[j] = (int)std::min<long long>(std::max<long long>(i, 0), n_in - 1);
+                out[o].w[j] = (j < 2 && valid && in) ? (float)wv[j] : 0.0f;
+            }
+            continue;
+        }
         double fl = floor(x);
         double w[4];
         cubic_w(x - fl, w);

@@ -268,20 +268,24 @@ def blur(img, kernel):
     return _ret(out, as_np)
 
 
-def ndi_zoom(img, factor: int = 2, order: int = 3):
-    """scipy.ndimage.zoom(img, factor, order=3) with scipy's defaults (integer factor)."""
-    if order != 3:
-        raise NotImplementedError("only order=3 (the reference's setting) is implemented")
-    if int(factor) != factor or factor < 1:
-        raise NotImplementedError("only integer zoom factors are implemented")
+def ndi_zoom(img, factor=2, order: int = 3):
+    """scipy.ndimage.zoom(img, factor, order) with scipy's other defaults: any scalar or (fy, fx) zoom factor (output shape
+    round(h * fy) x round(w * fx), as scipy rounds), spline order 0, 1 or 3 (the reference's setting)."""
+    if order not in (0, 1, 3):
+        raise NotImplementedError("spline orders 0, 1 and 3 are implemented (the reference uses 3)")
+    fy, fx = (factor, factor) if np.isscalar(factor) else factor
+    if fy <= 0 or fx <= 0:
+        raise ValueError("zoom factors must be positive")
     torch = _torch()
     lib = _lib.load()
     as_np = not _is_tensor(img)
     t = _dev(img)
     _check2d(t, "img")
-    f = int(factor)
-    out = torch.empty((t.shape[0] * f, t.shape[1] * f), dtype=torch.float32, device=t.device)
-    _lib.check(lib.sr459_zoom(_ptr(t), t.shape[0], t.shape[1], f, _ptr(out), _stream_ptr()))
+    H, W = int(round(t.shape[0] * fy)), int(round(t.shape[1] * fx))
+    if H < 1 or W < 1:
+        raise ValueError("zoom factor too small for this image")
+    out = torch.empty((H, W), dtype=torch.float32, device=t.device)
+    _lib.check(lib.sr459_zoom_to(_ptr(t), t.shape[0], t.shape[1], H, W, int(order), _ptr(out), _stream_ptr()))
     return _ret(out, as_np)
 
 
@@ -483,13 +487,16 @@ _DUMMY_PSF = np.array([[1.0]])
 
 def shift_and_add(lr_list, shifts_yx, factor=2, order=3):
     """SAA: mean over frames of shift(zoom(lr, factor), factor*shift) -- run_sr.py:181-187."""
-    if order != 3:
-        raise NotImplementedError("only order=3 (the reference's setting) is implemented")
     if len(lr_list) != len(shifts_yx):
         # the reference zips the two lists; a silent truncation is never intended
         raise ValueError("lr_list and shifts_yx differ in length")
     as_np = not _is_tensor(lr_list[0])
     h, w = lr_list[0].shape
+    if order != 3 or int(factor) != factor:
+        # `order` only reaches zoom (run_sr.py:185, quirk Q7); the shift stays cubic: frame by frame through the stand-alone
+        # operators (the fused plan path is built for the reference's order 3 and integer factors)
+        terms = [ndi_shift(ndi_zoom(_dev(lr), factor, order), (dy * factor, dx * factor)) for lr, (dy, dx) in zip(lr_list, shifts_yx)]
+        return _ret(mean_frames(terms), as_np)
     plan = get_plan(len(lr_list), h, w, shifts_yx, _DUMMY_PSF, factor)
     return _ret(plan.saa(lr_list), as_np)
 

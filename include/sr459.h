@@ -115,6 +115,10 @@ int sr459_blur(const float* d_img, int H, int W, const double* h_psf, int kh, in
 /* scipy.ndimage.zoom(a, factor, order=3), defaults      call sites run_sr.py:185, :279.
  * out is round(h*factor) x round(w*factor).                                   */
 int sr459_zoom(const float* d_in, int h, int w, int factor, float* d_out, void* stream);
+/* scipy.ndimage.zoom(img, zoom, order=order) for any output size H x W = round(h * zoom_y) x round(w * zoom_x) (the caller
+ * rounds as scipy does) and spline order 0, 1 or 3 -- what shift_and_add(lr_list, shifts, factor, order) hands to zoom,
+ * run_sr.py:185; other arguments scipy's defaults (mode='constant', grid_mode=False).  Synchronises the stream.        */
+int sr459_zoom_to(const float* d_in, int h, int w, int H, int W, int order, float* d_out, void* stream);
 /* One axis of back_project's  shift(zero_insert(err, factor), s, order=3, mode='nearest')  (run_sr.py:170-176) as a
  * banded matrix: out[o] = sum_{a<20} h_w[o*20 + a] * err[h_i0[o] + a], o = 0 .. factor*n_lr-1; `shift` is the HR
  * shift scipy receives (-factor*d).  Host only (no device work): the tables the FIR back-projection kernel uses.

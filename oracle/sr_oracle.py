@@ -200,6 +200,33 @@ def ndi_zoom_cubic(a: np.ndarray, factor) -> np.ndarray:
     return apply_tables(coef, axis_tables(xy, a.shape[0], vy), axis_tables(xx, a.shape[1], vx))
 
 
+def ndi_zoom_order(a: np.ndarray, factor, order: int = 3) -> np.ndarray:
+    """``scipy.ndimage.zoom(a, factor, order=order)`` for order 0 (nearest: floor(x + 0.5)), 1 (linear) and 3; no prefilter below
+    order 2, samples outside the array are cval = 0 (mode='constant')."""
+    if order == 3:
+        return ndi_zoom_cubic(a, factor)
+    if order not in (0, 1):
+        raise NotImplementedError("oracle restates orders 0, 1 and 3")
+    a = np.asarray(a, dtype=np.float64)
+    h, w = a.shape
+    fy, fx = (factor, factor) if np.isscalar(factor) else factor
+    oh, ow = int(round(h * fy)), int(round(w * fx))
+
+    def taps(n, m):
+        x, valid = zoom_coords(n, m)
+        if order == 0:
+            return [(np.floor(x + 0.5).astype(int), valid)]
+        fl = np.floor(x)
+        return [(fl.astype(int), (1.0 - (x - fl)) * valid), (fl.astype(int) + 1, (x - fl) * valid)]
+
+    out = np.zeros((oh, ow))
+    for iy, wy in taps(h, oh):
+        for ix, wx in taps(w, ow):
+            wy_in, wx_in = wy * ((iy >= 0) & (iy < h)), wx * ((ix >= 0) & (ix < w))
+            out += wy_in[:, None] * wx_in[None, :] * a[np.clip(iy, 0, h - 1)][:, np.clip(ix, 0, w - 1)]
+    return out
+
+
 def shift_coords(n: int, s: float, n_out: int | None = None, stride: int = 1):
     """Padded-array coordinate of output samples for ``shift(mode='nearest')``."""
     n_out = n if n_out is None else n_out
@@ -332,12 +359,10 @@ def native_2x(mean_lr, factor=2):
 
 
 def shift_and_add(lr_list, shifts_yx, factor=2, order=3):
-    """run_sr.py:181-187.  ``order`` only reaches zoom (quirk Q7); only 3 is restated."""
-    if order != 3:
-        raise NotImplementedError("oracle restates order=3 only")
+    """run_sr.py:181-187.  ``order`` only reaches zoom (quirk Q7); orders 0, 1 and 3 are restated."""
     acc = None
     for lr, (dy, dx) in zip(lr_list, shifts_yx):
-        up = ndi_zoom_cubic(lr, factor)
+        up = ndi_zoom_order(lr, factor, order)
         term = ndi_shift_cubic_nearest(up, (dy * factor, dx * factor))
         acc = term if acc is None else acc + term
     return acc / len(lr_list)

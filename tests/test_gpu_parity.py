@@ -790,6 +790,26 @@ def test_band_plan_fractional_shifts_get_the_wide_halo(sr):
         BandPlan(4, 64, 64, CALIBRATED, O.make_gaussian_psf(), 0, 4)
 
 
+def test_zoom_orders_and_factors_and_saa_order(sr):
+    """ndi_zoom for spline orders 0 / 1 / 3 and integer, fractional and per-axis factors; shift_and_add(order != 3) (the order only
+    reaches zoom, run_sr.py:185) -- against the oracle (pinned to live scipy in tests/test_oracle_pinning.py)."""
+    rng = np.random.default_rng(41)
+    for shape in [(33, 47), (7, 5), (64, 96), (2, 2)]:
+        a = rng.uniform(0, 255, shape)
+        for factor in (2, 3, 1.5, 2.37, (2, 1.5)):
+            for order in (0, 1, 3):
+                got = sr.ndi_zoom(a, factor, order)
+                ref = O.ndi_zoom_order(a, factor, order)
+                assert got.shape == ref.shape
+                _close(got, ref, what=f"zoom {shape} x{factor} order {order}")
+    with pytest.raises(NotImplementedError):
+        sr.ndi_zoom(a, 2, order=2)
+    lrs = [rng.uniform(0, 255, (40, 56)) for _ in NOMINAL]
+    for order in (0, 1):
+        for shifts in (NOMINAL, CALIBRATED):
+            _close(sr.shift_and_add(lrs, shifts, 2, order), O.shift_and_add(lrs, shifts, 2, order), what=f"saa order {order}")
+
+
 # ---------------------------------------------------------------- run_sr.py-compatible CLI on synthetic session folders
 def _png(path, arr):
     from PIL import Image

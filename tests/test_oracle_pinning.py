@@ -224,3 +224,25 @@ def test_oracle_vs_reference_png_goldens_rgb_cal_target():
     _same_png(native, np.array(Image.open(os.path.join(res_root, combo, "native_2x.png"))))
     saa = O.shift_and_add(frames, shifts)
     _same_png(saa, np.array(Image.open(os.path.join(res_root, combo, "SAA.png"))))
+
+
+def test_zoom_orders_0_and_1_and_non_integer_factors_match_scipy():
+    """`order` of shift_and_add reaches zoom (run_sr.py:185): the oracle's restatement of scipy.ndimage.zoom for orders 0 / 1 / 3 and
+    scalar or per-axis, integer or fractional factors against live scipy."""
+    ndi = pytest.importorskip("scipy.ndimage")
+    rng = np.random.default_rng(31)
+    for shape in [(7, 5), (33, 47), (2, 2), (1, 9), (64, 96)]:
+        a = rng.uniform(0, 255, shape)
+        for factor in (2, 3, 1.5, 2.37, (2, 1.5)):
+            for order in (0, 1, 3):
+                if order == 3 and min(shape) < 2:
+                    continue
+                ref = ndi.zoom(a, factor, order=order)
+                got = O.ndi_zoom_order(a, factor, order)
+                assert got.shape == ref.shape
+                assert np.max(np.abs(got - ref)) < 1e-9, (shape, factor, order)
+    lrs = [rng.uniform(0, 255, (12, 17)) for _ in range(3)]
+    shifts = [(0.5, -0.5), (0.3, 0.2), (0.0, 0.0)]
+    for order in (0, 1):
+        ref = sum(ndi.shift(ndi.zoom(l, 2, order=order), (2 * dy, 2 * dx), order=3, mode="nearest") for l, (dy, dx) in zip(lrs, shifts)) / 3
+        assert np.max(np.abs(O.shift_and_add(lrs, shifts, 2, order) - ref)) < 1e-9
