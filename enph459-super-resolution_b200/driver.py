@@ -29,14 +29,18 @@ class FrameSetPipeline:
     """
 
     def __init__(self, n_frames, h, w, shifts_yx, kernel, n_iter, factor=2, step=ops.IBP_STEP_SIZE,
-                 depth=3, in_dtype="f32", out_dtype="f32", device=None, use_graph=False):
+                 depth=3, in_dtype="f32", out_dtype="f32", device=None, use_graph=False, lanes=1):
+        """lanes: independent compute lanes (each its own plan = its own scratch, and its own compute stream); job i runs on lane
+        i mod lanes, so that the kernels of consecutive jobs overlap at their launch boundaries and tails."""
         torch = ops._torch()
         self.torch = torch
         self.use_graph = bool(use_graph)
         if device is not None:
             torch.cuda.set_device(device)
         self.dev = torch.device("cuda", torch.cuda.current_device())
-        self.plan = ops.Plan(n_frames, h, w, shifts_yx, kernel, factor, step)
+        self.lanes = max(1, int(lanes))
+        self.plans = [ops.Plan(n_frames, h, w, shifts_yx, kernel, factor, step) for _ in range(self.lanes)]
+        self.plan = self.plans[0]
         self.n, self.h, self.w, self.n_iter = int(n_frames), int(h), int(w), int(n_iter)
         self.H, self.W = self.plan.H, self.plan.W
         self.depth = int(depth)
@@ -44,9 +48,13 @@ class FrameSetPipeline:
         tin = torch.uint8 if in_dtype == "u8" else torch.float32
         tout = torch.uint8 if out_dtype == "u8" else torch.float32
         self.s_h2d, self.s_cmp, self.s_d2h = (torch.cuda.Stream() for _ in range(3))
+        self.s_lane = [self.s_cmp] + [torch.cuda.Stream() for _ in range(self.lanes - 1)]
+        if self.depth % self.lanes:
+            self.depth += self.lanes - self.depth % self.lanes          # slot i always runs on lane i mod lanes
         self.slots = []
-        for _ in range(self.depth):
+        for i in range(self.depth):
             self.slots.append(dict(
+                lane=i % self.lanes,
                 raw=torch.empty((self.n, self.h, self.w), dtype=tin, device=self.dev),
                 lr=torch.empty((self.n, self.h, self.w), dtype=torch.float32, device=self.dev) if in_dtype == "u8" else None,
                 hr=torch.empty((self.H, self.W), dtype=torch.float32, device=self.dev),
@@ -61,12 +69,13 @@ class FrameSetPipeline:
         if self.use_graph:
             # one captured launch sequence per slot (slot buffers and the plan's scratch are baked in); the
             # un-captured warm-up run allocates the plan's lazy scratch first
-            with torch.cuda.stream(self.s_cmp):
-                self._compute(self.slots[0])
+            for lane in range(self.lanes):
+                with torch.cuda.stream(self.s_lane[lane]):
+                    self._compute(self.slots[lane])
             torch.cuda.synchronize()
             for slot in self.slots:
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=self.s_cmp):
+                with torch.cuda.graph(g, stream=self.s_lane[slot["lane"]]):
                     self._compute(slot)
                 slot["graph"] = g
 
@@ -74,7 +83,8 @@ class FrameSetPipeline:
         self.torch.cuda.synchronize()
         for slot in self.slots:
             slot["graph"] = None
-        self.plan.close()
+        for p in self.plans:
+            p.close()
 
     def _compute(self, slot):
         """(u8 -> f32,) SAA + IBP (, clip + truncation to u8) of one slot on the current stream."""
@@ -86,7 +96,7 @@ class FrameSetPipeline:
             frames = slot["lr"]
         else:
             frames = slot["raw"]
-        self.plan.saa_ibp([frames[k] for k in range(self.n)], self.n_iter, out=slot["hr"], want_errors=False)
+        self.plans[slot["lane"]].saa_ibp([frames[k] for k in range(self.n)], self.n_iter, out=slot["hr"], want_errors=False)
         if self.out_dtype == "u8":
             ops._lib.check(lib.sr459_f32_to_u8(ops._ptr(slot["hr"]), slot["hr"].numel(), ops._ptr(slot["out"]), st))
 
@@ -101,14 +111,15 @@ class FrameSetPipeline:
             self.s_h2d.wait_event(slot["ev_cmp"])   # previous compute on this slot is done with raw/lr
             slot["raw"].copy_(host_frames, non_blocking=True)
             slot["ev_in"].record(self.s_h2d)
-        with torch.cuda.stream(self.s_cmp):
-            self.s_cmp.wait_event(slot["ev_in"])
-            self.s_cmp.wait_event(slot["ev_out"])   # previous D2H of this slot finished reading hr/out
+        s_cmp = self.s_lane[slot["lane"]]
+        with torch.cuda.stream(s_cmp):
+            s_cmp.wait_event(slot["ev_in"])
+            s_cmp.wait_event(slot["ev_out"])        # previous D2H of this slot finished reading hr/out
             if slot["graph"] is not None:
                 slot["graph"].replay()
             else:
                 self._compute(slot)
-            slot["ev_cmp"].record(self.s_cmp)
+            slot["ev_cmp"].record(s_cmp)
         with torch.cuda.stream(self.s_d2h):
             self.s_d2h.wait_event(slot["ev_cmp"])
             src = slot["out"] if self.out_dtype == "u8" else slot["hr"]

@@ -729,10 +729,12 @@ def test_burst_stream_matches_oracle(sr, use_graph):
         assert d.max() <= 1 and (d > 0).mean() < 1e-3, f"set {i}: {d.max()} / {(d > 0).mean()}"
 
 
+@pytest.mark.parametrize("lanes", [1, 2])
 @pytest.mark.parametrize("use_graph", [False, True])
 @pytest.mark.parametrize("dt", ["f32", "u8"])
-def test_frame_set_pipeline_matches_oracle(sr, dt, use_graph):
-    """Batched driver (config 3): pinned host sets in, results out, slots re-used, optional CUDA-graph replay."""
+def test_frame_set_pipeline_matches_oracle(sr, dt, use_graph, lanes):
+    """Batched driver (config 3): pinned host sets in, results out, slots re-used, optional CUDA-graph replay, one or two
+    independent compute lanes (own plan and stream each; results arrive in submission order either way)."""
     import torch
     from sr459.driver import FrameSetPipeline, shard_indices
     rng = np.random.default_rng(56)
@@ -742,7 +744,7 @@ def test_frame_set_pipeline_matches_oracle(sr, dt, use_graph):
         sets = [torch.from_numpy(rng.integers(0, 256, (4, h, w), dtype=np.uint8)).pin_memory() for _ in range(5)]
     else:
         sets = [torch.from_numpy(rng.uniform(0, 255, (4, h, w)).astype(np.float32)).pin_memory() for _ in range(5)]
-    pipe = FrameSetPipeline(4, h, w, NOMINAL, psf, K, depth=2, in_dtype=dt, out_dtype=dt, use_graph=use_graph)
+    pipe = FrameSetPipeline(4, h, w, NOMINAL, psf, K, depth=2, in_dtype=dt, out_dtype=dt, use_graph=use_graph, lanes=lanes)
     res = pipe.run(sets, keep_results=True)
     again = pipe.run(sets[:2], keep_results=True)              # the ring is re-usable
     pipe.close()
