@@ -688,7 +688,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", choices=["b200", "reference"], default="b200")
     ap.add_argument("--workload", choices=sorted(WORKLOADS), default="c1")
-    ap.add_argument("--lanes", type=int, default=3, help="independent compute lanes per GPU (own plan, stream and graphs): job i runs on lane i mod lanes")
+    ap.add_argument("--lanes", type=int, default=4, help="independent compute lanes per GPU (own plan, stream and graphs): job i runs on lane i mod lanes")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline and oracle spot-check legs")
     ap.add_argument("--no-configs", action="store_true", help="skip the `configs` object (other BASELINE configurations)")
     args = ap.parse_args()

@@ -10,7 +10,7 @@ from sr459.driver import FrameSetPipeline
 n, h, w, K = 4, 1536, 2048, 50
 rng = np.random.default_rng(1)
 sets = [torch.from_numpy(rng.integers(0, 256, (n, h, w), dtype=np.uint8)).pin_memory() for _ in range(4)]
-for lanes, depth in ((1, 3), (2, 4), (2, 6), (3, 6)):
+for lanes, depth in ((1, 3), (2, 4), (3, 6), (4, 8)):
     pipe = FrameSetPipeline(n, h, w, NOMINAL, sr459.make_gaussian_psf(), K, depth=depth, in_dtype="u8", out_dtype="u8", use_graph=True, lanes=lanes)
     pipe.run([sets[i % 4] for i in range(8)])
     best = 1e9
