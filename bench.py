@@ -292,6 +292,39 @@ def time_config(sr459, torch, name, h, w, shifts, psf, iters, reps, peak, seed, 
         if r:                                        # replay 0 is the warm-up
             saa_ms.append(ev[0].elapsed_time(ev[1])); ibp_ms.append(ev[1].elapsed_time(ev[2]))
     errs = plan.errors(iters)
+    # the same job on `lanes` independent compute lanes at once (independent frame sets, as the reference's per-session loops):
+    # the kernels of these configurations are latency- or wave-bound one job at a time, concurrent jobs fill the machine
+    lanes = 4
+    lane = [dict(plan=plan, hr=hr, g=(g_saa, g_ibp), st=torch.cuda.Stream())]
+    for _ in range(lanes - 1):
+        pl = sr459.Plan(n, h, w, shifts, psf)
+        hl = torch.empty((H, W), dtype=torch.float32, device="cuda")
+        pl.saa(frames, out=hl); pl.ibp_(frames, hl, iters, want_errors=False)
+        torch.cuda.synchronize()
+        ga, gb = torch.cuda.CUDAGraph(), torch.cuda.CUDAGraph()
+        with torch.cuda.graph(ga, stream=cap):
+            pl.saa(frames, out=hl)
+        with torch.cuda.graph(gb, stream=cap):
+            pl.ibp_(frames, hl, iters, want_errors=False)
+        lane.append(dict(plan=pl, hr=hl, g=(ga, gb), st=torch.cuda.Stream()))
+    batch_ms = []
+    for r in range(reps + 1):
+        e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        e0.record()
+        for ln in lane:
+            ln["st"].wait_event(e0)
+            with torch.cuda.stream(ln["st"]):
+                ln["g"][0].replay(); ln["g"][1].replay()
+        for ln in lane:
+            ej = torch.cuda.Event(); ej.record(ln["st"]); torch.cuda.current_stream().wait_event(ej)
+        e1.record()
+        torch.cuda.synchronize()
+        if r:
+            batch_ms.append(e0.elapsed_time(e1))
+    t_batch = statistics.median(batch_ms)
+    for ln in lane[1:]:
+        ln["g"] = None
+        ln["plan"].close()
     plan.close()
     t_saa, t_ibp = statistics.median(saa_ms), statistics.median(ibp_ms)
     us_iter = 1e3 * t_ibp / iters
@@ -300,6 +333,9 @@ def time_config(sr459, torch, name, h, w, shifts, psf, iters, reps, peak, seed, 
         "workload": desc, "n_frames": n, "hr_shape": [H, W], "ibp_iterations": iters, "integer_hr_shifts": bool(sr459.Plan.shifts_are_integer(shifts)),
         "saa_us": 1e3 * t_saa, "us_per_iteration": us_iter, "job_ms": t_saa + t_ibp,
         "hr_mpix_per_s": H * W / 1e6 / ((t_saa + t_ibp) / 1e3),
+        "batch": {"lanes": lanes, "jobs": lanes, "ms": t_batch, "hr_mpix_per_s": lanes * H * W / 1e6 / (t_batch / 1e3),
+                  "speedup_vs_one_job_at_a_time": lanes * (t_saa + t_ibp) / t_batch,
+                  "note": "`lanes` independent frame sets of this configuration at once (own plan and stream each)"},
         "launches_per_iteration": (c2 - c1 - 1) / iters, "launches_saa": c1 - c0,
         "roofline": {"bound": "hbm", "algorithmic_bytes_per_iteration": alg_iter, "achieved": alg_iter / (us_iter * 1e-6) / 1e9,
                      "peak": peak, "unit": "GB/s", "frac": alg_iter / (us_iter * 1e-6) / 1e9 / peak},
