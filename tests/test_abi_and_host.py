@@ -165,3 +165,33 @@ def test_fir_back_projection_tables_match_scipy_shift_of_zero_inserted_data(lib)
         assert np.abs(got - ref).max() < 1e-4, (n_lr, s, np.abs(got - ref).max())
     small = np.zeros(20, dtype=np.int32)
     assert lib.sr459_fir_bp_axis(10, 2, 0.5, small.ctypes.data_as(C.POINTER(C.c_int)), w.ctypes.data_as(C.POINTER(C.c_float))) == -4
+
+
+def test_rank_core_pinning_partitions_the_allowed_cores():
+    """driver.pin_rank_to_cores: every rank of a node gets its own contiguous share of the cores the process may run on."""
+    import os
+    from importlib import import_module
+    D = import_module("enph459-super-resolution_b200.driver")
+    if not hasattr(os, "sched_getaffinity"):
+        pytest.skip("no CPU affinity API")
+    before = sorted(os.sched_getaffinity(0))
+    try:
+        assert D.pin_rank_to_cores(0, 1) is None and sorted(os.sched_getaffinity(0)) == before      # single rank: untouched
+        world = 2 if len(before) >= 2 else 1
+        got = []
+        for r in range(world):
+            os.sched_setaffinity(0, before)
+            rng = D.pin_rank_to_cores(r, world)
+            if world == 1:
+                assert rng is None
+                continue
+            mine = sorted(os.sched_getaffinity(0))
+            assert rng == [mine[0], mine[-1]] and len(mine) == len(before) // world
+            got.append(set(mine))
+        if world == 2:
+            assert not (got[0] & got[1])
+        os.sched_setaffinity(0, before)
+        assert D.pin_rank_to_cores(0, 10 * len(before)) is None                                     # fewer cores than ranks: untouched
+    finally:
+        os.sched_setaffinity(0, before)
+    assert D.shard_indices(10, 1, 4) == [1, 5, 9]
