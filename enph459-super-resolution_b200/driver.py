@@ -205,7 +205,10 @@ class BurstStream:
     """
 
     def __init__(self, n_frames, h, w, shifts_yx, kernel, n_iter, factor=2, step=ops.IBP_STEP_SIZE,
-                 depth=3, use_graph=False, device=None):
+                 depth=3, use_graph=False, device=None, lanes=1):
+        """lanes = 1: every job on one compute stream (lowest latency per set: a job has the GPU to itself).
+        lanes > 1: slot i computes on stream i mod lanes, so that the jobs of a free-running source overlap at their kernel
+        boundaries (higher sustained rate, longer latency per set while several sets are in flight)."""
         torch = ops._torch()
         self.torch = torch
         if device is not None:
@@ -215,6 +218,8 @@ class BurstStream:
         self.depth = int(depth)
         self.use_graph = bool(use_graph)
         self.s_h2d, self.s_cmp, self.s_d2h = (torch.cuda.Stream() for _ in range(3))
+        self.lanes = max(1, min(int(lanes), self.depth))
+        self.s_lane = [self.s_cmp] + [torch.cuda.Stream() for _ in range(self.lanes - 1)]
         self.slots = []
         for _ in range(self.depth):
             plan = ops.Plan(n_frames, h, w, shifts_yx, kernel, factor, step)     # one plan per slot: graphs bake pointers
@@ -242,7 +247,7 @@ class BurstStream:
         if self.use_graph:
             for slot in self.slots:
                 g = torch.cuda.CUDAGraph()
-                with torch.cuda.graph(g, stream=self.s_cmp):
+                with torch.cuda.graph(g, stream=self.s_lane[self.slots.index(slot) % self.lanes]):
                     self._job(slot)
                 slot["graph"] = g
 
@@ -286,14 +291,15 @@ class BurstStream:
             return None
         slot["t_commit"] = time.perf_counter()
         slot["set_index"] = set_idx
-        with torch.cuda.stream(self.s_cmp):
-            self.s_cmp.wait_event(slot["ev_in"])
-            self.s_cmp.wait_event(slot["ev_out"])            # previous read-back of this slot's out buffer
+        s_cmp = self.s_lane[(set_idx % self.depth) % self.lanes]
+        with torch.cuda.stream(s_cmp):
+            s_cmp.wait_event(slot["ev_in"])
+            s_cmp.wait_event(slot["ev_out"])                 # previous read-back of this slot's out buffer
             if slot["graph"] is not None:
                 slot["graph"].replay()
             else:
                 self._job(slot)
-            slot["ev_cmp"].record(self.s_cmp)
+            slot["ev_cmp"].record(s_cmp)
         with torch.cuda.stream(self.s_d2h):
             self.s_d2h.wait_event(slot["ev_cmp"])
             slot["host_out"].copy_(slot["out"], non_blocking=True)

@@ -696,15 +696,16 @@ def test_row_bands_peer_memory_graph_replay_two_gpus(sr):
         p.close()
 
 
+@pytest.mark.parametrize("lanes", [1, 2])
 @pytest.mark.parametrize("use_graph", [False, True])
-def test_burst_stream_matches_oracle(sr, use_graph):
-    """Streaming burst mode (config 5): frames committed one by one, uint8 HR images out, ring re-use."""
+def test_burst_stream_matches_oracle(sr, use_graph, lanes):
+    """Streaming burst mode (config 5): frames committed one by one, uint8 HR images out, ring re-use, one or two compute lanes."""
     from sr459.driver import BurstStream
     rng = np.random.default_rng(55)
     h, w, K = 48, 64, 5
     psf = O.make_gaussian_psf()
     sets = [[rng.integers(0, 256, (h, w), dtype=np.uint8) for _ in NOMINAL] for _ in range(5)]
-    bs = BurstStream(4, h, w, NOMINAL, psf, K, depth=2, use_graph=use_graph)
+    bs = BurstStream(4, h, w, NOMINAL, psf, K, depth=2, use_graph=use_graph, lanes=lanes)
     got = []
     for i, frames in enumerate(sets):
         for k, f in enumerate(frames):
