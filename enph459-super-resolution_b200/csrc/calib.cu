@@ -410,14 +410,12 @@ __global__ void __launch_bounds__(256) k_radial(const double* data, int h, int w
     if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = mx;
     __syncthreads();
     mx = red[0]; for (int i = 1; i < 8; ++i) mx = fmax(mx, red[i]);
-    const double inv = mx > 0.0 ? 1.0 / mx : 1.0;
     for (int t = threadIdx.x; t < h * w; t += 256) {
         const int yy = t / w, xx = t - yy * w;
         const double dx = xx - cx, dy = yy - cy;
         const int ring = (int)sqrt(dx * dx + dy * dy);
-        if (ring < max_radius) { atomicAdd(&tot[ring], data[t] / mx * (mx > 0.0 ? 1.0 : 0.0) + (mx > 0.0 ? 0.0 : data[t])); atomicAdd(&cnt[ring], 1.0); }
+        if (ring < max_radius) { atomicAdd(&tot[ring], mx > 0.0 ? data[t] / mx : data[t]); atomicAdd(&cnt[ring], 1.0); }   // mtf_2d /= mtf_2d.max()
     }
-    (void)inv;
     __syncthreads();
     for (int i = threadIdx.x; i < max_radius; i += 256) prof[i] = cnt[i] > 0.0 ? tot[i] / cnt[i] : 0.0;
     if (threadIdx.x == 0 && peak_out) *peak_out = mx;

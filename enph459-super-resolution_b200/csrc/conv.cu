@@ -180,7 +180,6 @@ __global__ void __launch_bounds__(128) k_corr7(const __grid_constant__ Corr7Args
     #pragma unroll
     for (int step = 0; step < C7_RPW; ++step) {
         {   // the 7th row of this step's window
-            constexpr int dummy = 0; (void)dummy;
             #pragma unroll
             for (int q = 0; q < 3; ++q) {
                 const float4 v = *reinterpret_cast<const float4*>(col + (step + 6) * C7_SW + 4 * q);
