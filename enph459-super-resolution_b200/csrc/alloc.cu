@@ -8,6 +8,7 @@
 // out-of-range READ that matters pulls the pattern (0xC3C3C3C3 = -391.5f) into the result and fails parity.
 #include "internal.h"
 
+#include <stdio.h>
 #include <stdlib.h>
 #include <string.h>
 #include <map>
@@ -22,6 +23,19 @@ std::mutex g_mu;
 std::map<void*, Block> g_blocks;                  // user pointer -> block (guard mode only)
 size_t g_guard = []() -> size_t { const char* e = getenv("SR459_GUARD"); return e ? (size_t)atol(e) : 0; }();
 constexpr unsigned char kPattern = 0xC3;
+int g_bad_at_free = 0;                            // blocks released with a damaged band since the last check (guard mode)
+char g_bad_msg[160] = "";
+
+// both bands of one block, read back; true if any byte differs from the pattern (offset relative to the user pointer in *at)
+bool bands_damaged(const Block& b, long* at) {
+    const size_t user = (b.bytes + 255) & ~(size_t)255;
+    std::vector<unsigned char> host(user + 2 * b.guard);
+    if (cudaDeviceSynchronize() != cudaSuccess) return false;
+    if (cudaMemcpy(host.data(), b.base, host.size(), cudaMemcpyDeviceToHost) != cudaSuccess) return false;
+    for (size_t i = 0; i < b.guard; ++i) if (host[i] != kPattern) { *at = (long)i - (long)b.guard; return true; }
+    for (size_t i = b.guard + b.bytes; i < host.size(); ++i) if (host[i] != kPattern) { *at = (long)(i - b.guard); return true; }
+    return false;
+}
 }  // namespace
 
 cudaError_t gmalloc(void** p, size_t bytes) {
@@ -48,7 +62,16 @@ void gfree(void* p) {
     {
         std::lock_guard<std::mutex> lk(g_mu);
         auto it = g_blocks.find(p);
-        if (it != g_blocks.end()) { p = it->second.base; g_blocks.erase(it); }
+        if (it != g_blocks.end()) {
+            // entry points that free their scratch before returning (calib.cu, analysis.cu, the stand-alone operators) would
+            // otherwise never have their bands looked at: check them on release (guard mode only: this synchronises the device)
+            long at = 0;
+            if (bands_damaged(it->second, &at)) {
+                if (!g_bad_at_free) snprintf(g_bad_msg, sizeof(g_bad_msg), "guard band of a released %zu-byte allocation was written at byte offset %ld", it->second.bytes, at);
+                ++g_bad_at_free;
+            }
+            p = it->second.base; g_blocks.erase(it);
+        }
     }
     cudaFree(p);
 }
@@ -100,6 +123,10 @@ int sr459_debug_check_guards(void) {
         }
     }
     cudaSetDevice(prev);
+    {
+        std::lock_guard<std::mutex> lk(g_mu);
+        if (g_bad_at_free) { if (!bad) set_error("%s", g_bad_msg); bad += g_bad_at_free; g_bad_at_free = 0; }
+    }
     return bad;
 }
 

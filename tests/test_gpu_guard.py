@@ -58,6 +58,8 @@ CASES = [
     ("ws", NOMINAL, "gauss", (77, 116), 4),
     ("auto-two-lattices", MONOCAL, "gauss", (77, 116), 0),
     ("auto-four-lattices", FOUR, "gauss", (61, 100), 0),
+    ("stream-ml-one-strip", MONOCAL, "gauss", (9, 20), 7),
+    ("stream-ml-three-lattices", FOUR[:3], "gauss", (130, 60), 7),
     ("fast-k7", NOMINAL, "k7", (77, 116), 3),
     ("auto-k7", MONOCAL, "k7", (77, 116), 0),
     ("dense-odd-width", NOMINAL, "gauss", (33, 47), 2),
@@ -125,3 +127,33 @@ def test_guard_band_checker_detects_an_overrun(sr, guarded):
     assert guarded.sr459_debug_poke_guard(1) == 0
     assert guarded.sr459_debug_check_guards() == 0
     plan.close()
+
+
+def test_guard_bands_intact_for_the_analytics_and_calibration_kernels(sr, guarded):
+    """csrc/analysis.cu and csrc/calib.cu allocate their scratch through the same guarded allocator: ragged ROI / image sizes,
+    peaks at the image border (clipped ROIs), then every band must be intact (the entry points free their scratch, so the bands are
+    checked by the allocator when they are released: sr459_debug_check_guards also reports bands damaged at free time)."""
+    import torch
+    from sr459 import analysis, calibration
+    rng = np.random.default_rng(17)
+    n = 150
+    yy, xx = np.mgrid[:n, :n].astype(np.float64)
+    d = (xx - n / 2) * np.cos(0.3) + (yy - n / 2) * np.sin(0.3)
+    roi = (np.where(np.abs(d) < 6, 40.0, 205.0) + rng.normal(0, 1.5, (n, n))).astype(np.float32)
+    full = torch.full((n + 37, n + 53), 200.0, device="cuda")
+    full[11:11 + n, 29:29 + n] = torch.from_numpy(roi).cuda()
+    r = analysis.edge_mtf(full, (slice(11, 11 + n), slice(29, 29 + n)), "left")
+    assert r["mtf50"] > 0 and len(r["esf_x"]) > 30
+    analysis.local_contrast(rng.uniform(0, 255, 333), 20)
+    H, W = 97, 131
+    stack = rng.integers(0, 30, (5, H, W)).astype(np.uint8)
+    yy, xx = np.mgrid[:H, :W]
+    for k, (pr, pc) in enumerate([(2, 3), (50, 60), (H - 1, W - 1), (0, 70), (60, 0)]):
+        stack[k] = np.clip(stack[k] + 210 * np.exp(-((yy - pr) ** 2 + (xx - pc) ** 2) / 7.0), 0, 255).astype(np.uint8)
+    res = calibration.find_pinhole_centers(stack)
+    assert res["center"].shape == (5, 2) and np.isfinite(res["center"]).all()
+    calibration.compute_mtf(calibration.extract_psf(stack[1].astype(np.float64), (50, 60), 15), 3.45)
+    torch.cuda.synchronize()
+    bad = guarded.sr459_debug_check_guards()
+    assert bad == 0, guarded.sr459_last_error().decode()
+    assert torch.equal(full[:11], torch.full((11, n + 53), 200.0, device="cuda"))          # the image around the ROI is untouched
