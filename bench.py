@@ -616,6 +616,13 @@ def run_b200_arm(args):
     if world > 1:
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
     total_ms, ibp_ms_max, e2e8_ms, e2e8_worst_ms, single_ms = [float(x) for x in t.tolist()]
+    # every rank's own figures beside the max-over-ranks ones (a box whose GPUs do not all sit behind the same PCIe path shows up here)
+    mine = torch.tensor([e2e8_s * 1e3 / args.steps, start2.elapsed_time(end2) / args.steps], dtype=torch.float64, device="cuda")
+    per_rank = [mine.clone() for _ in range(world)]
+    if world > 1:
+        dist.all_gather(per_rank, mine)
+    per_rank_e2e_ms = [round(float(x[0]), 4) for x in per_rank]
+    per_rank_step_ms = [round(float(x[1]), 4) for x in per_rank]
 
     hr_mpix = H * W / 1e6
     value = world * args.steps * hr_mpix / (total_ms / 1e3)
@@ -639,7 +646,7 @@ def run_b200_arm(args):
         "ms_per_step": total_ms / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
         "dtype": "f32", "data": "synthetic",
         "config": workload_config(n, h, w, iters, world),
-        "lanes": L,
+        "lanes": L, "per_rank_ms_per_step": per_rank_step_ms,
         "single_lane": {"value": world * args.steps * hr_mpix / (single_ms / 1e3), "ms_per_step": single_ms / args.steps,
                         "note": "the same K jobs one at a time on one stream; stage_ms and roofline.launch_ms are measured in this pass"},
         "stage_ms": {"saa": saa_ms, "ibp": ibp_ms, "ibp_per_iteration": k_ms},
@@ -655,7 +662,7 @@ def run_b200_arm(args):
                              "in the 126 MB L2: ncu counts `traffic` DRAM bytes per launch (cold L2), dram_achieved = traffic / launch time"},
         "e2e": {"value": world * args.steps * hr_mpix / (e2e8_ms / 1e3), "unit": UNIT, "h2d_bytes_per_step": pipe8.h2d_bytes,
                 "d2h_bytes_per_step": pipe8.d2h_bytes, "ms_per_step": e2e8_ms / args.steps, "latency_ms_p50": 1e3 * statistics.median(lat8),
-                "runs": 3, "jobs_per_run": e2e_jobs, "cpu_affinity": cpu_aff, "worst_run_value": world * args.steps * hr_mpix / (e2e8_worst_ms / 1e3),
+                "runs": 3, "jobs_per_run": e2e_jobs, "per_rank_ms_per_step": per_rank_e2e_ms, "cpu_affinity": cpu_aff, "worst_run_value": world * args.steps * hr_mpix / (e2e8_worst_ms / 1e3),
                 "api": "sr459.driver.FrameSetPipeline.run(in_dtype='u8', out_dtype='u8'): run_sr.py's own I/O formats -- pinned uint8 frames in "
                        "(load_gray, :73-75), uint8 HR image out (clip + truncation, :303), conversions on the device; 2 jobs in flight on each of `lanes` compute lanes, "
                        "one CUDA-graph replay per job; median of 3 runs of `jobs_per_run` jobs each, reported per `steps` jobs (max over ranks of each rank's median)"},
